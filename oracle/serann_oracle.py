@@ -247,8 +247,12 @@ def _bn_infer(x, gamma, beta, mov_mean, mov_var):
     return q(q(x * inv) + shift)
 
 
-def forward(ind: Individual, x_img: torch.Tensor, g_in: torch.Tensor, training: bool) -> torch.Tensor:
-    """Returns the fused head logits (B, n_classes + genotype_size), fp16-valued."""
+def forward(ind: Individual, x_img: torch.Tensor, g_in: torch.Tensor, training: bool,
+            tape: Optional[Dict[int, torch.Tensor]] = None) -> torch.Tensor:
+    """Returns the fused head logits (B, n_classes + genotype_size), fp16-valued.
+
+    ``tape`` (optional) receives every layer output by tensor id, with ``retain_grad`` set, so the
+    parity tests can compare activations and activation gradients layer by layer."""
     t: Dict[int, torch.Tensor] = {0: x_img, 1: g_in}
     for i, (l, ps) in enumerate(zip(ind.ir.layers, ind.params)):
         x = t[l.inputs[0]]
@@ -265,6 +269,10 @@ def forward(ind: Individual, x_img: torch.Tensor, g_in: torch.Tensor, training: 
         else:
             raise ValueError(l.kind)
         t[2 + i] = y
+        if tape is not None:
+            if y.requires_grad:
+                y.retain_grad()
+            tape[2 + i] = y
     return t[1 + len(ind.ir.layers)].reshape(x_img.shape[0], -1)
 
 
@@ -333,14 +341,15 @@ def prepare_inputs(x: np.ndarray, g_bits: np.ndarray):
     return xi, gi
 
 
-def train_step(ind: Individual, xi, gi, labels, bits, t: int):
-    logits = forward(ind, xi, gi, training=True)
+def train_step(ind: Individual, xi, gi, labels, bits, t: int, tape=None, apply_adam: bool = True):
+    logits = forward(ind, xi, gi, training=True, tape=tape)
     ce, mse, correct, _ = losses(logits, labels, bits, ind.ir.n_classes)
     total, lc, lr = weighted_loss(ce, mse, ind.ir.loss_balance)
     total.backward()
-    adam_step(ind, t)
-    return {'loss': float(total), 'ce': float(lc), 'mse': float(lr), 'correct': int(correct.sum()),
-            'logits': logits.detach()}
+    if apply_adam:
+        adam_step(ind, t)
+    return {'loss': float(total.detach()), 'ce': float(lc.detach()), 'mse': float(lr.detach()),
+            'correct': int(correct.sum()), 'logits': logits.detach()}
 
 
 def evaluate(ind: Individual, x, g_bits, labels, chunk: int):
@@ -421,6 +430,13 @@ def readout(probs: np.ndarray, parent_bits: np.ndarray):
 
 # --------------------------------------------------------------------------- ribosomal autoencoder decode
 
+def _bn_affine_f32(x, w, name):
+    """tf.nn.batch_normalization, inference: x * inv + (beta - mean * inv), inv = rsqrt(var + eps) * gamma."""
+    f = lambda k: torch.tensor(np.asarray(w[f'{name}_{k}'], dtype=np.float32))
+    inv = (1.0 / torch.sqrt(f('var') + np.float32(1e-3))) * f('gamma')
+    return x * inv + (f('beta') - f('mean') * inv)
+
+
 def ae_decode(genotypes: np.ndarray, w: Dict[str, np.ndarray], max_tokens: int, vocab: int) -> np.ndarray:
     """fp32 ``generative_net`` in inference mode + argmax (ribosomal_autoencoder.py:122-124;
     model.py:35-48): one_hot -> Conv1D(32, 5) -> BN -> Flatten -> Dense -> Reshape -> BN -> argmax.
@@ -435,10 +451,8 @@ def ae_decode(genotypes: np.ndarray, w: Dict[str, np.ndarray], max_tokens: int, 
         k = torch.tensor(w['conv_kernel'], dtype=torch.float32)                       # (5, 2, 32)
         h = F.conv1d(oh.permute(0, 2, 1), k.permute(2, 1, 0)) + torch.tensor(w['conv_bias'])[None, :, None]
         h = h.permute(0, 2, 1)                                                        # (n, 96, 32)
-        h = (h - torch.tensor(w['bn1_mean'])) / torch.sqrt(torch.tensor(w['bn1_var']) + 1e-3) \
-            * torch.tensor(w['bn1_gamma']) + torch.tensor(w['bn1_beta'])
+        h = _bn_affine_f32(h, w, 'bn1')
         z = h.reshape(len(gen), -1) @ torch.tensor(w['dense_kernel']) + torch.tensor(w['dense_bias'])
         z = z.reshape(len(gen), max_tokens, vocab)
-        z = (z - torch.tensor(w['bn2_mean'])) / torch.sqrt(torch.tensor(w['bn2_var']) + 1e-3) \
-            * torch.tensor(w['bn2_gamma']) + torch.tensor(w['bn2_beta'])
+        z = _bn_affine_f32(z, w, 'bn2')
         return z.argmax(dim=-1).numpy().astype(np.int64), z.numpy()

@@ -1,0 +1,1027 @@
+// SeRANN population engine: host side of the C ABI in include/serann_b200.h.
+//
+// One engine = one GPU = one shard of the population.  srn_build turns the flat per-individual layer
+// lists into (a) packed arenas - fp16 parameters, fp16 Adam slots, fp32 gradient accumulators,
+// fp16 activations and activation gradients - and (b) a launch plan: layers of all individuals are
+// bucketed by (depth, kind, tile shape) and every bucket is ONE kernel launch over a device table of
+// problems.  A training step is then ~3 launches per bucket regardless of the population size.
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <random>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "../../include/serann_b200.h"
+#include "srn_gemm_simt.cuh"
+#include "srn_kernels.cuh"
+#include "srn_host.h"
+
+namespace srn {
+
+thread_local std::string g_error;
+std::atomic<unsigned long long> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_error = buf;
+    return code;
+}
+
+static inline float h16(float x) { return __half2float(__float2half_rn(x)); }
+
+enum Pass { P_FWD = 0, P_DGRAD, P_WGRAD, P_COL, P_BWD_EW, P_COUNT };
+
+struct Tensor {
+    int H = 0, W = 0, C = 0;
+    long long elems = 0;       // per sample
+    int root = -1;             // tensor whose storage this one views
+    bool needs_grad = false;
+    int depth = 0;
+    int consumers = 0;         // consumers needing din (counted on the root)
+    long long act_off = -1, grad_off = -1;   // offsets into the activation arena (elements)
+    __half* act = nullptr;
+    __half* grad = nullptr;
+};
+
+struct LayerRt {
+    srn_layer_desc d;
+    long long w_off = -1, w_cnt = 0, b_off = -1, b_cnt = 0;   // trainable arena (elements)
+    long long mov_off = -1;                                   // moving-statistics arena
+    long long save_off = -1;                                  // fp32 BN scratch arena
+};
+
+struct Indiv {
+    std::vector<LayerRt> layers;
+    std::vector<Tensor> tensors;
+    float lb = 0.f;
+    long long pcount = 0;
+};
+
+struct Cached {
+    int* prefix[P_COUNT] = {};
+    int total[P_COUNT] = {};
+};
+
+struct Group {
+    int depth, kind, cfgF, cfgC, ordinal;
+    std::vector<Prob> h;
+    Prob* d = nullptr;
+    std::map<int, Cached> cache;
+};
+
+}  // namespace srn
+
+using namespace srn;
+
+struct ProfRec { int cat; cudaEvent_t a, b; };
+
+struct srn_engine {
+    bool profiling = false;
+    std::vector<ProfRec*> prof;
+    srn_config cfg{};
+    cudaStream_t stream = 0;
+    int xe = 0, G = 0, ncls = 0, NL = 0;
+    // dataset
+    __half* x[2] = {nullptr, nullptr};
+    uint8_t* y[2] = {nullptr, nullptr};
+    uint8_t* gb[2] = {nullptr, nullptr};
+    int nrows[2] = {0, 0};
+    // staging
+    __half* xin = nullptr; __half* gin = nullptr; uint8_t* lab = nullptr;
+    // population
+    int n = 0;
+    std::vector<Indiv> inds;
+    std::vector<Group> groups;
+    Prob* d_loss = nullptr; std::vector<Prob> h_loss;
+    float* d_lb = nullptr;
+    __half *P = nullptr, *M = nullptr, *V = nullptr, *S = nullptr, *act = nullptr;
+    float *Gr = nullptr, *save = nullptr;
+    long long p_elems = 0, s_elems = 0, act_elems = 0, save_elems = 0;
+    long long device_bytes = 0;
+    int adam_t = 0;
+    bool built = false;
+    // metric buffers
+    int* met_correct = nullptr; float* met_ce = nullptr; float* met_mse = nullptr; long long met_slots = 0;
+    std::vector<int*> scratch_prefix;   // all cached prefix arrays, for cleanup
+};
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) return fail(SRN_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+// every launch is counted and, when profiling is on, bracketed by CUDA events tagged with its category
+#define LAUNCH(cat, kern, grid, block, ...)                                                        \
+    do {                                                                                           \
+        if (grid_nonzero(grid)) {                                                                          \
+            ProfRec* pr_ = h->profiling ? prof_begin(h, (cat)) : nullptr;                          \
+            kern<<<(grid), (block), 0, h->stream>>>(__VA_ARGS__);                                  \
+            if (pr_) cudaEventRecord(pr_->b, h->stream);                                           \
+            g_launches.fetch_add(1, std::memory_order_relaxed);                                    \
+        }                                                                                          \
+    } while (0)
+
+static inline bool grid_nonzero(unsigned g) { return g > 0; }
+static inline bool grid_nonzero(int g) { return g > 0; }
+static inline bool grid_nonzero(const dim3& g) { return g.x > 0 && g.y > 0 && g.z > 0; }
+
+static ProfRec* prof_begin(srn_engine* h, int cat) {
+    ProfRec* r = new ProfRec();
+    r->cat = cat;
+    cudaEventCreate(&r->a);
+    cudaEventCreate(&r->b);
+    cudaEventRecord(r->a, h->stream);
+    h->prof.push_back(r);
+    return r;
+}
+
+extern "C" const char* srn_last_error(void) { return g_error.c_str(); }
+extern "C" uint64_t srn_launch_count(void) { return g_launches.load(); }
+
+// ------------------------------------------------------------------ create / destroy
+static void free_population(srn_engine* h) {
+    for (auto& g : h->groups) cudaFree(g.d);
+    for (int* p : h->scratch_prefix) cudaFree(p);
+    h->scratch_prefix.clear();
+    h->groups.clear();
+    h->inds.clear();
+    cudaFree(h->d_loss); h->d_loss = nullptr;
+    cudaFree(h->d_lb); h->d_lb = nullptr;
+    cudaFree(h->P); cudaFree(h->M); cudaFree(h->V); cudaFree(h->S); cudaFree(h->act); cudaFree(h->Gr); cudaFree(h->save);
+    h->P = h->M = h->V = h->S = h->act = nullptr; h->Gr = h->save = nullptr;
+    cudaFree(h->met_correct); cudaFree(h->met_ce); cudaFree(h->met_mse);
+    h->met_correct = nullptr; h->met_ce = h->met_mse = nullptr; h->met_slots = 0;
+    h->built = false; h->n = 0; h->device_bytes = 0;
+}
+
+extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
+    if (!cfg || !out) return fail(SRN_ERR_ARG, "srn_create: null argument");
+    if (cfg->image_h <= 0 || cfg->image_w <= 0 || cfg->genotype_size <= 0 || cfg->n_classes <= 0 || cfg->max_batch <= 0)
+        return fail(SRN_ERR_ARG, "srn_create: non-positive dimension");
+    if (cfg->n_classes > 255) return fail(SRN_ERR_LIMIT, "srn_create: n_classes > 255");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(SRN_ERR_CUDA, "srn_create: no CUDA device (%s); this engine has no CPU path", cudaGetErrorString(e));
+    if (cfg->device < 0 || cfg->device >= count) return fail(SRN_ERR_ARG, "srn_create: device %d of %d", cfg->device, count);
+    CK(cudaSetDevice(cfg->device));
+    srn_engine* h = new srn_engine();
+    h->cfg = *cfg;
+    h->xe = cfg->image_h * cfg->image_w;
+    h->G = cfg->genotype_size;
+    h->ncls = cfg->n_classes;
+    h->NL = h->ncls + h->G;
+    CK(cudaMalloc(&h->xin, (size_t)cfg->max_batch * h->xe * sizeof(__half)));
+    CK(cudaMalloc(&h->gin, (size_t)cfg->max_batch * h->G * sizeof(__half)));
+    CK(cudaMalloc(&h->lab, (size_t)cfg->max_batch));
+    *out = h;
+    return SRN_OK;
+}
+
+extern "C" void srn_destroy(srn_engine* h) {
+    if (!h) return;
+    cudaSetDevice(h->cfg.device);
+    cudaDeviceSynchronize();
+    free_population(h);
+    for (int s = 0; s < 2; ++s) { cudaFree(h->x[s]); cudaFree(h->y[s]); cudaFree(h->gb[s]); }
+    cudaFree(h->xin); cudaFree(h->gin); cudaFree(h->lab);
+    delete h;
+}
+
+extern "C" int srn_set_dataset(srn_engine* h, const float* x_train, const uint8_t* y_train, const uint8_t* g_train,
+                               int32_t n_train, const float* x_test, const uint8_t* y_test, const uint8_t* g_test,
+                               int32_t n_test) {
+    if (!h) return fail(SRN_ERR_ARG, "null engine");
+    CK(cudaSetDevice(h->cfg.device));
+    const float* xs[2] = {x_train, x_test};
+    const uint8_t* ys[2] = {y_train, y_test};
+    const uint8_t* gs[2] = {g_train, g_test};
+    const int ns[2] = {n_train, n_test};
+    for (int s = 0; s < 2; ++s) {
+        cudaFree(h->x[s]); cudaFree(h->y[s]); cudaFree(h->gb[s]);
+        h->x[s] = nullptr; h->y[s] = nullptr; h->gb[s] = nullptr; h->nrows[s] = 0;
+        if (ns[s] <= 0) continue;
+        if (!xs[s] || !gs[s]) return fail(SRN_ERR_ARG, "srn_set_dataset: null array for split %d", s);
+        const long long ne = (long long)ns[s] * h->xe;
+        float* tmp = nullptr;
+        CK(cudaMalloc(&tmp, ne * sizeof(float)));
+        CK(cudaMemcpy(tmp, xs[s], ne * sizeof(float), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&h->x[s], ne * sizeof(__half)));
+        LAUNCH(SRN_CAT_OTHER, k_f32_to_f16, (unsigned)((ne + 255) / 256), 256, tmp, h->x[s], ne);
+        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaFree(tmp));
+        CK(cudaMalloc(&h->y[s], ns[s]));
+        if (ys[s]) CK(cudaMemcpy(h->y[s], ys[s], ns[s], cudaMemcpyHostToDevice));
+        else CK(cudaMemset(h->y[s], 0, ns[s]));
+        CK(cudaMalloc(&h->gb[s], (size_t)ns[s] * h->G));
+        CK(cudaMemcpy(h->gb[s], gs[s], (size_t)ns[s] * h->G, cudaMemcpyHostToDevice));
+        h->nrows[s] = ns[s];
+    }
+    return SRN_OK;
+}
+
+// ------------------------------------------------------------------ build
+static inline long long align_up(long long v, long long a) { return (v + a - 1) / a * a; }
+
+static int cfg_for(int n) { return n <= 16 ? 2 : (n <= 32 ? 1 : 0); }
+static const int CFG_BM[3] = {64, 128, 256};
+static const int CFG_BN[3] = {64, 32, 16};
+
+static bool has_params(int kind) { return kind == SRN_KIND_DENSE || kind == SRN_KIND_CONV || kind == SRN_KIND_BN; }
+
+static int validate_layer(const srn_layer_desc& d, const std::vector<Tensor>& ts, int li) {
+    if (d.n_in < 1 || d.n_in > SRN_MAX_CONCAT_INPUTS) return fail(SRN_ERR_UNSUPPORTED, "layer %d: %d inputs", li, d.n_in);
+    for (int j = 0; j < d.n_in; ++j)
+        if (d.in[j] < 0 || d.in[j] >= (int)ts.size()) return fail(SRN_ERR_ARG, "layer %d: input id %d out of range", li, d.in[j]);
+    if (d.kind != SRN_KIND_CONCAT && d.n_in != 1) return fail(SRN_ERR_ARG, "layer %d: needs exactly one input", li);
+    const Tensor& t0 = ts[d.in[0]];
+    const long long in_e = (long long)d.in_h * d.in_w * d.in_c, out_e = (long long)d.out_h * d.out_w * d.out_c;
+    if (in_e <= 0 || out_e <= 0) return fail(SRN_ERR_ARG, "layer %d: empty tensor", li);
+    if (d.kind != SRN_KIND_CONCAT && in_e != t0.elems) return fail(SRN_ERR_ARG, "layer %d: input has %lld elements, descriptor says %lld", li, t0.elems, in_e);
+    switch (d.kind) {
+        case SRN_KIND_DENSE:
+            if (d.units <= 0 || d.out_c != d.units || d.out_h * d.out_w != d.in_h * d.in_w) return fail(SRN_ERR_ARG, "layer %d: bad Dense shape", li);
+            break;
+        case SRN_KIND_CONV:
+            if (d.units <= 0 || d.out_c != d.units || d.kh <= 0 || d.kw <= 0 || d.sh <= 0 || d.sw <= 0 ||
+                d.in_h < d.kh || d.in_w < d.kw || d.out_h != (d.in_h - d.kh) / d.sh + 1 || d.out_w != (d.in_w - d.kw) / d.sw + 1)
+                return fail(SRN_ERR_ARG, "layer %d: bad convolution shape", li);
+            break;
+        case SRN_KIND_MAXPOOL:
+            if (d.kh <= 0 || d.kw <= 0 || d.sh <= 0 || d.sw <= 0 || d.in_h < d.kh || d.in_w < d.kw || d.out_c != d.in_c ||
+                d.out_h != (d.in_h - d.kh) / d.sh + 1 || d.out_w != (d.in_w - d.kw) / d.sw + 1)
+                return fail(SRN_ERR_ARG, "layer %d: bad pooling shape", li);
+            break;
+        case SRN_KIND_BN:
+        case SRN_KIND_RESHAPE:
+            if (in_e != out_e) return fail(SRN_ERR_ARG, "layer %d: element count changes", li);
+            if (d.kind == SRN_KIND_BN && d.in_c != d.out_c) return fail(SRN_ERR_ARG, "layer %d: BN channels", li);
+            break;
+        case SRN_KIND_CONCAT: {
+            long long csum = 0;
+            for (int j = 0; j < d.n_in; ++j) {
+                const Tensor& t = ts[d.in[j]];
+                const long long rows = (long long)d.out_h * d.out_w;
+                if (t.elems % rows) return fail(SRN_ERR_ARG, "layer %d: concat rows mismatch", li);
+                csum += t.elems / rows;
+            }
+            if (csum != d.out_c) return fail(SRN_ERR_ARG, "layer %d: concat channels %lld != %d", li, csum, d.out_c);
+            break;
+        }
+        default:
+            return fail(SRN_ERR_UNSUPPORTED, "layer %d: kind %d", li, d.kind);
+    }
+    return SRN_OK;
+}
+
+extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int32_t* off, const float* loss_balance,
+                         int32_t n, uint64_t seed) {
+    if (!h || !layers || !off || !loss_balance || n <= 0) return fail(SRN_ERR_ARG, "srn_build: bad argument");
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    free_population(h);
+    const int MB = h->cfg.max_batch;
+    h->inds.resize(n);
+    long long p_off = 0, s_off = 0, a_off = 0, sv_off = 0;
+    // ---- pass 1: tensors, parameter offsets, sizes
+    for (int i = 0; i < n; ++i) {
+        Indiv& ind = h->inds[i];
+        ind.lb = loss_balance[i];
+        const int nl = off[i + 1] - off[i];
+        if (nl <= 0) return fail(SRN_ERR_ARG, "individual %d has no layers", i);
+        ind.layers.resize(nl);
+        ind.tensors.resize(2 + nl);
+        Tensor& tx = ind.tensors[0]; tx.H = h->cfg.image_h; tx.W = h->cfg.image_w; tx.C = 1; tx.elems = h->xe; tx.root = 0;
+        Tensor& tg = ind.tensors[1]; tg.H = h->G; tg.W = 1; tg.C = 1; tg.elems = h->G; tg.root = 1;
+        for (int l = 0; l < nl; ++l) {
+            LayerRt& L = ind.layers[l];
+            L.d = layers[off[i] + l];
+            const srn_layer_desc& d = L.d;
+            std::vector<Tensor> visible(ind.tensors.begin(), ind.tensors.begin() + 2 + l);
+            int rc = validate_layer(d, visible, l);
+            if (rc) { std::string m = g_error; return fail(rc, "individual %d: %s", i, m.c_str()); }
+            Tensor& to = ind.tensors[2 + l];
+            to.H = d.out_h; to.W = d.out_w; to.C = d.out_c; to.elems = (long long)d.out_h * d.out_w * d.out_c;
+            bool ng = has_params(d.kind);
+            int depth = 0;
+            for (int j = 0; j < d.n_in; ++j) { ng = ng || ind.tensors[d.in[j]].needs_grad; depth = std::max(depth, ind.tensors[d.in[j]].depth); }
+            to.needs_grad = ng;
+            if (d.kind == SRN_KIND_RESHAPE) { to.root = ind.tensors[d.in[0]].root; to.depth = depth; }
+            else { to.root = 2 + l; to.depth = depth + 1; }
+            if (d.kind == SRN_KIND_DENSE || d.kind == SRN_KIND_CONV) {
+                L.w_cnt = (long long)d.kh * d.kw * d.in_c * d.units; L.b_cnt = d.units;
+                if (d.kind == SRN_KIND_DENSE) L.w_cnt = (long long)d.in_c * d.units;
+                L.w_off = p_off; p_off = align_up(p_off + L.w_cnt, 8);
+                L.b_off = p_off; p_off = align_up(p_off + L.b_cnt, 8);
+                ind.pcount += L.w_cnt + L.b_cnt;
+            } else if (d.kind == SRN_KIND_BN) {
+                L.w_cnt = L.b_cnt = d.in_c;
+                L.w_off = p_off; p_off = align_up(p_off + L.w_cnt, 8);
+                L.b_off = p_off; p_off = align_up(p_off + L.b_cnt, 8);
+                L.mov_off = s_off; s_off = align_up(s_off + 2LL * d.in_c, 8);
+                const long long rows_max = (long long)MB * d.in_h * d.in_w;
+                L.save_off = sv_off; sv_off += 4LL * d.in_c + 2LL * d.in_c * col_chunks(rows_max);
+                ind.pcount += 4LL * d.in_c;
+            }
+        }
+        if (ind.tensors.back().elems != h->NL)
+            return fail(SRN_ERR_ARG, "individual %d: last layer must emit n_classes + genotype_size = %d values, has %lld", i, h->NL, ind.tensors.back().elems);
+        // storage: every root tensor except the two inputs gets activations; grads where needed
+        for (size_t t = 2; t < ind.tensors.size(); ++t) {
+            Tensor& T = ind.tensors[t];
+            if (T.root != (int)t) continue;
+            a_off = align_up(a_off, 64);
+            T.act_off = a_off; a_off += T.elems * MB;
+            if (T.needs_grad) { a_off = align_up(a_off, 64); T.grad_off = a_off; a_off += T.elems * MB; }
+        }
+    }
+    h->p_elems = align_up(std::max(p_off, 8LL), 8); h->s_elems = std::max(s_off, 8LL);
+    h->act_elems = a_off; h->save_elems = std::max(sv_off, 8LL);
+    const size_t pb = (size_t)h->p_elems * sizeof(__half);
+    CK(cudaMalloc(&h->P, pb)); CK(cudaMalloc(&h->M, pb)); CK(cudaMalloc(&h->V, pb));
+    CK(cudaMalloc(&h->Gr, (size_t)h->p_elems * sizeof(float)));
+    CK(cudaMalloc(&h->S, (size_t)h->s_elems * sizeof(__half)));
+    CK(cudaMalloc(&h->save, (size_t)h->save_elems * sizeof(float)));
+    {
+        cudaError_t e = cudaMalloc(&h->act, (size_t)h->act_elems * sizeof(__half));
+        if (e != cudaSuccess) {
+            free_population(h);
+            return fail(SRN_ERR_LIMIT, "activation arena of %.2f GB does not fit: %s", h->act_elems * 2.0 / 1e9, cudaGetErrorString(e));
+        }
+    }
+    h->device_bytes = 3LL * pb + h->p_elems * 4 + h->s_elems * 2 + h->save_elems * 4 + h->act_elems * 2;
+    CK(cudaMemsetAsync(h->P, 0, pb, h->stream)); CK(cudaMemsetAsync(h->M, 0, pb, h->stream)); CK(cudaMemsetAsync(h->V, 0, pb, h->stream));
+    CK(cudaMemsetAsync(h->Gr, 0, (size_t)h->p_elems * sizeof(float), h->stream));
+    CK(cudaMemsetAsync(h->S, 0, (size_t)h->s_elems * sizeof(__half), h->stream));
+    CK(cudaMemsetAsync(h->save, 0, (size_t)h->save_elems * sizeof(float), h->stream));
+    CK(cudaMemsetAsync(h->act, 0, (size_t)h->act_elems * sizeof(__half), h->stream));
+    // ---- pass 2: fix up pointers, count consumers, build problem groups
+    std::map<std::tuple<int, int, int, int, int>, Group> gmap;
+    h->h_loss.clear();
+    for (int i = 0; i < n; ++i) {
+        Indiv& ind = h->inds[i];
+        for (auto& T : ind.tensors) {
+            if (T.act_off >= 0) T.act = h->act + T.act_off;
+            if (T.grad_off >= 0) T.grad = h->act + T.grad_off;
+        }
+        for (auto& T : ind.tensors) {            // views share the root's storage
+            if (T.root >= 2) { T.act = ind.tensors[T.root].act; T.grad = ind.tensors[T.root].grad; }
+            T.consumers = 0;
+        }
+        for (size_t l = 0; l < ind.layers.size(); ++l) {
+            const LayerRt& L = ind.layers[l];
+            const srn_layer_desc& d = L.d;
+            if (d.kind == SRN_KIND_RESHAPE) continue;
+            const Tensor& to = ind.tensors[2 + l];
+            for (int j = 0; j < d.n_in; ++j) {
+                const int tin = d.in[j];
+                Tensor& ti = ind.tensors[tin];
+                Tensor& troot = ind.tensors[ti.root];
+                Prob p{};
+                p.indiv = i;
+                p.in_sel = ti.root == 0 ? 1 : (ti.root == 1 ? 2 : 0);
+                p.in = ti.act;
+                p.in_bs = (int)ti.elems;
+                p.out = to.act; p.out_bs = (int)to.elems;
+                p.gout = to.grad;
+                p.din = ti.needs_grad ? ti.grad : nullptr;
+                int ordinal = 0;
+                if (p.din) ordinal = troot.consumers++;
+                p.H = d.in_h; p.W = d.in_w; p.C = d.in_c;
+                p.Ho = d.out_h; p.Wo = d.out_w; p.F = d.out_c;
+                p.kh = 1; p.kw = 1; p.sh = 1; p.sw = 1;
+                p.act = d.act;
+                int cfgF = 0, cfgC = 0;
+                if (d.kind == SRN_KIND_DENSE || d.kind == SRN_KIND_CONV) {
+                    if (d.kind == SRN_KIND_CONV) { p.kh = d.kh; p.kw = d.kw; p.sh = d.sh; p.sw = d.sw; }
+                    else { p.H = d.in_h * d.in_w; p.W = 1; p.Ho = p.H; p.Wo = 1; }
+                    p.w = h->P + L.w_off; p.bias = h->P + L.b_off;
+                    p.gw = h->Gr + L.w_off; p.gb = h->Gr + L.b_off;
+                    cfgF = cfg_for(p.F); cfgC = cfg_for(p.C);
+                } else if (d.kind == SRN_KIND_MAXPOOL) {
+                    p.kh = d.kh; p.kw = d.kw; p.sh = d.sh; p.sw = d.sw;
+                } else if (d.kind == SRN_KIND_BN) {
+                    p.H = d.in_h * d.in_w; p.W = 1;
+                    p.w = h->P + L.w_off; p.bias = h->P + L.b_off;
+                    p.gw = h->Gr + L.w_off; p.gb = h->Gr + L.b_off;
+                    p.mov = h->S + L.mov_off; p.save = h->save + L.save_off;
+                } else if (d.kind == SRN_KIND_CONCAT) {
+                    const long long rows = (long long)d.out_h * d.out_w;
+                    p.H = (int)rows; p.W = 1; p.C = (int)(ti.elems / rows);
+                    int coff = 0;
+                    for (int q = 0; q < j; ++q) coff += (int)(ind.tensors[d.in[q]].elems / rows);
+                    p.coff = coff;
+                }
+                auto key = std::make_tuple(to.depth, d.kind, cfgF, cfgC, ordinal);
+                Group& g = gmap[key];
+                g.depth = to.depth; g.kind = d.kind; g.cfgF = cfgF; g.cfgC = cfgC; g.ordinal = ordinal;
+                g.h.push_back(p);
+            }
+        }
+        Prob lp{};
+        lp.indiv = i;
+        lp.out = ind.tensors.back().act; lp.gout = ind.tensors.back().grad; lp.out_bs = h->NL;
+        h->h_loss.push_back(lp);
+    }
+    h->groups.clear();
+    for (auto& kv : gmap) h->groups.push_back(std::move(kv.second));   // std::map iterates in key order
+    // backward runs the groups in reverse: the first writer of each input gradient overwrites, later ones add
+    {
+        std::map<const __half*, bool> written;
+        for (int gi = (int)h->groups.size() - 1; gi >= 0; --gi)
+            for (auto& p : h->groups[gi].h) {
+                if (!p.din) continue;
+                bool& w = written[p.din];
+                p.din_acc = w ? 1 : 0;
+                w = true;
+            }
+    }
+    for (auto& g : h->groups) {
+        CK(cudaMalloc(&g.d, g.h.size() * sizeof(Prob)));
+        CK(cudaMemcpyAsync(g.d, g.h.data(), g.h.size() * sizeof(Prob), cudaMemcpyHostToDevice, h->stream));
+    }
+    CK(cudaMalloc(&h->d_loss, n * sizeof(Prob)));
+    CK(cudaMemcpyAsync(h->d_loss, h->h_loss.data(), n * sizeof(Prob), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMalloc(&h->d_lb, n * sizeof(float)));
+    CK(cudaMemcpyAsync(h->d_lb, loss_balance, n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    // ---- Keras default initialisation on the device
+    for (int i = 0; i < n; ++i) {
+        Indiv& ind = h->inds[i];
+        for (size_t l = 0; l < ind.layers.size(); ++l) {
+            const LayerRt& L = ind.layers[l];
+            const srn_layer_desc& d = L.d;
+            const uint64_t tseed = seed * 0x9E3779B97F4A7C15ull + ((uint64_t)i << 20) + l;
+            if (d.kind == SRN_KIND_DENSE || d.kind == SRN_KIND_CONV) {
+                const int rf = d.kind == SRN_KIND_CONV ? d.kh * d.kw : 1;
+                const double fan_in = (double)d.in_c * rf;
+                const bool heads = (l + 1 == ind.layers.size());
+                float la, lbm; int split = d.units;
+                if (heads) {      // the fused head stands for Dense(n_classes) and Dense(genotype_size)
+                    la = (float)std::sqrt(6.0 / (fan_in + h->ncls));
+                    lbm = (float)std::sqrt(6.0 / (fan_in + h->G));
+                    split = h->ncls;
+                } else {
+                    la = lbm = (float)std::sqrt(6.0 / (fan_in + (double)d.units * rf));
+                }
+                LAUNCH(SRN_CAT_OTHER, k_init_uniform, (unsigned)((L.w_cnt + 255) / 256), 256, h->P + L.w_off, L.w_cnt, d.units, split, la, lbm, tseed);
+            } else if (d.kind == SRN_KIND_BN) {
+                LAUNCH(SRN_CAT_OTHER, k_fill_f16, (unsigned)((L.w_cnt + 255) / 256), 256, h->P + L.w_off, L.w_cnt, 1.0f);          // gamma
+                LAUNCH(SRN_CAT_OTHER, k_fill_f16, (unsigned)((d.in_c + 255) / 256), 256, h->S + L.mov_off + d.in_c, (long long)d.in_c, 1.0f);  // moving variance
+            }
+        }
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
+    h->n = n;
+    h->adam_t = 0;
+    h->built = true;
+    return SRN_OK;
+}
+
+extern "C" int64_t srn_parameters_count(srn_engine* h, int32_t i) {
+    if (!h || !h->built || i < 0 || i >= h->n) return -1;
+    return h->inds[i].pcount;
+}
+
+extern "C" int64_t srn_device_bytes(srn_engine* h) { return h ? h->device_bytes : -1; }
+
+static int locate_weights(srn_engine* h, int ind, int layer, int which, __half** ptr, int64_t* cnt) {
+    if (!h || !h->built) return fail(SRN_ERR_STATE, "weights: engine has no population");
+    if (ind < 0 || ind >= h->n) return fail(SRN_ERR_ARG, "weights: individual %d", ind);
+    Indiv& I = h->inds[ind];
+    if (layer < 0 || layer >= (int)I.layers.size()) return fail(SRN_ERR_ARG, "weights: layer %d", layer);
+    const LayerRt& L = I.layers[layer];
+    const int kind = L.d.kind;
+    if (kind == SRN_KIND_DENSE || kind == SRN_KIND_CONV) {
+        if (which == 0) { *ptr = h->P + L.w_off; *cnt = L.w_cnt; return SRN_OK; }
+        if (which == 1) { *ptr = h->P + L.b_off; *cnt = L.b_cnt; return SRN_OK; }
+    } else if (kind == SRN_KIND_BN) {
+        const int C = L.d.in_c;
+        *cnt = C;
+        if (which == 0) { *ptr = h->P + L.w_off; return SRN_OK; }
+        if (which == 1) { *ptr = h->P + L.b_off; return SRN_OK; }
+        if (which == 2) { *ptr = h->S + L.mov_off; return SRN_OK; }
+        if (which == 3) { *ptr = h->S + L.mov_off + C; return SRN_OK; }
+    }
+    return fail(SRN_ERR_ARG, "weights: layer %d (kind %d) has no weight %d", layer, kind, which);
+}
+
+extern "C" int srn_get_weights(srn_engine* h, int32_t ind, int32_t layer, int32_t which, uint16_t* buf, int64_t* count) {
+    __half* p; int64_t c;
+    int rc = locate_weights(h, ind, layer, which, &p, &c);
+    if (rc) return rc;
+    if (count) *count = c;
+    if (buf) { CK(cudaSetDevice(h->cfg.device)); CK(cudaStreamSynchronize(h->stream)); CK(cudaMemcpy(buf, p, c * sizeof(__half), cudaMemcpyDeviceToHost)); }
+    return SRN_OK;
+}
+
+extern "C" int srn_set_weights(srn_engine* h, int32_t ind, int32_t layer, int32_t which, const uint16_t* buf, int64_t count) {
+    __half* p; int64_t c;
+    int rc = locate_weights(h, ind, layer, which, &p, &c);
+    if (rc) return rc;
+    if (!buf || count != c) return fail(SRN_ERR_ARG, "set_weights: expected %lld elements, got %lld", (long long)c, (long long)count);
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(p, buf, c * sizeof(__half), cudaMemcpyHostToDevice));
+    return SRN_OK;
+}
+
+// ------------------------------------------------------------------ launch plan per batch size
+static int pass_items(const Group& g, const Prob& p, int pass, int nb) {
+    const long long in_e = (long long)p.H * p.W * p.C, out_e = (long long)p.Ho * p.Wo * p.F;
+    switch (g.kind) {
+        case SRN_KIND_DENSE:
+        case SRN_KIND_CONV:
+            if (pass == P_FWD) return fwd_tiles(nb * p.Ho * p.Wo, p.F, CFG_BM[g.cfgF], CFG_BN[g.cfgF]);
+            if (pass == P_DGRAD) return p.din ? fwd_tiles(nb * p.H * p.W, p.C, CFG_BM[g.cfgC], CFG_BN[g.cfgC]) : 0;
+            if (pass == P_WGRAD) return wgrad_tiles(p.kh * p.kw * p.C, p.F, nb * p.Ho * p.Wo);
+            if (pass == P_COL) return col_chunks((long long)nb * p.Ho * p.Wo);
+            return 0;
+        case SRN_KIND_MAXPOOL:
+            if (pass == P_FWD) return ew_blocks((long long)nb * p.Ho * p.Wo * p.C);
+            if (pass == P_BWD_EW) return p.din ? ew_blocks(nb * in_e) : 0;
+            return 0;
+        case SRN_KIND_BN:
+            if (pass == P_FWD) return ew_blocks(nb * in_e);
+            if (pass == P_COL) return col_chunks((long long)nb * p.H * p.W);
+            if (pass == P_BWD_EW) return p.din ? ew_blocks(nb * in_e) : 0;
+            return 0;
+        case SRN_KIND_CONCAT:
+            if (pass == P_FWD) return ew_blocks(nb * in_e);
+            if (pass == P_BWD_EW) return p.din ? ew_blocks(nb * in_e) : 0;
+            return 0;
+    }
+    (void)out_e;
+    return 0;
+}
+
+static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
+    auto it = g.cache.find(nb);
+    if (it != g.cache.end()) { *out = &it->second; return SRN_OK; }
+    Cached c;
+    const int np = (int)g.h.size();
+    std::vector<int> host((size_t)P_COUNT * (np + 1));
+    for (int pass = 0; pass < P_COUNT; ++pass) {
+        int* pre = host.data() + (size_t)pass * (np + 1);
+        long long acc = 0;
+        for (int i = 0; i < np; ++i) { pre[i] = (int)acc; acc += pass_items(g, g.h[i], pass, nb); }
+        if (acc > 0x7fffffffLL) return fail(SRN_ERR_LIMIT, "launch grid too large");
+        pre[np] = (int)acc;
+        c.total[pass] = (int)acc;
+    }
+    int* dev = nullptr;
+    CK(cudaMalloc(&dev, host.size() * sizeof(int)));
+    CK(cudaMemcpyAsync(dev, host.data(), host.size() * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));      // host vector goes out of scope
+    h->scratch_prefix.push_back(dev);
+    for (int pass = 0; pass < P_COUNT; ++pass) c.prefix[pass] = dev + (size_t)pass * (np + 1);
+    g.cache[nb] = c;
+    *out = &g.cache[nb];
+    return SRN_OK;
+}
+
+template <int CFG>
+static void launch_fwd_cfg(srn_engine* h, Group& g, Cached* c, int nb, const Inputs& I) {
+    LAUNCH(SRN_CAT_GEMM_FWD, (k_conv_fwd<(CFG == 0 ? 64 : CFG == 1 ? 128 : 256), (CFG == 0 ? 64 : CFG == 1 ? 32 : 16)>), c->total[P_FWD], SIMT_THREADS,
+           g.d, c->prefix[P_FWD], (int)g.h.size(), nb, I);
+}
+template <int CFG>
+static void launch_dgrad_cfg(srn_engine* h, Group& g, Cached* c, int nb) {
+    LAUNCH(SRN_CAT_GEMM_DGRAD, (k_conv_dgrad<(CFG == 0 ? 64 : CFG == 1 ? 128 : 256), (CFG == 0 ? 64 : CFG == 1 ? 32 : 16)>), c->total[P_DGRAD], SIMT_THREADS,
+           g.d, c->prefix[P_DGRAD], (int)g.h.size(), nb);
+}
+
+static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
+    for (auto& g : h->groups) {
+        Cached* c;
+        int rc = plan_for(h, g, nb, &c);
+        if (rc) return rc;
+        const int np = (int)g.h.size();
+        switch (g.kind) {
+            case SRN_KIND_DENSE:
+            case SRN_KIND_CONV:
+                if (g.cfgF == 0) launch_fwd_cfg<0>(h, g, c, nb, I);
+                else if (g.cfgF == 1) launch_fwd_cfg<1>(h, g, c, nb, I);
+                else launch_fwd_cfg<2>(h, g, c, nb, I);
+                break;
+            case SRN_KIND_MAXPOOL:
+                LAUNCH(SRN_CAT_POOL, k_maxpool_fwd, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I);
+                break;
+            case SRN_KIND_BN:
+                if (training) {
+                    LAUNCH(SRN_CAT_BN, k_bn_partial, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I, 0);
+                    LAUNCH(SRN_CAT_BN, k_bn_finalize_fwd, np, 128, g.d, nb, I);
+                } else {
+                    LAUNCH(SRN_CAT_BN, k_bn_prepare_infer, np, 128, g.d);
+                }
+                LAUNCH(SRN_CAT_BN, k_bn_apply, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I);
+                break;
+            case SRN_KIND_CONCAT:
+                LAUNCH(SRN_CAT_CONCAT, k_concat, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I, 0);
+                break;
+        }
+    }
+    return SRN_OK;
+}
+
+static int backward_pass(srn_engine* h, int nb, const Inputs& I) {
+    for (int gi = (int)h->groups.size() - 1; gi >= 0; --gi) {
+        Group& g = h->groups[gi];
+        Cached* c;
+        int rc = plan_for(h, g, nb, &c);
+        if (rc) return rc;
+        const int np = (int)g.h.size();
+        switch (g.kind) {
+            case SRN_KIND_DENSE:
+            case SRN_KIND_CONV:
+                LAUNCH(SRN_CAT_ACT_BWD, k_act_bwd_bias, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb);
+                LAUNCH(SRN_CAT_GEMM_WGRAD, k_conv_wgrad, c->total[P_WGRAD], SIMT_THREADS, g.d, c->prefix[P_WGRAD], np, nb, I);
+                if (g.cfgC == 0) launch_dgrad_cfg<0>(h, g, c, nb);
+                else if (g.cfgC == 1) launch_dgrad_cfg<1>(h, g, c, nb);
+                else launch_dgrad_cfg<2>(h, g, c, nb);
+                break;
+            case SRN_KIND_MAXPOOL:
+                LAUNCH(SRN_CAT_POOL, k_maxpool_bwd, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I);
+                break;
+            case SRN_KIND_BN:
+                LAUNCH(SRN_CAT_BN, k_bn_partial, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I, 1);
+                LAUNCH(SRN_CAT_BN, k_bn_finalize_bwd, np, 128, g.d, nb);
+                LAUNCH(SRN_CAT_BN, k_bn_bwd_apply, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I);
+                break;
+            case SRN_KIND_CONCAT:
+                LAUNCH(SRN_CAT_CONCAT, k_concat, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I, 1);
+                break;
+        }
+    }
+    return SRN_OK;
+}
+
+static int ensure_metrics(srn_engine* h, long long slots) {
+    if (slots > h->met_slots) {
+        cudaFree(h->met_correct); cudaFree(h->met_ce); cudaFree(h->met_mse);
+        CK(cudaMalloc(&h->met_correct, slots * h->n * sizeof(int)));
+        CK(cudaMalloc(&h->met_ce, slots * h->n * sizeof(float)));
+        CK(cudaMalloc(&h->met_mse, slots * h->n * sizeof(float)));
+        h->met_slots = slots;
+    }
+    CK(cudaMemsetAsync(h->met_correct, 0, slots * h->n * sizeof(int), h->stream));
+    CK(cudaMemsetAsync(h->met_ce, 0, slots * h->n * sizeof(float), h->stream));
+    CK(cudaMemsetAsync(h->met_mse, 0, slots * h->n * sizeof(float), h->stream));
+    return SRN_OK;
+}
+
+static Inputs shared_inputs(srn_engine* h) {
+    Inputs I;
+    I.x = h->xin; I.x_istride = 0; I.x_bs = h->xe;
+    I.g = h->gin; I.g_istride = 0; I.g_bs = h->G;
+    return I;
+}
+
+static void launch_loss(srn_engine* h, int nb, const Inputs& I, int slot_base, int chunk, int row0, int training) {
+    LossArgs a;
+    a.labels = h->lab;
+    a.bits = I.g; a.bits_istride = I.g_istride; a.bits_bs = I.g_bs;
+    a.loss_balance = h->d_lb;
+    a.met_correct = h->met_correct; a.met_ce = h->met_ce; a.met_mse = h->met_mse;
+    a.n = h->n; a.ncls = h->ncls; a.G = h->G;
+    a.slot_base = slot_base; a.chunk = chunk; a.row0 = row0; a.training = training;
+    const int ctas = h->n * ((nb + 7) / 8);
+    LAUNCH(SRN_CAT_LOSS, k_loss, ctas, 256, h->d_loss, h->n, nb, a);
+}
+
+static AdamScalars adam_scalars(int t) {
+    // Keras Adam._prepare_local + TF ApplyAdam with every scalar held in fp16
+    const float lr = h16(1e-3f), b1 = h16(0.9f), b2 = h16(0.999f), eps = h16(1e-4f);
+    const float step = h16((float)t);
+    const float b1p = h16(powf(b1, step)), b2p = h16(powf(b2, step));
+    AdamScalars s;
+    s.alpha = h16(h16(lr * h16(sqrtf(h16(1.f - b2p)))) / h16(1.f - b1p));
+    s.omb1 = h16(1.f - b1);
+    s.omb2 = h16(1.f - b2);
+    s.eps = eps;
+    return s;
+}
+
+// one training step on staged rows: gather -> forward -> loss -> backward -> Adam
+static int train_step(srn_engine* h, const int* d_idx, int start, int nb, int slot, bool apply_adam) {
+    LAUNCH(SRN_CAT_GATHER, k_gather_batch, nb, 256, h->x[0], h->gb[0], h->y[0], d_idx, start, nb, h->xe, h->G, h->xin, h->gin, h->lab);
+    Inputs I = shared_inputs(h);
+    int rc = forward_pass(h, nb, I, true);
+    if (rc) return rc;
+    launch_loss(h, nb, I, slot, 1 << 30, 0, 1);
+    rc = backward_pass(h, nb, I);
+    if (rc) return rc;
+    if (apply_adam) {
+        h->adam_t += 1;
+        const long long n8 = h->p_elems / 8;
+        LAUNCH(SRN_CAT_ADAM, k_adam, (unsigned)((n8 + 255) / 256), 256, h->P, h->M, h->V, h->Gr, n8, adam_scalars(h->adam_t));
+    }
+    return SRN_OK;
+}
+
+// inference over dataset rows [start, start+rows) with metrics per `chunk` rows into slots slot_base..
+static int eval_rows(srn_engine* h, int split, int start, int rows, int chunk, int slot_base) {
+    const int MB = h->cfg.max_batch;
+    for (int r = 0; r < rows; r += MB) {
+        const int nb = std::min(MB, rows - r);
+        LAUNCH(SRN_CAT_GATHER, k_gather_batch, nb, 256, h->x[split], h->gb[split], h->y[split], (const int*)nullptr, start + r, nb, h->xe, h->G,
+               h->xin, h->gin, h->lab);
+        Inputs I = shared_inputs(h);
+        int rc = forward_pass(h, nb, I, false);
+        if (rc) return rc;
+        launch_loss(h, nb, I, slot_base, chunk, r, 0);
+    }
+    return SRN_OK;
+}
+
+static int check_ready(srn_engine* h, const char* what) {
+    if (!h) return fail(SRN_ERR_ARG, "%s: null engine", what);
+    if (!h->built) return fail(SRN_ERR_STATE, "%s: call srn_build first", what);
+    if (!h->x[0]) return fail(SRN_ERR_STATE, "%s: call srn_set_dataset first", what);
+    return SRN_OK;
+}
+
+extern "C" int srn_fit(srn_engine* h, int32_t epochs, int32_t batch, int32_t n_val, const int32_t* perms,
+                       uint64_t shuffle_seed, int32_t max_steps, int32_t* train_correct, float* train_loss,
+                       int32_t* val_correct, float* val_mse_sum, float* device_ms) {
+    int rc = check_ready(h, "srn_fit");
+    if (rc) return rc;
+    CK(cudaSetDevice(h->cfg.device));
+    const int n_fit = h->nrows[0] - n_val;
+    if (epochs <= 0 || batch <= 0 || batch > h->cfg.max_batch || n_val < 0 || n_fit <= 0)
+        return fail(SRN_ERR_ARG, "srn_fit: epochs %d batch %d (max %d) n_val %d of %d rows", epochs, batch, h->cfg.max_batch, n_val, h->nrows[0]);
+    const int S = (n_fit + batch - 1) / batch, Vc = n_val ? (n_val + batch - 1) / batch : 0;
+    std::vector<int32_t> gen;
+    if (!perms) {
+        gen.resize((size_t)epochs * n_fit);
+        std::mt19937_64 rng(shuffle_seed);
+        for (int e = 0; e < epochs; ++e) {
+            int32_t* p = gen.data() + (size_t)e * n_fit;
+            for (int i = 0; i < n_fit; ++i) p[i] = i;
+            for (int i = n_fit - 1; i > 0; --i) std::swap(p[i], p[rng() % (uint64_t)(i + 1)]);
+        }
+        perms = gen.data();
+    } else {
+        for (size_t i = 0; i < (size_t)epochs * n_fit; ++i)
+            if (perms[i] < 0 || perms[i] >= n_fit) return fail(SRN_ERR_ARG, "srn_fit: permutation entry %d out of range", perms[i]);
+    }
+    int* d_perm = nullptr;
+    CK(cudaMalloc(&d_perm, (size_t)epochs * n_fit * sizeof(int)));
+    CK(cudaMemcpy(d_perm, perms, (size_t)epochs * n_fit * sizeof(int), cudaMemcpyHostToDevice));
+    const long long slots = (long long)epochs * (S + Vc);
+    rc = ensure_metrics(h, slots);
+    if (rc) { cudaFree(d_perm); return rc; }
+    cudaEvent_t ev0, ev1;
+    CK(cudaEventCreate(&ev0)); CK(cudaEventCreate(&ev1));
+    float ms_total = 0.f;
+    int steps_done = 0;
+    bool stop = false;
+    // warm the launch plans outside the timed region
+    for (auto& g : h->groups) { Cached* c; rc = plan_for(h, g, batch, &c); if (rc) { cudaFree(d_perm); return rc; } }
+    for (int e = 0; e < epochs && !stop; ++e) {
+        CK(cudaEventRecord(ev0, h->stream));
+        for (int s = 0; s < S; ++s) {
+            const int nb = std::min(batch, n_fit - s * batch);
+            rc = train_step(h, d_perm + (size_t)e * n_fit + (size_t)s * batch, 0, nb, e * S + s, true);
+            if (rc) { cudaFree(d_perm); return rc; }
+            if (max_steps > 0 && ++steps_done >= max_steps) { stop = true; break; }
+        }
+        CK(cudaEventRecord(ev1, h->stream));
+        if (n_val && !stop) {
+            rc = eval_rows(h, 0, n_fit, n_val, batch, epochs * S + e * Vc);
+            if (rc) { cudaFree(d_perm); return rc; }
+        }
+        CK(cudaEventSynchronize(ev1));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, ev0, ev1));
+        ms_total += ms;
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    cudaFree(d_perm);
+    const size_t tn = (size_t)epochs * S * h->n, vn = (size_t)epochs * Vc * h->n;
+    if (train_correct) CK(cudaMemcpy(train_correct, h->met_correct, tn * sizeof(int), cudaMemcpyDeviceToHost));
+    if (train_loss) {
+        std::vector<float> ce(tn), mse(tn);
+        CK(cudaMemcpy(ce.data(), h->met_ce, tn * sizeof(float), cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(mse.data(), h->met_mse, tn * sizeof(float), cudaMemcpyDeviceToHost));
+        for (int e = 0; e < epochs; ++e)
+            for (int s = 0; s < S; ++s) {
+                const float nb = (float)std::min(batch, n_fit - s * batch);
+                for (int i = 0; i < h->n; ++i) {
+                    const size_t k = ((size_t)e * S + s) * h->n + i;
+                    train_loss[2 * k] = ce[k] / nb;
+                    train_loss[2 * k + 1] = mse[k] / nb;
+                }
+            }
+    }
+    if (val_correct && vn) CK(cudaMemcpy(val_correct, h->met_correct + tn, vn * sizeof(int), cudaMemcpyDeviceToHost));
+    if (val_mse_sum && vn) CK(cudaMemcpy(val_mse_sum, h->met_mse + tn, vn * sizeof(float), cudaMemcpyDeviceToHost));
+    if (device_ms) *device_ms = ms_total;
+    return SRN_OK;
+}
+
+extern "C" int srn_evaluate(srn_engine* h, int32_t split, int32_t start, int32_t rows, int32_t chunk,
+                            int32_t* correct, float* mse_sum) {
+    int rc = check_ready(h, "srn_evaluate");
+    if (rc) return rc;
+    if (split < 0 || split > 1 || start < 0 || rows <= 0 || chunk <= 0 || start + rows > h->nrows[split])
+        return fail(SRN_ERR_ARG, "srn_evaluate: rows [%d, %d) of split %d (%d rows), chunk %d", start, start + rows, split, split >= 0 && split <= 1 ? h->nrows[split] : -1, chunk);
+    CK(cudaSetDevice(h->cfg.device));
+    const int slots = (rows + chunk - 1) / chunk;
+    rc = ensure_metrics(h, slots);
+    if (rc) return rc;
+    rc = eval_rows(h, split, start, rows, chunk, 0);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
+    if (correct) CK(cudaMemcpy(correct, h->met_correct, (size_t)slots * h->n * sizeof(int), cudaMemcpyDeviceToHost));
+    if (mse_sum) CK(cudaMemcpy(mse_sum, h->met_mse, (size_t)slots * h->n * sizeof(float), cudaMemcpyDeviceToHost));
+    return SRN_OK;
+}
+
+// head logits of every individual -> [n][rows_total][NL] (rows r0.. of this chunk), optionally sigmoid of the
+// replication part -> [n][R][G]
+__global__ void k_collect_heads(const Prob* __restrict__ loss_probs, int n, int nb, int NL, int ncls, int r0, int rows_total,
+                                __half* __restrict__ logits, __half* __restrict__ probs) {
+    const int i = blockIdx.y;
+    const int b = blockIdx.x;
+    const Prob p = loss_probs[i];
+    const __half* z = p.out + (long long)b * p.out_bs;
+    for (int j = threadIdx.x; j < NL; j += blockDim.x) {
+        if (logits) logits[((long long)i * rows_total + r0 + b) * NL + j] = z[j];
+        if (probs && j >= ncls) {
+            float s = rh(1.f / (1.f + expf(-__half2float(z[j]))));
+            probs[((long long)i * rows_total + r0 + b) * (NL - ncls) + (j - ncls)] = __float2half_rn(s);
+        }
+    }
+    (void)n; (void)nb;
+}
+
+extern "C" int srn_forward_logits(srn_engine* h, int32_t split, int32_t start, int32_t rows, int32_t training,
+                                  uint16_t* logits) {
+    int rc = check_ready(h, "srn_forward_logits");
+    if (rc) return rc;
+    if (split < 0 || split > 1 || start < 0 || rows <= 0 || start + rows > h->nrows[split] || !logits)
+        return fail(SRN_ERR_ARG, "srn_forward_logits: bad range");
+    if (training && rows > h->cfg.max_batch) return fail(SRN_ERR_ARG, "srn_forward_logits: training-mode batch > max_batch");
+    CK(cudaSetDevice(h->cfg.device));
+    __half* d_out = nullptr;
+    CK(cudaMalloc(&d_out, (size_t)h->n * rows * h->NL * sizeof(__half)));
+    const int MB = h->cfg.max_batch;
+    for (int r = 0; r < rows; r += MB) {
+        const int nb = std::min(MB, rows - r);
+        LAUNCH(SRN_CAT_GATHER, k_gather_batch, nb, 256, h->x[split], h->gb[split], h->y[split], (const int*)nullptr, start + r, nb, h->xe, h->G,
+               h->xin, h->gin, h->lab);
+        Inputs I = shared_inputs(h);
+        rc = forward_pass(h, nb, I, training != 0);
+        if (rc) { cudaFree(d_out); return rc; }
+        dim3 grid(nb, h->n);
+        LAUNCH(SRN_CAT_OTHER, k_collect_heads, grid, 128, h->d_loss, h->n, nb, h->NL, h->ncls, r, rows, d_out, (__half*)nullptr);
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(logits, d_out, (size_t)h->n * rows * h->NL * sizeof(__half), cudaMemcpyDeviceToHost));
+    cudaFree(d_out);
+    return SRN_OK;
+}
+
+extern "C" int srn_replicate(srn_engine* h, const uint8_t* parent_bits, int32_t R, const int32_t* image_index,
+                             uint16_t* probs, uint32_t* packed_bits, int32_t* mutations) {
+    int rc = check_ready(h, "srn_replicate");
+    if (rc) return rc;
+    if (!parent_bits || R <= 0) return fail(SRN_ERR_ARG, "srn_replicate: bad argument");
+    if (!h->x[1]) return fail(SRN_ERR_STATE, "srn_replicate: no test split");
+    CK(cudaSetDevice(h->cfg.device));
+    const int n = h->n, G = h->G, xe = h->xe, words = (G + 31) / 32;
+    const long long rows = (long long)n * R;
+    std::vector<int32_t> idx((size_t)rows);
+    if (image_index) {
+        for (long long r = 0; r < rows; ++r) {
+            if (image_index[r] < 0 || image_index[r] >= h->nrows[1]) return fail(SRN_ERR_ARG, "srn_replicate: image index out of range");
+            idx[r] = image_index[r];
+        }
+    } else {      // np.repeat(x_test, ceil(n*R / n_test), axis=0)[:n*R]  (experiment_worker.py:139-150)
+        const long long repeat = (rows + h->nrows[1] - 1) / h->nrows[1];
+        for (long long r = 0; r < rows; ++r) idx[r] = (int32_t)(r / repeat);
+    }
+    int* d_idx = nullptr; __half* d_x = nullptr; __half* d_g = nullptr; uint8_t* d_par = nullptr;
+    __half* d_probs = nullptr; uint32_t* d_packed = nullptr; int* d_mut = nullptr;
+    auto cleanup = [&]() { cudaFree(d_idx); cudaFree(d_x); cudaFree(d_g); cudaFree(d_par); cudaFree(d_probs); cudaFree(d_packed); cudaFree(d_mut); };
+#define CKR(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); return fail(SRN_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); } } while (0)
+    CKR(cudaMalloc(&d_idx, rows * sizeof(int)));
+    CKR(cudaMemcpy(d_idx, idx.data(), rows * sizeof(int), cudaMemcpyHostToDevice));
+    CKR(cudaMalloc(&d_x, rows * xe * sizeof(__half)));
+    CKR(cudaMalloc(&d_g, (size_t)n * G * sizeof(__half)));
+    CKR(cudaMalloc(&d_par, (size_t)n * G));
+    CKR(cudaMemcpy(d_par, parent_bits, (size_t)n * G, cudaMemcpyHostToDevice));
+    CKR(cudaMalloc(&d_probs, rows * G * sizeof(__half)));
+    CKR(cudaMalloc(&d_packed, rows * words * sizeof(uint32_t)));
+    CKR(cudaMalloc(&d_mut, rows * sizeof(int)));
+    LAUNCH(SRN_CAT_GATHER, k_gather_batch, (unsigned)rows, 256, h->x[1], (const uint8_t*)nullptr, (const uint8_t*)nullptr, d_idx, 0, (int)rows, xe, G,
+           d_x, (__half*)nullptr, (uint8_t*)nullptr);
+    LAUNCH(SRN_CAT_OTHER, k_u8_to_f16, (unsigned)(((long long)n * G + 255) / 256), 256, d_par, d_g, (long long)n * G);
+    const int MB = h->cfg.max_batch;
+    for (int r0 = 0; r0 < R; r0 += MB) {
+        const int nb = std::min(MB, R - r0);
+        Inputs I;
+        I.x = d_x + (long long)r0 * xe; I.x_istride = (long long)R * xe; I.x_bs = xe;
+        I.g = d_g; I.g_istride = G; I.g_bs = 0;     // the parent's genotype, broadcast over its rows
+        rc = forward_pass(h, nb, I, false);
+        if (rc) { cleanup(); return rc; }
+        dim3 grid(nb, n);
+        LAUNCH(SRN_CAT_READOUT, k_collect_heads, grid, 128, h->d_loss, n, nb, h->NL, h->ncls, r0, R, (__half*)nullptr, d_probs);
+    }
+    LAUNCH(SRN_CAT_READOUT, k_readout, (unsigned)((rows + 7) / 8), 256, d_probs, d_par, (int)rows, R, G, d_packed, d_mut);
+    CKR(cudaStreamSynchronize(h->stream));
+    CKR(cudaGetLastError());
+    if (probs) CKR(cudaMemcpy(probs, d_probs, rows * G * sizeof(__half), cudaMemcpyDeviceToHost));
+    if (packed_bits) CKR(cudaMemcpy(packed_bits, d_packed, rows * words * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    if (mutations) CKR(cudaMemcpy(mutations, d_mut, rows * sizeof(int), cudaMemcpyDeviceToHost));
+    cleanup();
+#undef CKR
+    return SRN_OK;
+}
+
+// ------------------------------------------------------------------ debug / parity hooks (declared in srn_host.h)
+extern "C" int srn_debug_step(srn_engine* h, const int32_t* rows, int32_t nb, int32_t apply_adam) {
+    int rc = check_ready(h, "srn_debug_step");
+    if (rc) return rc;
+    if (!rows || nb <= 0 || nb > h->cfg.max_batch) return fail(SRN_ERR_ARG, "srn_debug_step: bad batch");
+    CK(cudaSetDevice(h->cfg.device));
+    int* d_idx = nullptr;
+    CK(cudaMalloc(&d_idx, nb * sizeof(int)));
+    CK(cudaMemcpy(d_idx, rows, nb * sizeof(int), cudaMemcpyHostToDevice));
+    rc = ensure_metrics(h, 1);
+    cudaMemsetAsync(h->Gr, 0, (size_t)h->p_elems * sizeof(float), h->stream);
+    if (!rc) rc = train_step(h, d_idx, 0, nb, 0, apply_adam != 0);
+    cudaError_t e = cudaStreamSynchronize(h->stream);
+    cudaFree(d_idx);
+    if (rc) return rc;
+    if (e != cudaSuccess) return fail(SRN_ERR_CUDA, "srn_debug_step: %s", cudaGetErrorString(e));
+    CK(cudaGetLastError());
+    return SRN_OK;
+}
+
+extern "C" int srn_debug_get_tensor(srn_engine* h, int32_t ind, int32_t tensor, int32_t grad, int32_t nb, uint16_t* buf) {
+    if (!h || !h->built || ind < 0 || ind >= h->n) return fail(SRN_ERR_ARG, "srn_debug_get_tensor: bad individual");
+    Indiv& I = h->inds[ind];
+    if (tensor < 2 || tensor >= (int)I.tensors.size() || nb <= 0 || nb > h->cfg.max_batch) return fail(SRN_ERR_ARG, "srn_debug_get_tensor: bad tensor/batch");
+    const Tensor& T = I.tensors[tensor];
+    const __half* src = grad ? T.grad : T.act;
+    if (!src) return fail(SRN_ERR_ARG, "srn_debug_get_tensor: tensor %d has no %s buffer", tensor, grad ? "gradient" : "activation");
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(buf, src, (size_t)nb * T.elems * sizeof(__half), cudaMemcpyDeviceToHost));
+    return SRN_OK;
+}
+
+extern "C" int srn_debug_get_grad(srn_engine* h, int32_t ind, int32_t layer, int32_t which, float* buf, int64_t count) {
+    __half* p; int64_t c;
+    int rc = locate_weights(h, ind, layer, which, &p, &c);
+    if (rc) return rc;
+    if (which > 1 || count != c) return fail(SRN_ERR_ARG, "srn_debug_get_grad: bad which/count");
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(buf, h->Gr + (p - h->P), c * sizeof(float), cudaMemcpyDeviceToHost));
+    return SRN_OK;
+}
+
+extern "C" int srn_debug_launch_groups(srn_engine* h) { return h && h->built ? (int)h->groups.size() : -1; }
+
+// ------------------------------------------------------------------ per-category device timing (bench.py roofline)
+extern "C" int srn_profile(srn_engine* h, int32_t on) {
+    if (!h) return fail(SRN_ERR_ARG, "srn_profile: null engine");
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    for (ProfRec* r : h->prof) { cudaEventDestroy(r->a); cudaEventDestroy(r->b); delete r; }
+    h->prof.clear();
+    h->profiling = on != 0;
+    return SRN_OK;
+}
+
+extern "C" int srn_profile_read(srn_engine* h, float* ms, int32_t* launches) {
+    if (!h || !ms || !launches) return fail(SRN_ERR_ARG, "srn_profile_read: null argument");
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    for (int c = 0; c < SRN_CAT_COUNT; ++c) { ms[c] = 0.f; launches[c] = 0; }
+    for (ProfRec* r : h->prof) {
+        float t = 0.f;
+        CK(cudaEventElapsedTime(&t, r->a, r->b));
+        ms[r->cat] += t;
+        launches[r->cat] += 1;
+    }
+    return SRN_OK;
+}

@@ -1,0 +1,24 @@
+// Host-side helpers shared by the translation units of libserann_b200.so, and the debug hooks
+// the parity tests use (not part of the product ABI in include/serann_b200.h).
+#pragma once
+#include <atomic>
+#include <stdint.h>
+#include <string>
+
+struct srn_engine;
+
+namespace srn {
+extern thread_local std::string g_error;
+extern std::atomic<unsigned long long> g_launches;
+int fail(int code, const char* fmt, ...);
+}  // namespace srn
+
+extern "C" {
+// one training step on the given rows of the training split; apply_adam = 0 leaves the fp32 gradients in place
+int srn_debug_step(srn_engine* h, const int32_t* rows, int32_t nb, int32_t apply_adam);
+// activation (grad = 0) or activation gradient (grad = 1) of tensor `tensor` of one individual, first nb rows
+int srn_debug_get_tensor(srn_engine* h, int32_t individual, int32_t tensor, int32_t grad, int32_t nb, uint16_t* buf);
+// fp32 gradient accumulator of a weight (which = 0 kernel/gamma, 1 bias/beta)
+int srn_debug_get_grad(srn_engine* h, int32_t individual, int32_t layer, int32_t which, float* buf, int64_t count);
+int srn_debug_launch_groups(srn_engine* h);
+}
