@@ -4,7 +4,7 @@ import sys
 import pytest
 
 ROOT = pathlib.Path(__file__).resolve().parent.parent
-for p in (str(ROOT), str(ROOT / 'tests')):
+for p in (str(ROOT), str(ROOT / 'tests'), str(ROOT / 'tests' / 'golden')):
     if p not in sys.path:
         sys.path.insert(0, p)
 
