@@ -1,6 +1,7 @@
 // Stand-alone entry points: ribosomal-autoencoder decode, genotype readout, BatchNormalizationF16 forward.
 #include <algorithm>
 #include <cmath>
+#include <cstddef>
 #include <vector>
 
 #include "../../include/serann_b200.h"
@@ -256,5 +257,71 @@ extern "C" int srn_bn_train_forward(int32_t device, const uint16_t* x, int64_t r
     CKR(cudaMemcpy(moving_variance, d_par + 3 * C, C * sizeof(__half), cudaMemcpyDeviceToHost));
     cleanup();
 #undef CKR
+    return SRN_OK;
+}
+
+// ------------------------------------------------------------------ BatchNormalizationF16 forward without allocation
+// Same three kernels as srn_bn_train_forward, but the per-channel statistics, the per-chunk partial sums and
+// the problem descriptor live in the file-scope array below instead of cudaMalloc'ed scratch.  The array is part
+// of the library image: every GPU that loads the library holds SRN_NOALLOC_SCRATCH_BYTES of it until exit.
+constexpr size_t NOALLOC_HEADER_BYTES = 512;                       // Prob descriptor + launch prefix
+constexpr size_t NOALLOC_FLOATS = (SRN_NOALLOC_SCRATCH_BYTES - NOALLOC_HEADER_BYTES) / sizeof(float);
+static_assert(sizeof(Prob) + 8 * sizeof(int) <= NOALLOC_HEADER_BYTES, "descriptor does not fit the scratch header");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[SRN_NOALLOC_SCRATCH_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};      // device address of the array, per device
+
+extern "C" int srn_bn_train_forward_noalloc(int32_t device, void* stream, const uint16_t* d_x, int64_t rows, int32_t C,
+                                            const uint16_t* d_gamma, const uint16_t* d_beta,
+                                            uint16_t* d_moving_mean, uint16_t* d_moving_variance, uint16_t* d_y) {
+    if (!d_x || !d_gamma || !d_beta || !d_moving_mean || !d_moving_variance || !d_y || rows <= 0 || C <= 0)
+        return fail(SRN_ERR_ARG, "srn_bn_train_forward_noalloc: bad argument");
+    if (rows * (int64_t)C > 0x7fffffffLL) return fail(SRN_ERR_LIMIT, "srn_bn_train_forward_noalloc: more than 2^31 elements");
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(SRN_ERR_ARG, "srn_bn_train_forward_noalloc: device %d", device);
+    if (d_moving_variance != d_moving_mean + C)
+        return fail(SRN_ERR_ARG, "srn_bn_train_forward_noalloc: moving_variance must directly follow moving_mean (one [2][C] array)");
+    const int chunks = col_chunks(rows);
+    const size_t need = 4 * (size_t)C + 2 * (size_t)C * chunks;
+    if (need > NOALLOC_FLOATS)
+        return fail(SRN_ERR_LIMIT, "srn_bn_train_forward_noalloc: C * (4 + 2 * ceil(rows / %d)) = %zu floats exceeds the built-in "
+                    "scratch of %zu floats (%zu bytes); use srn_bn_train_forward for this size", COL_ROWS, need, NOALLOC_FLOATS,
+                    (size_t)SRN_NOALLOC_SCRATCH_BYTES);
+    int rc = check_device(device);
+    if (rc) return rc;
+    if (!g_noalloc_ptr[device]) {
+        // In host code the array's name is only a handle for the runtime; the address kernels can use comes from
+        // cudaGetSymbolAddress, asked once per device while that device is current.
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) return fail(SRN_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch) on device %d: %s", device, cudaGetErrorString(e));
+        g_noalloc_ptr[device] = static_cast<unsigned char*>(p);
+    }
+    unsigned char* base = g_noalloc_ptr[device];
+    Prob* d_prob = reinterpret_cast<Prob*>(base);
+    int* d_prefix = reinterpret_cast<int*>(base + sizeof(Prob));
+    float* d_save = reinterpret_cast<float*>(base + NOALLOC_HEADER_BYTES);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    struct { Prob p; int pre[4]; } hdr{};
+    Prob& p = hdr.p;
+    p.in = reinterpret_cast<const __half*>(d_x); p.out = reinterpret_cast<__half*>(d_y);
+    p.w = reinterpret_cast<const __half*>(d_gamma); p.bias = reinterpret_cast<const __half*>(d_beta);
+    p.mov = reinterpret_cast<__half*>(d_moving_mean); p.save = d_save;
+    p.H = 1; p.W = 1; p.C = C; p.Ho = 1; p.Wo = 1; p.F = C; p.in_bs = C; p.out_bs = C;
+    const int nb = (int)rows;
+    const int blocks = ew_blocks(rows * (long long)C);
+    hdr.pre[0] = 0; hdr.pre[1] = chunks; hdr.pre[2] = 0; hdr.pre[3] = blocks;
+    static_assert(offsetof(decltype(hdr), pre) == sizeof(Prob), "descriptor layout");
+    CK(cudaMemcpyAsync(d_prob, &hdr, sizeof hdr, cudaMemcpyHostToDevice, st));
+    // Nothing in the scratch has to start at zero: every statistic and every partial sum that is read below is
+    // written first by this call (k_bn_partial covers all chunks x channels, k_bn_finalize_fwd all channels).
+    Inputs I{};
+    k_bn_partial<<<chunks, COL_THREADS, 0, st>>>(d_prob, d_prefix, 1, nb, I, 0);
+    k_bn_finalize_fwd<<<1, 128, 0, st>>>(d_prob, nb, I);
+    k_bn_apply<<<blocks, EW_THREADS, 0, st>>>(d_prob, d_prefix + 2, 1, nb, I);
+    g_launches.fetch_add(3);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(st));
     return SRN_OK;
 }
