@@ -75,6 +75,10 @@ const char* srn_last_error(void);
 /* Number of CUDA kernels this library has launched in the calling process (bench.py's gpu_launches). */
 uint64_t srn_launch_count(void);
 
+/* Process-wide switch read by srn_build: 1 (default) runs aligned Dense/Conv problems on the tcgen05 tensor-core
+ * kernels, 0 routes every GEMM through the general CUDA-core kernels (A/B parity tests). */
+int srn_set_tensor_cores(int32_t on);
+
 /* Replaces EvolutionaryExperimentWorker.__init__ (experiment_worker.py:24-43). */
 int srn_create(const srn_config* cfg, srn_engine** out);
 void srn_destroy(srn_engine* h);

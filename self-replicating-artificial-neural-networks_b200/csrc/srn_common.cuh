@@ -28,6 +28,7 @@ struct Prob {
     int din_acc;           // 1: add into din instead of overwriting
     int indiv;             // index of the individual in the shard
     int coff;              // concat: channel offset of this input inside out (out has F channels)
+    int ldw;               // leading dimension of the kernel rows (F rounded up to 8; the pad stays zero)
 };
 
 // Where tensors 0 (image) and 1 (genotype) come from in this launch.

@@ -19,6 +19,7 @@
 
 #include "../../include/serann_b200.h"
 #include "srn_gemm_simt.cuh"
+#include "srn_gemm_tc.cuh"
 #include "srn_kernels.cuh"
 #include "srn_host.h"
 
@@ -44,6 +45,7 @@ enum Pass { P_FWD = 0, P_DGRAD, P_WGRAD, P_COL, P_BWD_EW, P_COUNT };
 struct Tensor {
     int H = 0, W = 0, C = 0;
     long long elems = 0;       // per sample
+    long long bs = 0;          // batch stride in elements: elems rounded up to 8 (the pad stays zero)
     int root = -1;             // tensor whose storage this one views
     bool needs_grad = false;
     int depth = 0;
@@ -55,7 +57,8 @@ struct Tensor {
 
 struct LayerRt {
     srn_layer_desc d;
-    long long w_off = -1, w_cnt = 0, b_off = -1, b_cnt = 0;   // trainable arena (elements)
+    long long w_off = -1, w_cnt = 0, b_off = -1, b_cnt = 0;   // trainable arena (elements; w_cnt counts padded rows)
+    int w_rows = 0, w_cols = 0, ldw = 0;                      // kernel as [w_rows][ldw], w_cols real columns
     long long mov_off = -1;                                   // moving-statistics arena
     long long save_off = -1;                                  // fp32 BN scratch arena
 };
@@ -73,7 +76,7 @@ struct Cached {
 };
 
 struct Group {
-    int depth, kind, cfgF, cfgC, ordinal;
+    int depth, kind, cfgF, cfgC, ordinal, tc;
     std::vector<Prob> h;
     Prob* d = nullptr;
     std::map<int, Cached> cache;
@@ -136,6 +139,16 @@ static inline bool grid_nonzero(unsigned g) { return g > 0; }
 static inline bool grid_nonzero(int g) { return g > 0; }
 static inline bool grid_nonzero(const dim3& g) { return g.x > 0 && g.y > 0 && g.z > 0; }
 
+#define LAUNCH_SMEM(cat, kern, grid, block, smem, ...)                                             \
+    do {                                                                                           \
+        if (grid_nonzero(grid)) {                                                                  \
+            ProfRec* pr_ = h->profiling ? prof_begin(h, (cat)) : nullptr;                          \
+            kern<<<(grid), (block), (smem), h->stream>>>(__VA_ARGS__);                             \
+            if (pr_) cudaEventRecord(pr_->b, h->stream);                                           \
+            g_launches.fetch_add(1, std::memory_order_relaxed);                                    \
+        }                                                                                          \
+    } while (0)
+
 static ProfRec* prof_begin(srn_engine* h, int cat) {
     ProfRec* r = new ProfRec();
     r->cat = cat;
@@ -176,6 +189,12 @@ extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
         return fail(SRN_ERR_CUDA, "srn_create: no CUDA device (%s); this engine has no CPU path", cudaGetErrorString(e));
     if (cfg->device < 0 || cfg->device >= count) return fail(SRN_ERR_ARG, "srn_create: device %d of %d", cfg->device, count);
     CK(cudaSetDevice(cfg->device));
+    {
+        const int max_smem = tc_smem_bytes(256);
+        CK(cudaFuncSetAttribute(k_gemm_tc<TC_FWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CK(cudaFuncSetAttribute(k_gemm_tc<TC_DGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CK(cudaFuncSetAttribute(k_gemm_tc<TC_WGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+    }
     srn_engine* h = new srn_engine();
     h->cfg = *cfg;
     h->xe = cfg->image_h * cfg->image_w;
@@ -235,6 +254,10 @@ extern "C" int srn_set_dataset(srn_engine* h, const float* x_train, const uint8_
 static inline long long align_up(long long v, long long a) { return (v + a - 1) / a * a; }
 
 static int cfg_for(int n) { return n <= 16 ? 2 : (n <= 32 ? 1 : 0); }
+// tensor-core N tile: 32 / 64 / 128 / 256 columns
+static int tc_cfg_for(int n) { return n <= 32 ? 0 : (n <= 64 ? 1 : (n <= 128 ? 2 : 3)); }
+static const int TC_BN[4] = {32, 64, 128, 256};
+static int g_tensor_cores = 1;      // srn_set_tensor_cores: 0 routes every GEMM through the SIMT kernels
 static const int CFG_BM[3] = {64, 128, 256};
 static const int CFG_BN[3] = {64, 32, 16};
 
@@ -302,8 +325,8 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
         if (nl <= 0) return fail(SRN_ERR_ARG, "individual %d has no layers", i);
         ind.layers.resize(nl);
         ind.tensors.resize(2 + nl);
-        Tensor& tx = ind.tensors[0]; tx.H = h->cfg.image_h; tx.W = h->cfg.image_w; tx.C = 1; tx.elems = h->xe; tx.root = 0;
-        Tensor& tg = ind.tensors[1]; tg.H = h->G; tg.W = 1; tg.C = 1; tg.elems = h->G; tg.root = 1;
+        Tensor& tx = ind.tensors[0]; tx.H = h->cfg.image_h; tx.W = h->cfg.image_w; tx.C = 1; tx.elems = h->xe; tx.bs = h->xe; tx.root = 0;
+        Tensor& tg = ind.tensors[1]; tg.H = h->G; tg.W = 1; tg.C = 1; tg.elems = h->G; tg.bs = h->G; tg.root = 1;
         for (int l = 0; l < nl; ++l) {
             LayerRt& L = ind.layers[l];
             L.d = layers[off[i] + l];
@@ -313,6 +336,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
             if (rc) { std::string m = g_error; return fail(rc, "individual %d: %s", i, m.c_str()); }
             Tensor& to = ind.tensors[2 + l];
             to.H = d.out_h; to.W = d.out_w; to.C = d.out_c; to.elems = (long long)d.out_h * d.out_w * d.out_c;
+            to.bs = align_up(to.elems, 8);
             bool ng = has_params(d.kind);
             int depth = 0;
             for (int j = 0; j < d.n_in; ++j) { ng = ng || ind.tensors[d.in[j]].needs_grad; depth = std::max(depth, ind.tensors[d.in[j]].depth); }
@@ -320,13 +344,14 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
             if (d.kind == SRN_KIND_RESHAPE) { to.root = ind.tensors[d.in[0]].root; to.depth = depth; }
             else { to.root = 2 + l; to.depth = depth + 1; }
             if (d.kind == SRN_KIND_DENSE || d.kind == SRN_KIND_CONV) {
-                L.w_cnt = (long long)d.kh * d.kw * d.in_c * d.units; L.b_cnt = d.units;
-                if (d.kind == SRN_KIND_DENSE) L.w_cnt = (long long)d.in_c * d.units;
+                L.w_rows = d.kind == SRN_KIND_DENSE ? d.in_c : d.kh * d.kw * d.in_c;
+                L.w_cols = d.units; L.ldw = (int)align_up(d.units, 8);
+                L.w_cnt = (long long)L.w_rows * L.ldw; L.b_cnt = d.units;
                 L.w_off = p_off; p_off = align_up(p_off + L.w_cnt, 8);
                 L.b_off = p_off; p_off = align_up(p_off + L.b_cnt, 8);
-                ind.pcount += L.w_cnt + L.b_cnt;
+                ind.pcount += (long long)L.w_rows * L.w_cols + L.b_cnt;
             } else if (d.kind == SRN_KIND_BN) {
-                L.w_cnt = L.b_cnt = d.in_c;
+                L.w_cnt = L.b_cnt = d.in_c; L.w_rows = 1; L.w_cols = L.ldw = d.in_c;
                 L.w_off = p_off; p_off = align_up(p_off + L.w_cnt, 8);
                 L.b_off = p_off; p_off = align_up(p_off + L.b_cnt, 8);
                 L.mov_off = s_off; s_off = align_up(s_off + 2LL * d.in_c, 8);
@@ -342,8 +367,8 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
             Tensor& T = ind.tensors[t];
             if (T.root != (int)t) continue;
             a_off = align_up(a_off, 64);
-            T.act_off = a_off; a_off += T.elems * MB;
-            if (T.needs_grad) { a_off = align_up(a_off, 64); T.grad_off = a_off; a_off += T.elems * MB; }
+            T.act_off = a_off; a_off += T.bs * MB;
+            if (T.needs_grad) { a_off = align_up(a_off, 64); T.grad_off = a_off; a_off += T.bs * MB; }
         }
     }
     h->p_elems = align_up(std::max(p_off, 8LL), 8); h->s_elems = std::max(s_off, 8LL);
@@ -392,8 +417,8 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                 p.indiv = i;
                 p.in_sel = ti.root == 0 ? 1 : (ti.root == 1 ? 2 : 0);
                 p.in = ti.act;
-                p.in_bs = (int)ti.elems;
-                p.out = to.act; p.out_bs = (int)to.elems;
+                p.in_bs = (int)ti.bs;
+                p.out = to.act; p.out_bs = (int)to.bs;
                 p.gout = to.grad;
                 p.din = ti.needs_grad ? ti.grad : nullptr;
                 int ordinal = 0;
@@ -402,13 +427,21 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                 p.Ho = d.out_h; p.Wo = d.out_w; p.F = d.out_c;
                 p.kh = 1; p.kw = 1; p.sh = 1; p.sw = 1;
                 p.act = d.act;
-                int cfgF = 0, cfgC = 0;
+                int cfgF = 0, cfgC = 0, tc = 0;
                 if (d.kind == SRN_KIND_DENSE || d.kind == SRN_KIND_CONV) {
                     if (d.kind == SRN_KIND_CONV) { p.kh = d.kh; p.kw = d.kw; p.sh = d.sh; p.sw = d.sw; }
                     else { p.H = d.in_h * d.in_w; p.W = 1; p.Ho = p.H; p.Wo = 1; }
                     p.w = h->P + L.w_off; p.bias = h->P + L.b_off;
                     p.gw = h->Gr + L.w_off; p.gb = h->Gr + L.b_off;
+                    p.ldw = L.ldw;
                     cfgF = cfg_for(p.F); cfgC = cfg_for(p.C);
+                    // tensor-core path: every 16-byte operand chunk must be aligned and stay inside one pixel
+                    const bool in_ok = p.in_sel == 0 && (p.C % 8 == 0 || (long long)d.in_h * d.in_w * d.in_c == d.in_c);
+                    const bool out_ok = p.F % 8 == 0 || (long long)d.out_h * d.out_w * d.out_c == d.out_c;
+                    if (g_tensor_cores && in_ok && out_ok && tc_k_fwd(p) >= 32) {
+                        tc = 1;
+                        cfgF = tc_cfg_for(p.F); cfgC = tc_cfg_for(p.C);
+                    }
                 } else if (d.kind == SRN_KIND_MAXPOOL) {
                     p.kh = d.kh; p.kw = d.kw; p.sh = d.sh; p.sw = d.sw;
                 } else if (d.kind == SRN_KIND_BN) {
@@ -423,15 +456,15 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                     for (int q = 0; q < j; ++q) coff += (int)(ind.tensors[d.in[q]].elems / rows);
                     p.coff = coff;
                 }
-                auto key = std::make_tuple(to.depth, d.kind, cfgF, cfgC, ordinal);
+                auto key = std::make_tuple(to.depth, d.kind, cfgF + 16 * tc, cfgC, ordinal);
                 Group& g = gmap[key];
-                g.depth = to.depth; g.kind = d.kind; g.cfgF = cfgF; g.cfgC = cfgC; g.ordinal = ordinal;
+                g.depth = to.depth; g.kind = d.kind; g.cfgF = cfgF; g.cfgC = cfgC; g.ordinal = ordinal; g.tc = tc;
                 g.h.push_back(p);
             }
         }
         Prob lp{};
         lp.indiv = i;
-        lp.out = ind.tensors.back().act; lp.gout = ind.tensors.back().grad; lp.out_bs = h->NL;
+        lp.out = ind.tensors.back().act; lp.gout = ind.tensors.back().grad; lp.out_bs = (int)ind.tensors.back().bs;
         h->h_loss.push_back(lp);
     }
     h->groups.clear();
@@ -474,7 +507,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                 } else {
                     la = lbm = (float)std::sqrt(6.0 / (fan_in + (double)d.units * rf));
                 }
-                LAUNCH(SRN_CAT_OTHER, k_init_uniform, (unsigned)((L.w_cnt + 255) / 256), 256, h->P + L.w_off, L.w_cnt, d.units, split, la, lbm, tseed);
+                LAUNCH(SRN_CAT_OTHER, k_init_uniform, (unsigned)((L.w_cnt + 255) / 256), 256, h->P + L.w_off, L.w_cnt, d.units, L.ldw, split, la, lbm, tseed);
             } else if (d.kind == SRN_KIND_BN) {
                 LAUNCH(SRN_CAT_OTHER, k_fill_f16, (unsigned)((L.w_cnt + 255) / 256), 256, h->P + L.w_off, L.w_cnt, 1.0f);          // gamma
                 LAUNCH(SRN_CAT_OTHER, k_fill_f16, (unsigned)((d.in_c + 255) / 256), 256, h->S + L.mov_off + d.in_c, (long long)d.in_c, 1.0f);  // moving variance
@@ -496,44 +529,57 @@ extern "C" int64_t srn_parameters_count(srn_engine* h, int32_t i) {
 
 extern "C" int64_t srn_device_bytes(srn_engine* h) { return h ? h->device_bytes : -1; }
 
-static int locate_weights(srn_engine* h, int ind, int layer, int which, __half** ptr, int64_t* cnt) {
+// weight `which` of a layer as a [rows][cols] matrix with leading dimension ld inside the arena
+static int locate_weights(srn_engine* h, int ind, int layer, int which, __half** ptr, int64_t* cnt, int* rows, int* cols, int* ld) {
     if (!h || !h->built) return fail(SRN_ERR_STATE, "weights: engine has no population");
     if (ind < 0 || ind >= h->n) return fail(SRN_ERR_ARG, "weights: individual %d", ind);
     Indiv& I = h->inds[ind];
     if (layer < 0 || layer >= (int)I.layers.size()) return fail(SRN_ERR_ARG, "weights: layer %d", layer);
     const LayerRt& L = I.layers[layer];
     const int kind = L.d.kind;
+    *ptr = nullptr;
     if (kind == SRN_KIND_DENSE || kind == SRN_KIND_CONV) {
-        if (which == 0) { *ptr = h->P + L.w_off; *cnt = L.w_cnt; return SRN_OK; }
-        if (which == 1) { *ptr = h->P + L.b_off; *cnt = L.b_cnt; return SRN_OK; }
+        if (which == 0) { *ptr = h->P + L.w_off; *rows = L.w_rows; *cols = L.w_cols; *ld = L.ldw; }
+        if (which == 1) { *ptr = h->P + L.b_off; *rows = 1; *cols = (int)L.b_cnt; *ld = (int)L.b_cnt; }
     } else if (kind == SRN_KIND_BN) {
         const int C = L.d.in_c;
-        *cnt = C;
-        if (which == 0) { *ptr = h->P + L.w_off; return SRN_OK; }
-        if (which == 1) { *ptr = h->P + L.b_off; return SRN_OK; }
-        if (which == 2) { *ptr = h->S + L.mov_off; return SRN_OK; }
-        if (which == 3) { *ptr = h->S + L.mov_off + C; return SRN_OK; }
+        *rows = 1; *cols = C; *ld = C;
+        if (which == 0) *ptr = h->P + L.w_off;
+        if (which == 1) *ptr = h->P + L.b_off;
+        if (which == 2) *ptr = h->S + L.mov_off;
+        if (which == 3) *ptr = h->S + L.mov_off + C;
     }
-    return fail(SRN_ERR_ARG, "weights: layer %d (kind %d) has no weight %d", layer, kind, which);
+    if (!*ptr) return fail(SRN_ERR_ARG, "weights: layer %d (kind %d) has no weight %d", layer, kind, which);
+    *cnt = (int64_t)*rows * *cols;
+    return SRN_OK;
 }
 
 extern "C" int srn_get_weights(srn_engine* h, int32_t ind, int32_t layer, int32_t which, uint16_t* buf, int64_t* count) {
-    __half* p; int64_t c;
-    int rc = locate_weights(h, ind, layer, which, &p, &c);
+    __half* p; int64_t c; int rows, cols, ld;
+    int rc = locate_weights(h, ind, layer, which, &p, &c, &rows, &cols, &ld);
     if (rc) return rc;
     if (count) *count = c;
-    if (buf) { CK(cudaSetDevice(h->cfg.device)); CK(cudaStreamSynchronize(h->stream)); CK(cudaMemcpy(buf, p, c * sizeof(__half), cudaMemcpyDeviceToHost)); }
+    if (buf) {
+        CK(cudaSetDevice(h->cfg.device));
+        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaMemcpy2D(buf, (size_t)cols * sizeof(__half), p, (size_t)ld * sizeof(__half), (size_t)cols * sizeof(__half), rows, cudaMemcpyDeviceToHost));
+    }
     return SRN_OK;
 }
 
 extern "C" int srn_set_weights(srn_engine* h, int32_t ind, int32_t layer, int32_t which, const uint16_t* buf, int64_t count) {
-    __half* p; int64_t c;
-    int rc = locate_weights(h, ind, layer, which, &p, &c);
+    __half* p; int64_t c; int rows, cols, ld;
+    int rc = locate_weights(h, ind, layer, which, &p, &c, &rows, &cols, &ld);
     if (rc) return rc;
     if (!buf || count != c) return fail(SRN_ERR_ARG, "set_weights: expected %lld elements, got %lld", (long long)c, (long long)count);
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
-    CK(cudaMemcpy(p, buf, c * sizeof(__half), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy2D(p, (size_t)ld * sizeof(__half), buf, (size_t)cols * sizeof(__half), (size_t)cols * sizeof(__half), rows, cudaMemcpyHostToDevice));
+    return SRN_OK;
+}
+
+extern "C" int srn_set_tensor_cores(int32_t on) {
+    g_tensor_cores = on ? 1 : 0;
     return SRN_OK;
 }
 
@@ -543,6 +589,13 @@ static int pass_items(const Group& g, const Prob& p, int pass, int nb) {
     switch (g.kind) {
         case SRN_KIND_DENSE:
         case SRN_KIND_CONV:
+            if (g.tc) {
+                if (pass == P_FWD) return tc_tiles_fwd(p, nb, TC_BN[g.cfgF]);
+                if (pass == P_DGRAD) return p.din ? tc_tiles_dgrad(p, nb, TC_BN[g.cfgC]) : 0;
+                if (pass == P_WGRAD) return tc_tiles_wgrad(p, nb, TC_BN[g.cfgF]);
+                if (pass == P_COL) return col_chunks((long long)nb * p.Ho * p.Wo);
+                return 0;
+            }
             if (pass == P_FWD) return fwd_tiles(nb * p.Ho * p.Wo, p.F, CFG_BM[g.cfgF], CFG_BN[g.cfgF]);
             if (pass == P_DGRAD) return p.din ? fwd_tiles(nb * p.H * p.W, p.C, CFG_BM[g.cfgC], CFG_BN[g.cfgC]) : 0;
             if (pass == P_WGRAD) return wgrad_tiles(p.kh * p.kw * p.C, p.F, nb * p.Ho * p.Wo);
@@ -611,6 +664,11 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
         switch (g.kind) {
             case SRN_KIND_DENSE:
             case SRN_KIND_CONV:
+                if (g.tc) {
+                    const int BN = TC_BN[g.cfgF];
+                    LAUNCH_SMEM(SRN_CAT_GEMM_FWD, k_gemm_tc<TC_FWD>, c->total[P_FWD], TC_THREADS, tc_smem_bytes(BN), g.d, c->prefix[P_FWD], np, nb, BN);
+                    break;
+                }
                 if (g.cfgF == 0) launch_fwd_cfg<0>(h, g, c, nb, I);
                 else if (g.cfgF == 1) launch_fwd_cfg<1>(h, g, c, nb, I);
                 else launch_fwd_cfg<2>(h, g, c, nb, I);
@@ -646,6 +704,12 @@ static int backward_pass(srn_engine* h, int nb, const Inputs& I) {
             case SRN_KIND_DENSE:
             case SRN_KIND_CONV:
                 LAUNCH(SRN_CAT_ACT_BWD, k_act_bwd_bias, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb);
+                if (g.tc) {
+                    const int BNf = TC_BN[g.cfgF], BNc = TC_BN[g.cfgC];
+                    LAUNCH_SMEM(SRN_CAT_GEMM_WGRAD, k_gemm_tc<TC_WGRAD>, c->total[P_WGRAD], TC_THREADS, tc_smem_bytes(BNf), g.d, c->prefix[P_WGRAD], np, nb, BNf);
+                    LAUNCH_SMEM(SRN_CAT_GEMM_DGRAD, k_gemm_tc<TC_DGRAD>, c->total[P_DGRAD], TC_THREADS, tc_smem_bytes(BNc), g.d, c->prefix[P_DGRAD], np, nb, BNc);
+                    break;
+                }
                 LAUNCH(SRN_CAT_GEMM_WGRAD, k_conv_wgrad, c->total[P_WGRAD], SIMT_THREADS, g.d, c->prefix[P_WGRAD], np, nb, I);
                 if (g.cfgC == 0) launch_dgrad_cfg<0>(h, g, c, nb);
                 else if (g.cfgC == 1) launch_dgrad_cfg<1>(h, g, c, nb);
@@ -984,18 +1048,18 @@ extern "C" int srn_debug_get_tensor(srn_engine* h, int32_t ind, int32_t tensor, 
     if (!src) return fail(SRN_ERR_ARG, "srn_debug_get_tensor: tensor %d has no %s buffer", tensor, grad ? "gradient" : "activation");
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
-    CK(cudaMemcpy(buf, src, (size_t)nb * T.elems * sizeof(__half), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy2D(buf, (size_t)T.elems * sizeof(__half), src, (size_t)T.bs * sizeof(__half), (size_t)T.elems * sizeof(__half), nb, cudaMemcpyDeviceToHost));
     return SRN_OK;
 }
 
 extern "C" int srn_debug_get_grad(srn_engine* h, int32_t ind, int32_t layer, int32_t which, float* buf, int64_t count) {
-    __half* p; int64_t c;
-    int rc = locate_weights(h, ind, layer, which, &p, &c);
+    __half* p; int64_t c; int rows, cols, ld;
+    int rc = locate_weights(h, ind, layer, which, &p, &c, &rows, &cols, &ld);
     if (rc) return rc;
     if (which > 1 || count != c) return fail(SRN_ERR_ARG, "srn_debug_get_grad: bad which/count");
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
-    CK(cudaMemcpy(buf, h->Gr + (p - h->P), c * sizeof(float), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy2D(buf, (size_t)cols * sizeof(float), h->Gr + (p - h->P), (size_t)ld * sizeof(float), (size_t)cols * sizeof(float), rows, cudaMemcpyDeviceToHost));
     return SRN_OK;
 }
 

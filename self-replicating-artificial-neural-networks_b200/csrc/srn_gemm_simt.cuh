@@ -103,7 +103,7 @@ k_conv_fwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, int n
         for (int r = 0; r < BR; ++r) {
             int k = k0 + bk0 + BKSTEP * r, n = n0 + bn;
             float v = 0.f;
-            if (k < K && n < N) v = __half2float(p.w[(long long)k * N + n]);
+            if (k < K && n < N) v = __half2float(p.w[(long long)k * p.ldw + n]);
             Bs[bk0 + BKSTEP * r][bn] = v;
         }
         __syncthreads();
@@ -190,7 +190,7 @@ k_conv_dgrad(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
             float v = 0.f;
             if (k < K && c < N) {
                 int ij = k / F, f = k - ij * F;
-                v = __half2float(p.w[((long long)ij * N + c) * F + f]);
+                v = __half2float(p.w[((long long)ij * N + c) * p.ldw + f]);
             }
             Bs[bk0 + BKSTEP * r][bn] = v;
         }
@@ -283,7 +283,7 @@ k_conv_wgrad(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             int f = f0 + tx * 4 + j;
-            if (f < F && acc[i][j] != 0.f) atomicAdd(&p.gw[(long long)kk * F + f], acc[i][j]);
+            if (f < F && acc[i][j] != 0.f) atomicAdd(&p.gw[(long long)kk * p.ldw + f], acc[i][j]);
         }
     }
 }

@@ -513,13 +513,16 @@ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
 }
 
 // uniform(-limit, limit) per element; columns >= split_col use limit_b (the fused head: two Dense layers)
-static __global__ void k_init_uniform(__half* w, long long count, int ncols, int split_col, float limit_a, float limit_b,
+// rows are `ld` elements apart; the pad columns [ncols, ld) stay zero
+static __global__ void k_init_uniform(__half* w, long long count, int ncols, int ld, int split_col, float limit_a, float limit_b,
                                uint64_t seed) {
     long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count) return;
+    const int col = (int)(i % ld);
+    if (col >= ncols) { w[i] = __float2half_rn(0.f); return; }
     uint64_t r = splitmix64(seed ^ splitmix64((uint64_t)i));
     float u = (float)(r >> 40) * (1.0f / 16777216.0f);          // [0, 1)
-    float limit = ((int)(i % ncols) >= split_col) ? limit_b : limit_a;
+    float limit = (col >= split_col) ? limit_b : limit_a;
     w[i] = __float2half_rn((2.f * u - 1.f) * limit);
 }
 

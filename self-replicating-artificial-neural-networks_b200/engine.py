@@ -80,6 +80,7 @@ def load_library(rebuild: bool = False) -> C.CDLL:
     lib.srn_readout.argtypes = [i32, vp, vp, i32, i32, i32, vp, vp]
     lib.srn_bn_train_forward.argtypes = [i32, vp, i64, i32, vp, vp, vp, vp, vp]
     lib.srn_bn_train_forward_noalloc.argtypes = [i32, vp, vp, i64, i32, vp, vp, vp, vp, vp]
+    lib.srn_set_tensor_cores.argtypes = [i32]
     lib.srn_profile.argtypes = [vp, i32]
     lib.srn_profile_read.argtypes = [vp, vp, vp]
     lib.srn_debug_step.argtypes = [vp, vp, i32, i32]
@@ -97,6 +98,11 @@ def _check(rc: int):
 
 def _ptr(a: Optional[np.ndarray]):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def set_tensor_cores(on: bool):
+    """Process-wide: route aligned GEMMs through tcgen05 (default) or everything through the SIMT kernels."""
+    _check(load_library().srn_set_tensor_cores(int(on)))
 
 
 def launch_count() -> int:

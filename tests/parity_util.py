@@ -51,7 +51,21 @@ con = Dense(units=32, activation='sigmoid')(con)
 
 loss_balance = 0.9"""
 
-HANDCRAFTED = [NET_A, NET_B, NET_C, NET_D]
+# tensor-core shapes: 64-wide and 256-wide N tiles, stride-2 convolution from 64 channels, Conv1D from 48 channels
+NET_E = """X_layer = Conv2D(filters=16, kernel_size=3, strides=1)(X_layer)
+X_layer = MaxPool2D(pool_size=2)(X_layer)
+X_layer = Conv2D(filters=64, kernel_size=3, strides=1)(X_layer)
+X_layer = Conv2D(filters=8, kernel_size=3, strides=2)(X_layer)
+g_layer = Dense(units=16, activation='relu')(g_layer)
+g_layer = Dense(units=48, activation='sigmoid')(g_layer)
+g_layer = Conv1D(filters=24, kernel_size=5, strides=1)(g_layer)
+con = concatenate([Reshape((1, -1))(X_layer), Reshape((1, -1))(g_layer)])
+con = Dense(units=200, activation='relu')(con)
+con = Dense(units=256, activation='sigmoid')(con)
+
+loss_balance = 0.5"""
+
+HANDCRAFTED = [NET_A, NET_B, NET_C, NET_D, NET_E]
 
 
 def small_population(n_generated=3, seed=11, max_flops=2.0e6):

@@ -17,13 +17,19 @@ ACT_TOL = 1e-2
 GRAD_TOL = 3e-2
 
 
-@pytest.fixture(scope='module')
-def setup():
+@pytest.fixture(scope='module', params=['tensor_cores', 'simt_only'])
+def setup(request):
+    """Every engine test runs twice: aligned GEMMs on the tcgen05 kernels (the product default), and everything
+    on the general CUDA-core kernels."""
+    from serann_b200.engine import set_tensor_cores
+    set_tensor_cores(request.param == 'tensor_cores')
     srcs, irs = U.small_population()
     data = U.small_dataset()
     eng, inds = U.make_engine_and_oracle(irs, data)
+    U.report([f'#### {request.param}'])
     yield srcs, irs, data, eng, inds
     eng.close()
+    set_tensor_cores(True)
 
 
 def test_parameters_count(setup):
