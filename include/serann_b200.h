@@ -189,15 +189,16 @@ int srn_bn_train_forward(int32_t device, const uint16_t* x, int64_t rows, int32_
  * already claimed the GPU's memory (a raw cudaMalloc from a plug-in can fail there, or break the
  * framework's accounting), and latency-sensitive loops, because cudaMalloc/cudaFree synchronise the
  * whole device.  This entry point calls no cudaMalloc, cudaFree or allocating library routine: its working
- * storage (per-channel statistics, per-1024-row partial sums, the launch descriptor) is a fixed array of
+ * storage (per-channel statistics, per-block partial sums, the launch descriptor) is a fixed array of
  * SRN_NOALLOC_SCRATCH_BYTES that is part of the library image - every GPU that loads the library holds
  * those bytes until the process exits.
  *   - All d_* pointers are DEVICE pointers that the caller allocated; d_moving_variance must be
  *     d_moving_mean + C (one [2][C] fp16 array).  `stream` is a cudaStream_t (NULL = default stream);
  *     the call returns after the stream has finished the work.
- *   - Limit: C * (4 + 2 * ceil(rows / 1024)) floats must fit in SRN_NOALLOC_SCRATCH_BYTES - 512
- *     (e.g. 750*784 rows x 128 channels fits; 16M rows x 64 channels does not).  Larger problems are
- *     refused with SRN_ERR_LIMIT; use srn_bn_train_forward for those.
+ *   - Limit: C * (4 + 2 * ceil(rows / R)) floats must fit in SRN_NOALLOC_SCRATCH_BYTES - 512, where R is the
+ *     number of rows one thread block reduces: R = 16 * max(1, 256 / n) with n = C / 8 when C is a multiple
+ *     of 8, else n = C (e.g. 750*784 rows x 128 channels fits; 16M rows x 64 channels does not).  Larger
+ *     problems are refused with SRN_ERR_LIMIT; use srn_bn_train_forward for those.
  *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress); make that
  *     first call before starting any stream capture.
  *   - Every call uses the same array and leaves its last contents there.  Nothing in it has to be zero on

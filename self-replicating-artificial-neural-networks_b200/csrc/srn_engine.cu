@@ -43,10 +43,12 @@ static inline float h16(float x) { return __half2float(__float2half_rn(x)); }
 enum Pass { P_FWD = 0, P_DGRAD, P_WGRAD, P_COL, P_BWD_EW, P_COUNT };
 
 struct Tensor {
-    int H = 0, W = 0, C = 0;
-    long long elems = 0;       // per sample
-    long long bs = 0;          // batch stride in elements: elems rounded up to 8 (the pad stays zero)
+    long long rows = 0;        // per sample: product of the leading axes
+    int C = 0, Cs = 0;         // channels and channel stride (C rounded up to 8; 1 for the model inputs)
+    long long elems = 0;       // rows * C
+    long long bs = 0;          // batch stride in elements = rows * Cs
     int root = -1;             // tensor whose storage this one views
+    bool view = false;
     bool needs_grad = false;
     int depth = 0;
     int consumers = 0;         // consumers needing din (counted on the root)
@@ -61,6 +63,7 @@ struct LayerRt {
     int w_rows = 0, w_cols = 0, ldw = 0;                      // kernel as [w_rows][ldw], w_cols real columns
     long long mov_off = -1;                                   // moving-statistics arena
     long long save_off = -1;                                  // fp32 BN scratch arena
+    bool copy = false, dead = false;                          // reshape that needs a compacting copy / is never read
 };
 
 struct Indiv {
@@ -191,9 +194,11 @@ extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
     CK(cudaSetDevice(cfg->device));
     {
         const int max_smem = tc_smem_bytes(256);
-        CK(cudaFuncSetAttribute(k_gemm_tc<TC_FWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CK(cudaFuncSetAttribute(k_gemm_tc<TC_DGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CK(cudaFuncSetAttribute(k_gemm_tc<TC_WGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CK(cudaFuncSetAttribute(k_gemm_tc<TC_FWD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CK(cudaFuncSetAttribute(k_gemm_tc<TC_FWD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CK(cudaFuncSetAttribute(k_gemm_tc<TC_DGRAD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CK(cudaFuncSetAttribute(k_gemm_tc<TC_WGRAD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CK(cudaFuncSetAttribute(k_gemm_tc<TC_WGRAD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
     }
     srn_engine* h = new srn_engine();
     h->cfg = *cfg;
@@ -272,6 +277,8 @@ static int validate_layer(const srn_layer_desc& d, const std::vector<Tensor>& ts
     const long long in_e = (long long)d.in_h * d.in_w * d.in_c, out_e = (long long)d.out_h * d.out_w * d.out_c;
     if (in_e <= 0 || out_e <= 0) return fail(SRN_ERR_ARG, "layer %d: empty tensor", li);
     if (d.kind != SRN_KIND_CONCAT && in_e != t0.elems) return fail(SRN_ERR_ARG, "layer %d: input has %lld elements, descriptor says %lld", li, t0.elems, in_e);
+    if (d.kind != SRN_KIND_CONCAT && d.kind != SRN_KIND_RESHAPE && (d.in_c != t0.C || (long long)d.in_h * d.in_w != t0.rows))
+        return fail(SRN_ERR_ARG, "layer %d: input is (%lld rows, %d channels), descriptor says (%d x %d, %d)", li, t0.rows, t0.C, d.in_h, d.in_w, d.in_c);
     switch (d.kind) {
         case SRN_KIND_DENSE:
             if (d.units <= 0 || d.out_c != d.units || d.out_h * d.out_w != d.in_h * d.in_w) return fail(SRN_ERR_ARG, "layer %d: bad Dense shape", li);
@@ -317,7 +324,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
     const int MB = h->cfg.max_batch;
     h->inds.resize(n);
     long long p_off = 0, s_off = 0, a_off = 0, sv_off = 0;
-    // ---- pass 1: tensors, parameter offsets, sizes
+    // ---- pass 1: tensors (rows, C, channel stride), parameter offsets, sizes
     for (int i = 0; i < n; ++i) {
         Indiv& ind = h->inds[i];
         ind.lb = loss_balance[i];
@@ -325,8 +332,20 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
         if (nl <= 0) return fail(SRN_ERR_ARG, "individual %d has no layers", i);
         ind.layers.resize(nl);
         ind.tensors.resize(2 + nl);
-        Tensor& tx = ind.tensors[0]; tx.H = h->cfg.image_h; tx.W = h->cfg.image_w; tx.C = 1; tx.elems = h->xe; tx.bs = h->xe; tx.root = 0;
-        Tensor& tg = ind.tensors[1]; tg.H = h->G; tg.W = 1; tg.C = 1; tg.elems = h->G; tg.bs = h->G; tg.root = 1;
+        Tensor& tx = ind.tensors[0]; tx.rows = h->xe; tx.C = tx.Cs = 1; tx.elems = h->xe; tx.bs = h->xe; tx.root = 0;
+        Tensor& tg = ind.tensors[1]; tg.rows = h->G; tg.C = tg.Cs = 1; tg.elems = h->G; tg.bs = h->G; tg.root = 1;
+        // a concatenate reads through reshapes (flat order is preserved), so a reshape that would need a
+        // compacting copy is only materialised when something else consumes it
+        std::vector<int> used(2 + nl, 0);
+        auto chase = [&](int t) { while (t >= 2 && layers[off[i] + t - 2].kind == SRN_KIND_RESHAPE) t = layers[off[i] + t - 2].in[0]; return t; };
+        for (int l = 0; l < nl; ++l) {
+            const srn_layer_desc& d = layers[off[i] + l];
+            for (int j = 0; j < d.n_in && j < SRN_MAX_CONCAT_INPUTS; ++j) {
+                if (d.in[j] < 0 || d.in[j] >= 2 + l) return fail(SRN_ERR_ARG, "individual %d layer %d: input id %d out of range", i, l, d.in[j]);
+                used[d.kind == SRN_KIND_CONCAT ? chase(d.in[j]) : d.in[j]] += 1;
+            }
+        }
+        used[1 + nl] += 1;
         for (int l = 0; l < nl; ++l) {
             LayerRt& L = ind.layers[l];
             L.d = layers[off[i] + l];
@@ -335,14 +354,29 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
             int rc = validate_layer(d, visible, l);
             if (rc) { std::string m = g_error; return fail(rc, "individual %d: %s", i, m.c_str()); }
             Tensor& to = ind.tensors[2 + l];
-            to.H = d.out_h; to.W = d.out_w; to.C = d.out_c; to.elems = (long long)d.out_h * d.out_w * d.out_c;
-            to.bs = align_up(to.elems, 8);
+            const Tensor& ti = ind.tensors[d.in[0]];
+            to.rows = (long long)d.out_h * d.out_w; to.C = d.out_c; to.elems = to.rows * to.C;
             bool ng = has_params(d.kind);
             int depth = 0;
-            for (int j = 0; j < d.n_in; ++j) { ng = ng || ind.tensors[d.in[j]].needs_grad; depth = std::max(depth, ind.tensors[d.in[j]].depth); }
+            for (int j = 0; j < d.n_in; ++j) {
+                const Tensor& tj = ind.tensors[d.kind == SRN_KIND_CONCAT ? chase(d.in[j]) : d.in[j]];
+                ng = ng || tj.needs_grad; depth = std::max(depth, tj.depth);
+            }
             to.needs_grad = ng;
-            if (d.kind == SRN_KIND_RESHAPE) { to.root = ind.tensors[d.in[0]].root; to.depth = depth; }
-            else { to.root = 2 + l; to.depth = depth + 1; }
+            to.root = 2 + l; to.depth = depth + 1;
+            to.Cs = (int)align_up(to.C, 8);
+            if (d.kind == SRN_KIND_BN || d.kind == SRN_KIND_MAXPOOL) to.Cs = ti.Cs;     // same channels in and out
+            if (d.kind == SRN_KIND_RESHAPE) {
+                const bool src_flat = ti.Cs == ti.C || ti.rows == 1;
+                if (src_flat && (to.rows == 1 || to.C % 8 == 0)) {       // pure view of the source's storage
+                    to.root = ti.root; to.depth = depth; to.view = true;
+                    to.Cs = to.rows == 1 ? (int)ti.bs : to.C;
+                } else {
+                    L.copy = true;                                       // compacting copy, skipped when unused
+                    L.dead = used[2 + l] == 0;
+                }
+            }
+            to.bs = to.view ? ti.bs : to.rows * to.Cs;
             if (d.kind == SRN_KIND_DENSE || d.kind == SRN_KIND_CONV) {
                 L.w_rows = d.kind == SRN_KIND_DENSE ? d.in_c : d.kh * d.kw * d.in_c;
                 L.w_cols = d.units; L.ldw = (int)align_up(d.units, 8);
@@ -355,24 +389,24 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                 L.w_off = p_off; p_off = align_up(p_off + L.w_cnt, 8);
                 L.b_off = p_off; p_off = align_up(p_off + L.b_cnt, 8);
                 L.mov_off = s_off; s_off = align_up(s_off + 2LL * d.in_c, 8);
-                const long long rows_max = (long long)MB * d.in_h * d.in_w;
-                L.save_off = sv_off; sv_off += 4LL * d.in_c + 2LL * d.in_c * col_chunks(rows_max);
+                const long long rows_max = (long long)MB * ti.rows;
+                L.save_off = sv_off; sv_off += 4LL * ti.Cs + 2LL * ti.Cs * col_chunks(rows_max, ti.Cs);
                 ind.pcount += 4LL * d.in_c;
             }
         }
-        if (ind.tensors.back().elems != h->NL)
-            return fail(SRN_ERR_ARG, "individual %d: last layer must emit n_classes + genotype_size = %d values, has %lld", i, h->NL, ind.tensors.back().elems);
-        // storage: every root tensor except the two inputs gets activations; grads where needed
+        if (ind.tensors.back().elems != h->NL || ind.tensors.back().rows != 1)
+            return fail(SRN_ERR_ARG, "individual %d: last layer must emit one row of n_classes + genotype_size = %d values", i, h->NL);
+        // storage: every tensor that owns memory gets activations; gradients where needed
         for (size_t t = 2; t < ind.tensors.size(); ++t) {
             Tensor& T = ind.tensors[t];
-            if (T.root != (int)t) continue;
+            if (T.view || ind.layers[t - 2].dead) continue;
             a_off = align_up(a_off, 64);
             T.act_off = a_off; a_off += T.bs * MB;
             if (T.needs_grad) { a_off = align_up(a_off, 64); T.grad_off = a_off; a_off += T.bs * MB; }
         }
     }
     h->p_elems = align_up(std::max(p_off, 8LL), 8); h->s_elems = std::max(s_off, 8LL);
-    h->act_elems = a_off; h->save_elems = std::max(sv_off, 8LL);
+    h->act_elems = std::max(a_off, 64LL); h->save_elems = std::max(sv_off, 8LL);
     const size_t pb = (size_t)h->p_elems * sizeof(__half);
     CK(cudaMalloc(&h->P, pb)); CK(cudaMalloc(&h->M, pb)); CK(cudaMalloc(&h->V, pb));
     CK(cudaMalloc(&h->Gr, (size_t)h->p_elems * sizeof(float)));
@@ -386,12 +420,13 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
         }
     }
     h->device_bytes = 3LL * pb + h->p_elems * 4 + h->s_elems * 2 + h->save_elems * 4 + h->act_elems * 2;
+    // everything starts at zero; the channel / row pads of tensors and kernels are never written afterwards
     CK(cudaMemsetAsync(h->P, 0, pb, h->stream)); CK(cudaMemsetAsync(h->M, 0, pb, h->stream)); CK(cudaMemsetAsync(h->V, 0, pb, h->stream));
     CK(cudaMemsetAsync(h->Gr, 0, (size_t)h->p_elems * sizeof(float), h->stream));
     CK(cudaMemsetAsync(h->S, 0, (size_t)h->s_elems * sizeof(__half), h->stream));
     CK(cudaMemsetAsync(h->save, 0, (size_t)h->save_elems * sizeof(float), h->stream));
     CK(cudaMemsetAsync(h->act, 0, (size_t)h->act_elems * sizeof(__half), h->stream));
-    // ---- pass 2: fix up pointers, count consumers, build problem groups
+    // ---- pass 2: pointers, consumer ordinals, problem groups
     std::map<std::tuple<int, int, int, int, int>, Group> gmap;
     h->h_loss.clear();
     for (int i = 0; i < n; ++i) {
@@ -399,18 +434,20 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
         for (auto& T : ind.tensors) {
             if (T.act_off >= 0) T.act = h->act + T.act_off;
             if (T.grad_off >= 0) T.grad = h->act + T.grad_off;
-        }
-        for (auto& T : ind.tensors) {            // views share the root's storage
-            if (T.root >= 2) { T.act = ind.tensors[T.root].act; T.grad = ind.tensors[T.root].grad; }
             T.consumers = 0;
         }
+        for (auto& T : ind.tensors)              // views share the root's storage (roots precede their views)
+            if (T.view) { T.act = ind.tensors[T.root].act; T.grad = ind.tensors[T.root].grad; }
+        auto chase = [&](int t) { while (t >= 2 && ind.layers[t - 2].d.kind == SRN_KIND_RESHAPE) t = ind.layers[t - 2].d.in[0]; return t; };
         for (size_t l = 0; l < ind.layers.size(); ++l) {
             const LayerRt& L = ind.layers[l];
             const srn_layer_desc& d = L.d;
-            if (d.kind == SRN_KIND_RESHAPE) continue;
+            if (d.kind == SRN_KIND_RESHAPE && (!L.copy || L.dead)) continue;
+            const bool is_copy = d.kind == SRN_KIND_CONCAT || d.kind == SRN_KIND_RESHAPE;
             const Tensor& to = ind.tensors[2 + l];
+            int coff = 0;
             for (int j = 0; j < d.n_in; ++j) {
-                const int tin = d.in[j];
+                const int tin = d.kind == SRN_KIND_CONCAT ? chase(d.in[j]) : d.in[j];
                 Tensor& ti = ind.tensors[tin];
                 Tensor& troot = ind.tensors[ti.root];
                 Prob p{};
@@ -423,42 +460,42 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                 p.din = ti.needs_grad ? ti.grad : nullptr;
                 int ordinal = 0;
                 if (p.din) ordinal = troot.consumers++;
-                p.H = d.in_h; p.W = d.in_w; p.C = d.in_c;
-                p.Ho = d.out_h; p.Wo = d.out_w; p.F = d.out_c;
+                p.H = d.in_h; p.W = d.in_w; p.C = ti.C; p.Cs = ti.Cs;
+                p.Ho = d.out_h; p.Wo = d.out_w; p.F = to.C; p.Fs = to.Cs;
                 p.kh = 1; p.kw = 1; p.sh = 1; p.sw = 1;
                 p.act = d.act;
-                int cfgF = 0, cfgC = 0, tc = 0;
+                int cfgF = 0, cfgC = 0, tc = 0, kind = d.kind;
                 if (d.kind == SRN_KIND_DENSE || d.kind == SRN_KIND_CONV) {
                     if (d.kind == SRN_KIND_CONV) { p.kh = d.kh; p.kw = d.kw; p.sh = d.sh; p.sw = d.sw; }
-                    else { p.H = d.in_h * d.in_w; p.W = 1; p.Ho = p.H; p.Wo = 1; }
+                    else { p.H = (int)ti.rows; p.W = 1; p.Ho = p.H; p.Wo = 1; }
                     p.w = h->P + L.w_off; p.bias = h->P + L.b_off;
                     p.gw = h->Gr + L.w_off; p.gb = h->Gr + L.b_off;
                     p.ldw = L.ldw;
                     cfgF = cfg_for(p.F); cfgC = cfg_for(p.C);
-                    // tensor-core path: every 16-byte operand chunk must be aligned and stay inside one pixel
-                    const bool in_ok = p.in_sel == 0 && (p.C % 8 == 0 || (long long)d.in_h * d.in_w * d.in_c == d.in_c);
-                    const bool out_ok = p.F % 8 == 0 || (long long)d.out_h * d.out_w * d.out_c == d.out_c;
-                    if (g_tensor_cores && in_ok && out_ok && tc_k_fwd(p) >= 32) {
-                        tc = 1;
-                        cfgF = tc_cfg_for(p.F); cfgC = tc_cfg_for(p.C);
+                    if (g_tensor_cores) {
+                        // 1: operands in 16-byte chunks (channel stride padded to 8); 2: first layers on a one-channel
+                        // model input, im2col gathered element by element
+                        if (p.Cs % 8 == 0 && p.Fs % 8 == 0 && tc_k_fwd(p) >= 32) tc = 1;
+                        else if (p.in_sel != 0 && p.Cs == 1 && p.C == 1 && p.Fs % 8 == 0 && p.kh * p.kw >= 9) tc = 2;
+                        if (tc) { cfgF = tc_cfg_for(p.F); cfgC = tc_cfg_for(p.C); }
                     }
                 } else if (d.kind == SRN_KIND_MAXPOOL) {
                     p.kh = d.kh; p.kw = d.kw; p.sh = d.sh; p.sw = d.sw;
                 } else if (d.kind == SRN_KIND_BN) {
-                    p.H = d.in_h * d.in_w; p.W = 1;
+                    p.H = (int)ti.rows; p.W = 1;
                     p.w = h->P + L.w_off; p.bias = h->P + L.b_off;
                     p.gw = h->Gr + L.w_off; p.gb = h->Gr + L.b_off;
                     p.mov = h->S + L.mov_off; p.save = h->save + L.save_off;
-                } else if (d.kind == SRN_KIND_CONCAT) {
-                    const long long rows = (long long)d.out_h * d.out_w;
-                    p.H = (int)rows; p.W = 1; p.C = (int)(ti.elems / rows);
-                    int coff = 0;
-                    for (int q = 0; q < j; ++q) coff += (int)(ind.tensors[d.in[q]].elems / rows);
+                } else if (is_copy) {
+                    kind = SRN_KIND_CONCAT;
+                    p.n_el = (int)ti.elems;
+                    p.Cj = (int)(ti.elems / to.rows);
                     p.coff = coff;
+                    coff += p.Cj;
                 }
-                auto key = std::make_tuple(to.depth, d.kind, cfgF + 16 * tc, cfgC, ordinal);
+                auto key = std::make_tuple(to.depth, kind, cfgF + 16 * tc, cfgC, ordinal);
                 Group& g = gmap[key];
-                g.depth = to.depth; g.kind = d.kind; g.cfgF = cfgF; g.cfgC = cfgC; g.ordinal = ordinal; g.tc = tc;
+                g.depth = to.depth; g.kind = kind; g.cfgF = cfgF; g.cfgC = cfgC; g.ordinal = ordinal; g.tc = tc;
                 g.h.push_back(p);
             }
         }
@@ -585,37 +622,35 @@ extern "C" int srn_set_tensor_cores(int32_t on) {
 
 // ------------------------------------------------------------------ launch plan per batch size
 static int pass_items(const Group& g, const Prob& p, int pass, int nb) {
-    const long long in_e = (long long)p.H * p.W * p.C, out_e = (long long)p.Ho * p.Wo * p.F;
+    const long long in_rows = (long long)nb * p.H * p.W, out_rows = (long long)nb * p.Ho * p.Wo;
     switch (g.kind) {
         case SRN_KIND_DENSE:
         case SRN_KIND_CONV:
+            if (pass == P_COL) return col_chunks(out_rows, p.Fs);
             if (g.tc) {
                 if (pass == P_FWD) return tc_tiles_fwd(p, nb, TC_BN[g.cfgF]);
                 if (pass == P_DGRAD) return p.din ? tc_tiles_dgrad(p, nb, TC_BN[g.cfgC]) : 0;
                 if (pass == P_WGRAD) return tc_tiles_wgrad(p, nb, TC_BN[g.cfgF]);
-                if (pass == P_COL) return col_chunks((long long)nb * p.Ho * p.Wo);
                 return 0;
             }
             if (pass == P_FWD) return fwd_tiles(nb * p.Ho * p.Wo, p.F, CFG_BM[g.cfgF], CFG_BN[g.cfgF]);
             if (pass == P_DGRAD) return p.din ? fwd_tiles(nb * p.H * p.W, p.C, CFG_BM[g.cfgC], CFG_BN[g.cfgC]) : 0;
             if (pass == P_WGRAD) return wgrad_tiles(p.kh * p.kw * p.C, p.F, nb * p.Ho * p.Wo);
-            if (pass == P_COL) return col_chunks((long long)nb * p.Ho * p.Wo);
             return 0;
         case SRN_KIND_MAXPOOL:
-            if (pass == P_FWD) return ew_blocks((long long)nb * p.Ho * p.Wo * p.C);
-            if (pass == P_BWD_EW) return p.din ? ew_blocks(nb * in_e) : 0;
+            if (pass == P_FWD) return ew_blocks(out_rows, p.Cs);
+            if (pass == P_BWD_EW) return p.din ? ew_blocks(in_rows, p.Cs) : 0;
             return 0;
         case SRN_KIND_BN:
-            if (pass == P_FWD) return ew_blocks(nb * in_e);
-            if (pass == P_COL) return col_chunks((long long)nb * p.H * p.W);
-            if (pass == P_BWD_EW) return p.din ? ew_blocks(nb * in_e) : 0;
+            if (pass == P_FWD) return ew_blocks(in_rows, p.Cs);
+            if (pass == P_COL) return col_chunks(in_rows, p.Cs);
+            if (pass == P_BWD_EW) return p.din ? ew_blocks(in_rows, p.Cs) : 0;
             return 0;
         case SRN_KIND_CONCAT:
-            if (pass == P_FWD) return ew_blocks(nb * in_e);
-            if (pass == P_BWD_EW) return p.din ? ew_blocks(nb * in_e) : 0;
+            if (pass == P_FWD) return copy_blocks((long long)nb * p.n_el);
+            if (pass == P_BWD_EW) return p.din ? copy_blocks((long long)nb * p.n_el) : 0;
             return 0;
     }
-    (void)out_e;
     return 0;
 }
 
@@ -666,7 +701,8 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
             case SRN_KIND_CONV:
                 if (g.tc) {
                     const int BN = TC_BN[g.cfgF];
-                    LAUNCH_SMEM(SRN_CAT_GEMM_FWD, k_gemm_tc<TC_FWD>, c->total[P_FWD], TC_THREADS, tc_smem_bytes(BN), g.d, c->prefix[P_FWD], np, nb, BN);
+                    if (g.tc == 1) LAUNCH_SMEM(SRN_CAT_GEMM_FWD, (k_gemm_tc<TC_FWD, false>), c->total[P_FWD], TC_THREADS, tc_smem_bytes(BN), g.d, c->prefix[P_FWD], np, nb, BN, I);
+                    else LAUNCH_SMEM(SRN_CAT_GEMM_FWD, (k_gemm_tc<TC_FWD, true>), c->total[P_FWD], TC_THREADS, tc_smem_bytes(BN), g.d, c->prefix[P_FWD], np, nb, BN, I);
                     break;
                 }
                 if (g.cfgF == 0) launch_fwd_cfg<0>(h, g, c, nb, I);
@@ -686,7 +722,7 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
                 LAUNCH(SRN_CAT_BN, k_bn_apply, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I);
                 break;
             case SRN_KIND_CONCAT:
-                LAUNCH(SRN_CAT_CONCAT, k_concat, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I, 0);
+                LAUNCH(SRN_CAT_CONCAT, k_copy, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I, 0);
                 break;
         }
     }
@@ -706,8 +742,9 @@ static int backward_pass(srn_engine* h, int nb, const Inputs& I) {
                 LAUNCH(SRN_CAT_ACT_BWD, k_act_bwd_bias, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb);
                 if (g.tc) {
                     const int BNf = TC_BN[g.cfgF], BNc = TC_BN[g.cfgC];
-                    LAUNCH_SMEM(SRN_CAT_GEMM_WGRAD, k_gemm_tc<TC_WGRAD>, c->total[P_WGRAD], TC_THREADS, tc_smem_bytes(BNf), g.d, c->prefix[P_WGRAD], np, nb, BNf);
-                    LAUNCH_SMEM(SRN_CAT_GEMM_DGRAD, k_gemm_tc<TC_DGRAD>, c->total[P_DGRAD], TC_THREADS, tc_smem_bytes(BNc), g.d, c->prefix[P_DGRAD], np, nb, BNc);
+                    if (g.tc == 1) LAUNCH_SMEM(SRN_CAT_GEMM_WGRAD, (k_gemm_tc<TC_WGRAD, false>), c->total[P_WGRAD], TC_THREADS, tc_smem_bytes(BNf), g.d, c->prefix[P_WGRAD], np, nb, BNf, I);
+                    else LAUNCH_SMEM(SRN_CAT_GEMM_WGRAD, (k_gemm_tc<TC_WGRAD, true>), c->total[P_WGRAD], TC_THREADS, tc_smem_bytes(BNf), g.d, c->prefix[P_WGRAD], np, nb, BNf, I);
+                    LAUNCH_SMEM(SRN_CAT_GEMM_DGRAD, (k_gemm_tc<TC_DGRAD, false>), c->total[P_DGRAD], TC_THREADS, tc_smem_bytes(BNc), g.d, c->prefix[P_DGRAD], np, nb, BNc, I);
                     break;
                 }
                 LAUNCH(SRN_CAT_GEMM_WGRAD, k_conv_wgrad, c->total[P_WGRAD], SIMT_THREADS, g.d, c->prefix[P_WGRAD], np, nb, I);
@@ -724,7 +761,7 @@ static int backward_pass(srn_engine* h, int nb, const Inputs& I) {
                 LAUNCH(SRN_CAT_BN, k_bn_bwd_apply, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I);
                 break;
             case SRN_KIND_CONCAT:
-                LAUNCH(SRN_CAT_CONCAT, k_concat, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I, 1);
+                LAUNCH(SRN_CAT_CONCAT, k_copy, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I, 1);
                 break;
         }
     }
@@ -1048,7 +1085,7 @@ extern "C" int srn_debug_get_tensor(srn_engine* h, int32_t ind, int32_t tensor, 
     if (!src) return fail(SRN_ERR_ARG, "srn_debug_get_tensor: tensor %d has no %s buffer", tensor, grad ? "gradient" : "activation");
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
-    CK(cudaMemcpy2D(buf, (size_t)T.elems * sizeof(__half), src, (size_t)T.bs * sizeof(__half), (size_t)T.elems * sizeof(__half), nb, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy2D(buf, (size_t)T.C * sizeof(__half), src, (size_t)T.Cs * sizeof(__half), (size_t)T.C * sizeof(__half), (size_t)nb * T.rows, cudaMemcpyDeviceToHost));
     return SRN_OK;
 }
 

@@ -70,7 +70,7 @@ k_conv_fwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, int n
         if (m < M) {
             int b = m / HoWo, rem = m - b * HoWo;
             int ho = rem / p.Wo, wo = rem - ho * p.Wo;
-            arow_off[r] = (long long)b * in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * p.C;
+            arow_off[r] = (long long)b * in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * p.Cs;
         } else {
             arow_off[r] = -1;
         }
@@ -82,15 +82,16 @@ k_conv_fwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, int n
 
     const int ty = tid / T::TX, tx = tid % T::TX;
     float acc[4][4] = {};
-    const int kwC = p.kw * p.C, WC = p.W * p.C;
+    const int kwC = p.kw * p.C;
 
     for (int k0 = 0; k0 < K; k0 += SIMT_BK) {
         {
             int k = k0 + ak;
             int koff = -1;
-            if (k < K) {
-                int i = k / kwC;
-                koff = i * WC + (k - i * kwC);
+            if (k < K) {                      // k = (i, j, c) over real channels; memory steps by the channel stride
+                int i = k / kwC, rem = k - i * kwC;
+                int j = rem / p.C, c = rem - j * p.C;
+                koff = (i * p.W + j) * p.Cs + c;
             }
 #pragma unroll
             for (int r = 0; r < AR; ++r) {
@@ -116,7 +117,7 @@ k_conv_fwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, int n
         int m = m0 + ty * 4 + i;
         if (m >= M) continue;
         int b = m / HoWo, rem = m - b * HoWo;
-        __half* orow = p.out + (long long)b * p.out_bs + (long long)rem * N;
+        __half* orow = p.out + (long long)b * p.out_bs + (long long)rem * p.Fs;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             int n = n0 + tx * 4 + j;
@@ -178,7 +179,7 @@ k_conv_dgrad(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
                     if (hh >= 0 && ww >= 0) {
                         int ho = hh / p.sh, wo = ww / p.sw;
                         if (ho * p.sh == hh && wo * p.sw == ww && ho < p.Ho && wo < p.Wo)
-                            v = __half2float(p.gout[(long long)ab[r] * p.out_bs + ((long long)ho * p.Wo + wo) * F + f]);
+                            v = __half2float(p.gout[(long long)ab[r] * p.out_bs + ((long long)ho * p.Wo + wo) * p.Fs + f]);
                     }
                 }
                 As[ak][tid / SIMT_BK + 16 * r] = v;
@@ -203,7 +204,7 @@ k_conv_dgrad(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
         int m = m0 + ty * 4 + i;
         if (m >= M) continue;
         int b = m / HW, rem = m - b * HW;
-        __half* drow = p.din + (long long)b * p.in_bs + (long long)rem * N;
+        __half* drow = p.din + (long long)b * p.in_bs + (long long)rem * p.Cs;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             int c = n0 + tx * 4 + j;
@@ -247,8 +248,9 @@ k_conv_wgrad(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
     long long akoff = -1;
     if (akk < Kf) {
         int kwC = p.kw * p.C;
-        int i = akk / kwC;
-        akoff = (long long)i * p.W * p.C + (akk - i * kwC);
+        int i = akk / kwC, rem = akk - i * kwC;
+        int j = rem / p.C, c = rem - j * p.C;
+        akoff = ((long long)i * p.W + j) * p.Cs + c;
     }
     const int bf = f0 + (tid % 64);
     const int mr0 = tid / 64;                 // 0..3
@@ -265,9 +267,9 @@ k_conv_wgrad(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
                 int b = m / HoWo, rem = m - b * HoWo;
                 if (akoff >= 0) {
                     int ho = rem / p.Wo, wo = rem - ho * p.Wo;
-                    av = __half2float(in[(long long)b * in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * p.C + akoff]);
+                    av = __half2float(in[(long long)b * in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * p.Cs + akoff]);
                 }
-                if (bf < F) bv = __half2float(p.gout[(long long)b * p.out_bs + (long long)rem * F + bf]);
+                if (bf < F) bv = __half2float(p.gout[(long long)b * p.out_bs + (long long)rem * p.Fs + bf]);
             }
             As[ml][tid % 64] = av;
             Bs[ml][tid % 64] = bv;

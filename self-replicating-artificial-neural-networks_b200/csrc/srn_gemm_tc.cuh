@@ -13,9 +13,11 @@
 // k-block and commits to the ring's mbarriers; the fp32 accumulator lives in TMEM and is read back with
 // tcgen05.ld by the four warps (warp w owns TMEM lanes 32w..32w+31) for the same epilogues as the SIMT kernels.
 //
-// Eligibility (checked on the host): channel counts that keep every 16-byte chunk inside one pixel and
-// 16-byte aligned (C % 8 == 0), or single-row tensors (Dense on (B, 1, F)), whose padded batch stride makes
-// the rows aligned and whose pad is kept at zero.
+// Every activation tensor has its channel stride padded to 8 with zero pad (srn_common.cuh), so a 16-byte
+// chunk is always aligned and inside one pixel; the k index of a pass runs over the padded (pixel, channel)
+// space and weight rows of pad channels are zero-filled.  Layers reading a model input (one channel, no pad)
+// use the SCALAR_A variant: the im2col operand is gathered element by element and stored to shared memory
+// with ordinary 16-byte stores; everything else is identical.
 #pragma once
 #include "srn_common.cuh"
 
@@ -24,7 +26,7 @@ namespace srn {
 constexpr int TC_BM = 128;            // UMMA M
 constexpr int TC_BK = 64;             // k elements per stage (4 MMAs of K = 16)
 constexpr int TC_STAGES = 4;
-constexpr int TC_PF = 2;              // prefetch distance in k-blocks
+constexpr int TC_PF = 3;              // prefetch distance in k-blocks
 constexpr int TC_THREADS = 128;
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;
 constexpr int TC_WGRAD_ROWS = 4096;   // reduction rows per wgrad CTA (64 k-blocks)
@@ -35,9 +37,9 @@ __host__ __device__ inline int tc_smem_bytes(int BN) { return TC_STAGES * (TC_A_
 __host__ __device__ inline int tc_tmem_cols(int BN) { return BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256)); }
 __host__ __device__ inline int round_up8(int v) { return (v + 7) & ~7; }
 
-// reduction length of each pass as the kernel sees it (dense rows are read through their zero pad)
-__host__ __device__ inline int tc_k_fwd(const Prob& p) { return (p.kh * p.kw == 1) ? round_up8(p.C) : p.kh * p.kw * p.C; }
-__host__ __device__ inline int tc_k_dgrad(const Prob& p) { return (p.kh * p.kw == 1) ? round_up8(p.F) : p.kh * p.kw * p.F; }
+// reduction length of each pass as the kernel sees it: over padded channels
+__host__ __device__ inline int tc_k_fwd(const Prob& p) { return p.kh * p.kw * p.Cs; }
+__host__ __device__ inline int tc_k_dgrad(const Prob& p) { return p.kh * p.kw * p.Fs; }
 
 __host__ __device__ inline int tc_tiles_fwd(const Prob& p, int nb, int BN) {
     return ((nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM) * ((p.F + BN - 1) / BN);
@@ -55,6 +57,10 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
     const int sz = valid ? 16 : 0;                      // src-size 0: the 16 bytes are zero-filled
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async16_ca(uint32_t dst, const void* src, bool valid) {   // keeps the line in L1 (im2col reuse)
+    const int sz = valid ? 16 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(src), "r"(sz) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 template <int N>
@@ -125,18 +131,20 @@ __device__ __forceinline__ uint32_t core_off(int mn_group, int k_group, int r8) 
 }
 
 // ------------------------------------------------------------------ the kernel
-template <int MODE>
+template <int MODE, bool SCALAR_A>
 static __global__ void __launch_bounds__(TC_THREADS)
-k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, int BN) {
+k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, int BN, Inputs I) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int l8 = lane & 7, lq = lane >> 3;              // row inside a core matrix, chunk inside a quad
-    const uint32_t sbase = (smem_u32(smem_raw) + 127u) & ~127u;
+    const uint32_t sraw = smem_u32(smem_raw);
+    const uint32_t sbase = (sraw + 127u) & ~127u;
+    unsigned char* sgen = smem_raw + (sbase - sraw);      // generic pointer to the same place as sbase
     const uint32_t B_BYTES = (uint32_t)BN * TC_BK * 2;
     const uint32_t sA = sbase, sB = sbase + TC_STAGES * TC_A_BYTES;
     const uint32_t sBar = sB + TC_STAGES * B_BYTES;      // TC_STAGES "empty" barriers + 1 "done" barrier
     const uint32_t sSlot = sBar + (TC_STAGES + 1) * 8;
-    volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (sSlot - smem_u32(smem_raw)));
+    volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(sgen + (sSlot - sbase));
 
     const int pi = find_prob(prefix, nprob, blockIdx.x);
     const Prob p = probs[pi];
@@ -154,21 +162,26 @@ k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int np
     const uint32_t tmem = *slot_ptr;
 
     // ---- problem geometry
+    int in_bs;
+    const __half* in = resolve_in(p, I, in_bs);
     const int HoWo = p.Ho * p.Wo, HW = p.H * p.W;
-    const bool dense = (p.kh * p.kw == 1);
+    const int Cs = p.Cs, Fs = p.Fs;
+    const int KK = p.kh * p.kw;
+    const int Kf = SCALAR_A ? KK : KK * Cs;               // forward reduction length (padded channels)
+    const int Kd = KK * Fs;
     int m0 = 0, n0 = 0, Mrows = 0, Ncols = 0, nk = 0, r0 = 0, r1 = 0;
     if (MODE == TC_FWD) {
         Mrows = nb * HoWo; Ncols = p.F;
         const int tn = (Ncols + BN - 1) / BN;
         m0 = (tile / tn) * TC_BM; n0 = (tile % tn) * BN;
-        nk = (tc_k_fwd(p) + TC_BK - 1) / TC_BK;
+        nk = (Kf + TC_BK - 1) / TC_BK;
     } else if (MODE == TC_DGRAD) {
         Mrows = nb * HW; Ncols = p.C;
         const int tn = (Ncols + BN - 1) / BN;
         m0 = (tile / tn) * TC_BM; n0 = (tile % tn) * BN;
-        nk = (tc_k_dgrad(p) + TC_BK - 1) / TC_BK;
+        nk = (Kd + TC_BK - 1) / TC_BK;
     } else {
-        Mrows = tc_k_fwd(p); Ncols = p.F;                // output rows are kk = (i, j, c)
+        Mrows = Kf; Ncols = p.F;                          // output rows are kk = (i, j, padded c)
         const int tm = (Mrows + TC_BM - 1) / TC_BM, tn = (Ncols + BN - 1) / BN;
         const int split = tile / (tm * tn);
         tile -= split * tm * tn;
@@ -176,15 +189,12 @@ k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int np
         r0 = split * TC_WGRAD_ROWS; r1 = min(nb * HoWo, r0 + TC_WGRAD_ROWS);
         nk = (r1 - r0 + TC_BK - 1) / TC_BK;
     }
-    int n_umma = min(BN, ((Ncols - n0 + 15) / 16) * 16);
-    const int kwC = p.kw * p.C, WC = p.W * p.C;
-    const int Kf = tc_k_fwd(p), Kd = tc_k_dgrad(p);
-    const int Fpad = dense ? round_up8(p.F) : p.F;       // readable width of a dOut row
+    const int n_umma = min(BN, ((Ncols - n0 + 15) / 16) * 16);
 
     // ---- per-thread loader state that does not change over the k loop
-    const __half* a_row[4];          // FWD: base of im2col row; null = out of range
+    const __half* a_row[4];          // FWD: base of the im2col row; null = out of range
     int a_b[4], a_h[4], a_w[4];      // DGRAD: input position of the row
-    long long w_koff[4]; bool w_kok[4];   // WGRAD: offset of this thread's four kk chunks inside an input pixel window
+    long long w_koff[4]; bool w_kok[4];   // WGRAD (vector): offset of this thread's four kk chunks inside the window
     if (MODE == TC_FWD) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -193,7 +203,7 @@ k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int np
             if (m < Mrows) {
                 const int b = m / HoWo, rem = m - b * HoWo;
                 const int ho = rem / p.Wo, wo = rem - ho * p.Wo;
-                a_row[j] = p.in + (long long)b * p.in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * p.C;
+                a_row[j] = in + (long long)b * in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * Cs;
             }
         }
     } else if (MODE == TC_DGRAD) {
@@ -207,13 +217,14 @@ k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int np
                 a_h[j] = rem / p.W; a_w[j] = rem - a_h[j] * p.W;
             }
         }
-    } else {
+    } else if (!SCALAR_A) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             const int kk = m0 + (q * 4 + lq) * 8;
             w_kok[q] = kk < Kf;
-            const int i = dense ? 0 : kk / kwC;
-            w_koff[q] = (long long)i * WC + (kk - i * kwC);
+            const int ij = kk / Cs, cp = kk - ij * Cs;
+            const int i = ij / p.kw, j = ij - i * p.kw;
+            w_koff[q] = ((long long)i * p.W + j) * Cs + cp;
         }
     }
 
@@ -227,19 +238,32 @@ k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int np
                 const int q = warp * 8 + i, blk = q >> 1, ch = (q & 1) * 4 + lq;
                 const int k = kb * TC_BK + ch * 8;
                 const __half* row = a_row[i >> 1];
-                bool ok = row != nullptr && k < Kf;
-                long long koff = k;
-                if (!dense && ok) { const int ii = k / kwC; koff = (long long)ii * WC + (k - ii * kwC); }
-                cp_async16(aS + core_off(blk, ch, l8), ok ? (const void*)(row + koff) : (const void*)p.in, ok);
+                if (SCALAR_A) {
+                    Half8 v;
+                    int ki = k / p.kw, kj = k - ki * p.kw;
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        v.v[e] = (row != nullptr && k + e < Kf) ? row[ki * p.W + kj] : __float2half_rn(0.f);
+                        if (++kj == p.kw) { kj = 0; ++ki; }
+                    }
+                    *reinterpret_cast<Half8*>(sgen + (aS - sbase) + core_off(blk, ch, l8)) = v;
+                } else {
+                    const bool ok = row != nullptr && k < Kf;
+                    const int ij = k / Cs, cp = k - ij * Cs;
+                    const int ki = ij / p.kw, kj = ij - ki * p.kw;
+                    cp_async16_ca(aS + core_off(blk, ch, l8),
+                                  ok ? (const void*)(row + ((long long)ki * p.W + kj) * Cs + cp) : (const void*)p.w, ok);
+                }
             }
-            // B, MN-major: 8 k blocks x BN/32 quads of n chunks; W rows are [k][ldw]
+            // B, MN-major: 8 k blocks x BN/32 quads of n chunks; W rows are [(ij, c)][ldw], pad channels have no row
             const int Q = BN >> 5;
             for (int i = 0; i < items_b; ++i) {
                 const int q = warp * items_b + i, blk = q / Q, nch = (q - blk * Q) * 4 + lq;
                 const int k = kb * TC_BK + blk * 8 + l8, n = n0 + nch * 8;
-                const int kreal = dense ? p.C : Kf;
-                const bool ok = k < kreal && n < p.ldw;
-                cp_async16(bS + core_off(nch, blk, l8), ok ? (const void*)(p.w + (long long)k * p.ldw + n) : (const void*)p.w, ok);
+                long long wrow = k;
+                bool ok = k < Kf && n < p.ldw;
+                if (!SCALAR_A) { const int ij = k / Cs, cp = k - ij * Cs; ok = ok && cp < p.C; wrow = (long long)ij * p.C + cp; }
+                cp_async16(bS + core_off(nch, blk, l8), ok ? (const void*)(p.w + wrow * p.ldw + n) : (const void*)p.w, ok);
             }
         } else if (MODE == TC_DGRAD) {
 #pragma unroll
@@ -250,24 +274,24 @@ k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int np
                 bool ok = a_b[j] >= 0 && k < Kd;
                 const __half* src = p.gout;
                 if (ok) {
-                    const int ij = dense ? 0 : k / p.F, f = k - ij * p.F;
+                    const int ij = k / Fs, f = k - ij * Fs;
                     const int ki = ij / p.kw, kj = ij - ki * p.kw;
                     const int hh = a_h[j] - ki, ww = a_w[j] - kj;
                     ok = hh >= 0 && ww >= 0;
                     if (ok) {
                         const int ho = hh / p.sh, wo = ww / p.sw;
                         ok = ho * p.sh == hh && wo * p.sw == ww && ho < p.Ho && wo < p.Wo;
-                        if (ok) src = p.gout + (long long)a_b[j] * p.out_bs + ((long long)ho * p.Wo + wo) * p.F + f;
+                        if (ok) src = p.gout + (long long)a_b[j] * p.out_bs + ((long long)ho * p.Wo + wo) * Fs + f;
                     }
                 }
-                cp_async16(aS + core_off(blk, ch, l8), src, ok);
+                cp_async16_ca(aS + core_off(blk, ch, l8), src, ok);
             }
             // B, K-major: rows n = input channel c, k = (ij, f) contiguous in f
             for (int i = 0; i < items_b; ++i) {
                 const int q = warp * items_b + i, blk = q >> 1, ch = (q & 1) * 4 + lq;
                 const int c = n0 + blk * 8 + l8, k = kb * TC_BK + ch * 8;
                 const bool ok = c < p.C && k < Kd;
-                const int ij = dense ? 0 : k / p.F, f = k - ij * p.F;
+                const int ij = k / Fs, f = k - ij * Fs;
                 cp_async16(bS + core_off(blk, ch, l8),
                            ok ? (const void*)(p.w + ((long long)ij * p.C + c) * p.ldw + f) : (const void*)p.w, ok);
             }
@@ -281,33 +305,45 @@ k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int np
                 if (r < r1) {
                     const int b = r / HoWo, rem = r - b * HoWo;
                     const int ho = rem / p.Wo, wo = rem - ho * p.Wo;
-                    in_row[j] = p.in + (long long)b * p.in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * p.C;
-                    go_row[j] = p.gout + (long long)b * p.out_bs + (long long)rem * p.F;
+                    in_row[j] = in + (long long)b * in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * Cs;
+                    go_row[j] = p.gout + (long long)b * p.out_bs + (long long)rem * Fs;
                 }
             }
             // A, MN-major: 8 row blocks x 4 quads of kk chunks
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int q = warp * 8 + i, blk = q >> 2, qd = q & 3, cc = qd * 4 + lq;
-                const __half* row = in_row[blk - warp * 2];
-                const bool ok = row != nullptr && w_kok[qd];
-                cp_async16(aS + core_off(cc, blk, l8), ok ? (const void*)(row + w_koff[qd]) : (const void*)p.in, ok);
+                const __half* row = (i < 4) ? in_row[0] : in_row[1];
+                if (SCALAR_A) {
+                    Half8 v;
+                    const int kk = m0 + cc * 8;
+                    int ki = kk / p.kw, kj = kk - ki * p.kw;
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        v.v[e] = (row != nullptr && kk + e < Kf) ? row[ki * p.W + kj] : __float2half_rn(0.f);
+                        if (++kj == p.kw) { kj = 0; ++ki; }
+                    }
+                    *reinterpret_cast<Half8*>(sgen + (aS - sbase) + core_off(cc, blk, l8)) = v;
+                } else {
+                    const bool ok = row != nullptr && w_kok[qd];
+                    cp_async16_ca(aS + core_off(cc, blk, l8), ok ? (const void*)(row + w_koff[qd]) : (const void*)p.w, ok);
+                }
             }
             // B, MN-major: 8 row blocks x BN/32 quads of f chunks
             const int Q = BN >> 5;
             for (int i = 0; i < items_b; ++i) {
                 const int q = warp * items_b + i, blk = q / Q, nch = (q - blk * Q) * 4 + lq;
-                const __half* row = go_row[blk - warp * 2];
+                const __half* row = (blk - warp * 2) ? go_row[1] : go_row[0];
                 const int f = n0 + nch * 8;
-                const bool ok = row != nullptr && f < Fpad;
-                cp_async16(bS + core_off(nch, blk, l8), ok ? (const void*)(row + f) : (const void*)p.gout, ok);
+                const bool ok = row != nullptr && f < Fs;
+                cp_async16(bS + core_off(nch, blk, l8), ok ? (const void*)(row + f) : (const void*)p.w, ok);
             }
         }
     };
 
     const uint32_t idesc = umma_idesc(MODE == TC_WGRAD ? 1 : 0, MODE == TC_DGRAD ? 0 : 1, n_umma);
 
-    // ---- main loop: fill two k-blocks ahead, one thread issues the MMAs
+    // ---- main loop: fill TC_PF k-blocks ahead, one thread issues the MMAs
     for (int s = 0; s < TC_PF; ++s) {
         if (s < nk) load_stage(s, s);
         cp_async_commit();
@@ -337,14 +373,15 @@ k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int np
     mbar_wait(sBar + TC_STAGES * 8, 0);
     tc_fence_after();
 
-    // ---- epilogue: this thread owns accumulator row (warp * 32 + lane)
+    // ---- epilogue: this thread owns accumulator row (warp * 32 + lane); whole 8-channel chunks are written,
+    //      pad channels as zero
     const int mrow = m0 + warp * 32 + lane;
     const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
     if (MODE == TC_FWD) {
         __half* orow = nullptr;
         if (mrow < Mrows) {
             const int b = mrow / HoWo, rem = mrow - b * HoWo;
-            orow = p.out + (long long)b * p.out_bs + (long long)rem * p.F;
+            orow = p.out + (long long)b * p.out_bs + (long long)rem * Fs;
         }
         for (int cb = 0; cb < n_umma; cb += 16) {
             float v[16];
@@ -354,25 +391,21 @@ k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int np
             for (int h8 = 0; h8 < 2; ++h8) {
                 const int n = n0 + cb + h8 * 8;
                 if (n >= Ncols) break;
-                __align__(16) __half o[8];
+                Half8 o;
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     float z = 0.f;
                     if (n + j < Ncols) z = act_forward(rh(rh(v[h8 * 8 + j]) + __half2float(p.bias[n + j])), p.act);
-                    o[j] = __float2half_rn(z);
+                    o.v[j] = __float2half_rn(z);
                 }
-                if (n + 8 <= Ncols && ((reinterpret_cast<uintptr_t>(orow + n) & 15) == 0)) {
-                    *reinterpret_cast<uint4*>(orow + n) = *reinterpret_cast<const uint4*>(o);
-                } else {
-                    for (int j = 0; j < 8 && n + j < Ncols; ++j) orow[n + j] = o[j];
-                }
+                st8(orow + n, o);
             }
         }
     } else if (MODE == TC_DGRAD) {
         __half* drow = nullptr;
         if (mrow < Mrows) {
             const int b = mrow / HW, rem = mrow - b * HW;
-            drow = p.din + (long long)b * p.in_bs + (long long)rem * p.C;
+            drow = p.din + (long long)b * p.in_bs + (long long)rem * Cs;
         }
         for (int cb = 0; cb < n_umma; cb += 16) {
             float v[16];
@@ -382,27 +415,25 @@ k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int np
             for (int h8 = 0; h8 < 2; ++h8) {
                 const int c = n0 + cb + h8 * 8;
                 if (c >= Ncols) break;
-                __align__(16) __half o[8];
-                const bool vec = c + 8 <= Ncols && ((reinterpret_cast<uintptr_t>(drow + c) & 15) == 0);
-                if (p.din_acc) {
+                Half8 o;
+                if (p.din_acc) o = ld8(drow + c);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        o[j] = (c + j < Ncols) ? __float2half_rn(rh(v[h8 * 8 + j]) + __half2float(drow[c + j])) : __float2half_rn(0.f);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) o[j] = __float2half_rn(v[h8 * 8 + j]);
+                for (int j = 0; j < 8; ++j) {
+                    float x = (c + j < Ncols) ? v[h8 * 8 + j] : 0.f;
+                    if (p.din_acc) x = rh(x) + __half2float(o.v[j]);
+                    o.v[j] = __float2half_rn(x);
                 }
-                if (vec) {
-                    *reinterpret_cast<uint4*>(drow + c) = *reinterpret_cast<const uint4*>(o);
-                } else {
-                    for (int j = 0; j < 8 && c + j < Ncols; ++j) drow[c + j] = o[j];
-                }
+                st8(drow + c, o);
             }
         }
     } else {
-        const int kreal = dense ? p.C : Kf;
+        // accumulator row = kk = (ij, padded c): rows of pad channels have no weight row
+        float* grow = nullptr;
+        if (mrow < Kf) {
+            if (SCALAR_A) grow = p.gw + (long long)mrow * p.ldw;
+            else { const int ij = mrow / Cs, cp = mrow - ij * Cs; if (cp < p.C) grow = p.gw + ((long long)ij * p.C + cp) * p.ldw; }
+        }
         const bool single = (nb * HoWo) <= TC_WGRAD_ROWS;     // one split: plain stores, else fp32 atomics
-        float* grow = (mrow < kreal) ? p.gw + (long long)mrow * p.ldw : nullptr;
         for (int cb = 0; cb < n_umma; cb += 16) {
             float v[16];
             tmem_ld16(trow + cb, v);

@@ -1,111 +1,179 @@
 // HBM-bound kernels of the SeRANN engine: activation backward + bias gradient, BatchNormalizationF16,
-// max pooling, concat, fused losses, multi-tensor Adam, batch gather, readout, initialisation.
+// max pooling, copy (concatenate / reshape), fused losses, multi-tensor Adam, batch gather, readout, init.
 // All are population-grouped (see Prob in srn_common.cuh) except Adam/readout, which run flat.
+// Tensors are [row][Cs] with Cs a multiple of 8 (srn_common.cuh), so the elementwise kernels move 16-byte
+// chunks of 8 channels; the scalar branch (Cs = 1) only serves layers applied directly to a model input.
 #pragma once
 #include "srn_common.cuh"
 
 namespace srn {
 
-constexpr int COL_THREADS = 256;      // 32 channel lanes x 8 row lanes
-constexpr int COL_ROWS = 1024;        // rows per CTA of the column-reduction kernels
+constexpr int COL_THREADS = 256;
+constexpr int COL_ITERS = 16;         // rows per row lane and CTA in the column-reduction kernels
 
-__host__ __device__ inline int col_chunks(long long rows) { return (int)((rows + COL_ROWS - 1) / COL_ROWS); }
-
-// rows x C view of a per-sample-strided tensor: row r -> sample r / rps, inner row r % rps
-__device__ __forceinline__ long long row_off(long long r, int rps, int bs, int C) {
-    long long b = r / rps;
-    return b * bs + (r - b * rps) * (long long)C;
+// Thread layout of the column reductions: channel chunk cq = tid % nq, row lane rl = tid / nq.
+struct ColGeom { int cw, nq, RL, rows_per_cta; };
+__host__ __device__ inline ColGeom col_geom(int Cs) {
+    ColGeom g;
+    g.cw = (Cs % 8 == 0) ? 8 : 1;
+    g.nq = Cs / g.cw;
+    g.RL = g.nq <= COL_THREADS ? COL_THREADS / g.nq : 1;
+    g.rows_per_cta = g.RL * COL_ITERS;
+    return g;
+}
+__host__ __device__ inline int col_chunks(long long rows, int Cs) {
+    const int rpc = col_geom(Cs).rows_per_cta;
+    return (int)((rows + rpc - 1) / rpc);
 }
 
-// block-level sum over the 8 row lanes; result valid in row lane 0
-__device__ __forceinline__ float rowlane_sum(float v, float (*sm)[33], int cl, int rl) {
-    sm[rl][cl] = v;
-    __syncthreads();
+// offset of row r (over all samples) of an input tensor; model inputs may be strided or broadcast per sample
+__device__ __forceinline__ long long in_row_off(long long r, int rps, int bs, int Cs) {
+    long long b = r / rps;
+    return b * bs + (r - b * rps) * (long long)Cs;
+}
+
+// sums over the row lanes of a CTA: sm holds one value per (thread, j); thread `ch` (< nq * cw) gets channel ch
+__device__ __forceinline__ float col_block_sum(const float* sm, const ColGeom& g, int ch) {
+    const int cq = ch / g.cw, j = ch - cq * g.cw;
     float s = 0.f;
-    if (rl == 0) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) s += sm[i][cl];
-    }
-    __syncthreads();
+    for (int rl = 0; rl < g.RL; ++rl) s += sm[(rl * g.nq + cq) * 8 + j];
     return s;
 }
 
 // ------------------------------------------------------------------ activation backward + bias gradient
-// gout <- fp16(gout * act'(out)) in place; gb[f] += column sums of the result.
+// gout <- fp16(gout * act'(out)) in place (TF's ReluGrad / SigmoidGrad); gb[f] += column sums of the result.
 static __global__ void __launch_bounds__(COL_THREADS)
 k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb) {
-    __shared__ float sm[8][33];
+    __shared__ float sm[COL_THREADS * 8];
     const int pi = find_prob(prefix, nprob, blockIdx.x);
     const Prob p = probs[pi];
     const int chunk = blockIdx.x - prefix[pi];
-    const int rps = p.Ho * p.Wo, F = p.F;
-    const long long rows = (long long)nb * rps;
-    const long long r0 = (long long)chunk * COL_ROWS, r1 = min(rows, r0 + COL_ROWS);
-    const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
-    for (int f0 = 0; f0 < F; f0 += 32) {
-        const int f = f0 + cl;
-        float s = 0.f;
-        if (f < F) {
-            for (long long r = r0 + rl; r < r1; r += 8) {
-                long long o = row_off(r, rps, p.out_bs, F) + f;
-                float g = __half2float(p.gout[o]);
-                if (p.act == 1) {
-                    g = __half2float(p.out[o]) > 0.f ? g : 0.f;
-                    p.gout[o] = __float2half_rn(g);
-                } else if (p.act == 2) {
-                    float y = __half2float(p.out[o]);
-                    g = rh(rh(g * y) * rh(1.f - y));
-                    p.gout[o] = __float2half_rn(g);
+    const int F = p.F, Fs = p.Fs;
+    const ColGeom g = col_geom(Fs);
+    const long long rows = (long long)nb * p.Ho * p.Wo;
+    const long long r0 = (long long)chunk * g.rows_per_cta, r1 = min(rows, r0 + g.rows_per_cta);
+    const int tid = threadIdx.x;
+    for (int cq0 = 0; cq0 < g.nq; cq0 += COL_THREADS) {
+        const int cq = g.nq <= COL_THREADS ? tid % g.nq : cq0 + tid;
+        const int rl = g.nq <= COL_THREADS ? tid / g.nq : 0;
+        const bool active = rl < g.RL && cq < g.nq;
+        float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (active) {
+            for (long long r = r0 + rl; r < r1; r += g.RL) {
+                const long long o = r * Fs + (long long)cq * g.cw;
+                if (g.cw == 8) {
+                    Half8 gv = ld8(p.gout + o);
+                    if (p.act == 1) {
+                        const Half8 y = ld8(p.out + o);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) if (!(__half2float(y.v[j]) > 0.f)) gv.v[j] = __float2half_rn(0.f);
+                        st8(p.gout + o, gv);
+                    } else if (p.act == 2) {
+                        const Half8 y = ld8(p.out + o);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float yy = __half2float(y.v[j]);
+                            gv.v[j] = __float2half_rn(rh(__half2float(gv.v[j]) * yy) * rh(1.f - yy));
+                        }
+                        st8(p.gout + o, gv);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) s[j] += __half2float(gv.v[j]);
+                } else {
+                    float gg = __half2float(p.gout[o]);
+                    if (p.act == 1) { gg = __half2float(p.out[o]) > 0.f ? gg : 0.f; p.gout[o] = __float2half_rn(gg); }
+                    else if (p.act == 2) { const float yy = __half2float(p.out[o]); gg = rh(rh(gg * yy) * rh(1.f - yy)); p.gout[o] = __float2half_rn(gg); }
+                    s[0] += gg;
                 }
-                s += g;
             }
         }
-        s = rowlane_sum(s, sm, cl, rl);
-        if (rl == 0 && f < F && s != 0.f) atomicAdd(&p.gb[f], s);
+        if (g.RL == 1) {
+            if (active)
+                for (int j = 0; j < g.cw; ++j) { const int f = cq * g.cw + j; if (f < F && s[j] != 0.f) atomicAdd(&p.gb[f], s[j]); }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sm[tid * 8 + j] = active ? s[j] : 0.f;
+            __syncthreads();
+            for (int ch = tid; ch < g.nq * g.cw; ch += COL_THREADS) {
+                const float t = col_block_sum(sm, g, ch);
+                if (ch < F && t != 0.f) atomicAdd(&p.gb[ch], t);
+            }
+            __syncthreads();
+        }
     }
 }
 
 // ------------------------------------------------------------------ BatchNormalizationF16
-// save layout per problem: [0][C] mean16, [1][C] inv_raw (rsqrt(var16 + eps), fp16-valued),
-// [2][C] inv (times gamma), [3][C] shift; then partial sums [chunks][C][2].
+// save layout per problem: [0][Cs] mean16, [1][Cs] inv_raw (rsqrt(var16 + eps), fp16-valued), [2][Cs] inv
+// (times gamma), [3][Cs] shift; then partial sums [chunks][Cs][2].
 constexpr float BN_EPS16 = 0.0010004043579101562f;       // fp16(1e-3)
 constexpr float BN_DECAY16 = 0.01000213623046875f;        // fp16(1 - 0.99)
 constexpr float BN_ONE_EPS16 = 1.0009765625f;             // fp16(1 + 1e-3)
 
+// forward: shifted sums (x - x0), (x - x0)^2 around the first row; backward: sum dy, sum dy * (x - mean16)
 static __global__ void __launch_bounds__(COL_THREADS)
 k_bn_partial(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, Inputs I, int bwd) {
-    __shared__ float sm[8][33];
+    __shared__ float sm1[COL_THREADS * 8];
+    __shared__ float sm2[COL_THREADS * 8];
     const int pi = find_prob(prefix, nprob, blockIdx.x);
     const Prob p = probs[pi];
     const int chunk = blockIdx.x - prefix[pi];
-    const int rps = p.H * p.W, C = p.C;
+    const int rps = p.H * p.W, Cs = p.Cs;
+    const ColGeom g = col_geom(Cs);
     const long long rows = (long long)nb * rps;
-    const long long r0 = (long long)chunk * COL_ROWS, r1 = min(rows, r0 + COL_ROWS);
+    const long long r0 = (long long)chunk * g.rows_per_cta, r1 = min(rows, r0 + g.rows_per_cta);
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
-    float* part = p.save + 4 * C + (long long)chunk * C * 2;
-    const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
-    for (int c0 = 0; c0 < C; c0 += 32) {
-        const int c = c0 + cl;
-        float s1 = 0.f, s2 = 0.f;
-        if (c < C) {
-            // forward: shifted sums around the first row's value; backward: sum dy, sum dy * (x - mean16)
-            const float pivot = bwd ? p.save[c] : __half2float(in[c]);
-            for (long long r = r0 + rl; r < r1; r += 8) {
-                float x = __half2float(in[row_off(r, rps, in_bs, C) + c]) - pivot;
-                if (bwd) {
-                    float dy = __half2float(p.gout[row_off(r, rps, p.out_bs, C) + c]);
-                    s1 += dy;
-                    s2 += dy * x;
+    float* part = p.save + 4 * Cs + (long long)chunk * Cs * 2;
+    const int tid = threadIdx.x;
+    for (int cq0 = 0; cq0 < g.nq; cq0 += COL_THREADS) {
+        const int cq = g.nq <= COL_THREADS ? tid % g.nq : cq0 + tid;
+        const int rl = g.nq <= COL_THREADS ? tid / g.nq : 0;
+        const bool active = rl < g.RL && cq < g.nq;
+        float s1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, s2[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (active) {
+            float pivot[8];
+            for (int j = 0; j < g.cw; ++j) pivot[j] = bwd ? p.save[cq * g.cw + j] : __half2float(in[cq * g.cw + j]);
+            for (long long r = r0 + rl; r < r1; r += g.RL) {
+                const long long io = in_row_off(r, rps, in_bs, Cs) + (long long)cq * g.cw;
+                if (g.cw == 8) {
+                    const Half8 x = ld8(in + io);
+                    if (bwd) {
+                        const Half8 dy = ld8(p.gout + r * Cs + (long long)cq * 8);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float d = __half2float(dy.v[j]);
+                            s1[j] += d;
+                            s2[j] += d * (__half2float(x.v[j]) - pivot[j]);
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float xv = __half2float(x.v[j]) - pivot[j];
+                            s1[j] += xv;
+                            s2[j] += xv * xv;
+                        }
+                    }
                 } else {
-                    s1 += x;
-                    s2 += x * x;
+                    const float xv = __half2float(in[io]) - pivot[0];
+                    if (bwd) { const float d = __half2float(p.gout[r * Cs + cq]); s1[0] += d; s2[0] += d * xv; }
+                    else { s1[0] += xv; s2[0] += xv * xv; }
                 }
             }
         }
-        s1 = rowlane_sum(s1, sm, cl, rl);
-        s2 = rowlane_sum(s2, sm, cl, rl);
-        if (rl == 0 && c < C) { part[c * 2] = s1; part[c * 2 + 1] = s2; }
+        if (g.RL == 1) {
+            if (active)
+                for (int j = 0; j < g.cw; ++j) { part[(cq * g.cw + j) * 2] = s1[j]; part[(cq * g.cw + j) * 2 + 1] = s2[j]; }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { sm1[tid * 8 + j] = active ? s1[j] : 0.f; sm2[tid * 8 + j] = active ? s2[j] : 0.f; }
+            __syncthreads();
+            for (int ch = tid; ch < g.nq * g.cw; ch += COL_THREADS) {
+                part[ch * 2] = col_block_sum(sm1, g, ch);
+                part[ch * 2 + 1] = col_block_sum(sm2, g, ch);
+            }
+            __syncthreads();
+        }
     }
 }
 
@@ -120,15 +188,19 @@ __device__ __forceinline__ void bn_scale_shift(float mean16, float var16, float 
 static __global__ void __launch_bounds__(128)
 k_bn_finalize_fwd(const Prob* __restrict__ probs, int nb, Inputs I) {
     const Prob p = probs[blockIdx.x];
-    const int C = p.C;
+    const int C = p.C, Cs = p.Cs;
     const long long rows = (long long)nb * p.H * p.W;
-    const int chunks = col_chunks(rows);
+    const int chunks = col_chunks(rows, Cs);
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
-    const float* part = p.save + 4 * C;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float* part = p.save + 4 * Cs;
+    for (int c = threadIdx.x; c < Cs; c += blockDim.x) {
+        if (c >= C) {           // pad channels: identity scale of zero so that they stay exactly zero
+            p.save[c] = 0.f; p.save[Cs + c] = 0.f; p.save[2 * Cs + c] = 0.f; p.save[3 * Cs + c] = 0.f;
+            continue;
+        }
         double s1 = 0.0, s2 = 0.0;
-        for (int k = 0; k < chunks; ++k) { s1 += part[((long long)k * C + c) * 2]; s2 += part[((long long)k * C + c) * 2 + 1]; }
+        for (int k = 0; k < chunks; ++k) { s1 += part[((long long)k * Cs + c) * 2]; s2 += part[((long long)k * Cs + c) * 2 + 1]; }
         const double n = (double)rows;
         const double dm = s1 / n;
         const float mean32 = (float)((double)__half2float(in[c]) + dm);
@@ -136,7 +208,7 @@ k_bn_finalize_fwd(const Prob* __restrict__ probs, int nb, Inputs I) {
         const float mean16 = rh(mean32), var16 = rh(var32);
         float inv_raw, inv, shift;
         bn_scale_shift(mean16, var16, __half2float(p.w[c]), __half2float(p.bias[c]), inv_raw, inv, shift);
-        p.save[c] = mean16; p.save[C + c] = inv_raw; p.save[2 * C + c] = inv; p.save[3 * C + c] = shift;
+        p.save[c] = mean16; p.save[Cs + c] = inv_raw; p.save[2 * Cs + c] = inv; p.save[3 * Cs + c] = shift;
         // moving statistics: variance * n16 / (n16 - (1 + eps)) with n cast to fp16 (inf/inf = NaN above 65504)
         const float n16 = rh((float)rows);
         const float bessel = rh(n16 / rh(n16 - BN_ONE_EPS16));
@@ -153,19 +225,24 @@ k_bn_finalize_fwd(const Prob* __restrict__ probs, int nb, Inputs I) {
 static __global__ void __launch_bounds__(128)
 k_bn_prepare_infer(const Prob* __restrict__ probs) {
     const Prob p = probs[blockIdx.x];
-    const int C = p.C;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-        float inv_raw, inv, shift;
-        bn_scale_shift(__half2float(p.mov[c]), __half2float(p.mov[C + c]), __half2float(p.w[c]),
-                       __half2float(p.bias[c]), inv_raw, inv, shift);
-        p.save[2 * C + c] = inv; p.save[3 * C + c] = shift;
+    const int C = p.C, Cs = p.Cs;
+    for (int c = threadIdx.x; c < Cs; c += blockDim.x) {
+        float inv_raw, inv = 0.f, shift = 0.f;
+        if (c < C)
+            bn_scale_shift(__half2float(p.mov[c]), __half2float(p.mov[C + c]), __half2float(p.w[c]),
+                           __half2float(p.bias[c]), inv_raw, inv, shift);
+        p.save[2 * Cs + c] = inv; p.save[3 * Cs + c] = shift;
     }
 }
 
 constexpr int EW_THREADS = 256;
-constexpr int EW_PER_THREAD = 8;
+constexpr int EW_PER_THREAD = 4;      // 16-byte chunks (or scalars) per thread
 constexpr int EW_PER_CTA = EW_THREADS * EW_PER_THREAD;
-__host__ __device__ inline int ew_blocks(long long elems) { return (int)((elems + EW_PER_CTA - 1) / EW_PER_CTA); }
+// work items of an elementwise pass over `rows` rows of channel stride Cs
+__host__ __device__ inline int ew_blocks(long long rows, int Cs) {
+    const long long units = rows * (Cs % 8 == 0 ? Cs / 8 : Cs);
+    return (int)((units + EW_PER_CTA - 1) / EW_PER_CTA);
+}
 
 // y = fp16(fp16(x * inv) + shift)
 static __global__ void __launch_bounds__(EW_THREADS)
@@ -173,39 +250,48 @@ k_bn_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, int n
     const int pi = find_prob(prefix, nprob, blockIdx.x);
     const Prob p = probs[pi];
     const int blk = blockIdx.x - prefix[pi];
-    const int C = p.C, per = p.H * p.W * C;
-    const long long total = (long long)nb * per;
+    const int Cs = p.Cs, rps = p.H * p.W;
+    const int cw = (Cs % 8 == 0) ? 8 : 1, nq = Cs / cw;
+    const long long total = (long long)nb * rps * nq;
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
-    const float* inv = p.save + 2 * C;
-    const float* shift = p.save + 3 * C;
-    long long e = (long long)blk * EW_PER_CTA + threadIdx.x;
+    const float* inv = p.save + 2 * Cs;
+    const float* shift = p.save + 3 * Cs;
+    long long q = (long long)blk * EW_PER_CTA + threadIdx.x;
 #pragma unroll
-    for (int i = 0; i < EW_PER_THREAD; ++i, e += EW_THREADS) {
-        if (e >= total) break;
-        long long b = e / per; int r = (int)(e - b * per); int c = r % C;
-        float x = __half2float(in[b * in_bs + r]);
-        p.out[b * p.out_bs + r] = __float2half_rn(rh(x * inv[c]) + shift[c]);
+    for (int i = 0; i < EW_PER_THREAD; ++i, q += EW_THREADS) {
+        if (q >= total) break;
+        const long long r = q / nq; const int c0 = (int)(q - r * nq) * cw;
+        const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = r * Cs + c0;
+        if (cw == 8) {
+            const Half8 x = ld8(in + io);
+            Half8 y;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) y.v[j] = __float2half_rn(rh(__half2float(x.v[j]) * inv[c0 + j]) + shift[c0 + j]);
+            st8(p.out + oo, y);
+        } else {
+            p.out[oo] = __float2half_rn(rh(__half2float(in[io]) * inv[c0]) + shift[c0]);
+        }
     }
 }
 
-// one CTA per problem: dgamma, dbeta into the fp32 gradient arena; coefficients for the dx pass
-// save[3][C] is reused: [3][c] <- inv * s1 / n ... kept simple: store s1/n and k2 = gamma*inv_raw^3*s2/n
+// one CTA per problem: dgamma, dbeta into the fp32 gradient arena; coefficients for the dx pass are left in
+// chunk 0's partial slots: [c][0] = mean(dy), [c][1] = gamma * inv_raw^3 * mean(dy * (x - mean16))
 static __global__ void __launch_bounds__(128)
 k_bn_finalize_bwd(const Prob* __restrict__ probs, int nb) {
     const Prob p = probs[blockIdx.x];
-    const int C = p.C;
+    const int C = p.C, Cs = p.Cs;
     const long long rows = (long long)nb * p.H * p.W;
-    const int chunks = col_chunks(rows);
-    float* part = p.save + 4 * C;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const int chunks = col_chunks(rows, Cs);
+    float* part = p.save + 4 * Cs;
+    for (int c = threadIdx.x; c < Cs; c += blockDim.x) {
+        if (c >= C) { part[c * 2] = 0.f; part[c * 2 + 1] = 0.f; continue; }
         double s1 = 0.0, s2 = 0.0;
-        for (int k = 0; k < chunks; ++k) { s1 += part[((long long)k * C + c) * 2]; s2 += part[((long long)k * C + c) * 2 + 1]; }
-        const float inv_raw = p.save[C + c];
+        for (int k = 0; k < chunks; ++k) { s1 += part[((long long)k * Cs + c) * 2]; s2 += part[((long long)k * Cs + c) * 2 + 1]; }
+        const float inv_raw = p.save[Cs + c];
         const float gamma = __half2float(p.w[c]);
         atomicAdd(&p.gb[c], (float)s1);                       // dbeta
         atomicAdd(&p.gw[c], (float)(s2 * inv_raw));           // dgamma
-        // coefficients overwrite chunk 0's slot of this channel (only this thread reads it); dx pass reads them
         part[c * 2] = (float)(s1 / (double)rows);
         part[c * 2 + 1] = (float)((double)gamma * inv_raw * inv_raw * inv_raw * s2 / (double)rows);
     }
@@ -218,51 +304,86 @@ k_bn_bwd_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
     const Prob p = probs[pi];
     if (p.din == nullptr) return;
     const int blk = blockIdx.x - prefix[pi];
-    const int C = p.C, per = p.H * p.W * C;
-    const long long total = (long long)nb * per;
+    const int Cs = p.Cs, rps = p.H * p.W;
+    const int cw = (Cs % 8 == 0) ? 8 : 1, nq = Cs / cw;
+    const long long total = (long long)nb * rps * nq;
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
     const float* mean16 = p.save;
-    const float* inv = p.save + 2 * C;
-    const float* coef = p.save + 4 * C;
-    long long e = (long long)blk * EW_PER_CTA + threadIdx.x;
+    const float* inv = p.save + 2 * Cs;
+    const float* coef = p.save + 4 * Cs;
+    long long q = (long long)blk * EW_PER_CTA + threadIdx.x;
 #pragma unroll
-    for (int i = 0; i < EW_PER_THREAD; ++i, e += EW_THREADS) {
-        if (e >= total) break;
-        long long b = e / per; int r = (int)(e - b * per); int c = r % C;
-        float x = __half2float(in[b * in_bs + r]) - mean16[c];
-        float dy = __half2float(p.gout[b * p.out_bs + r]);
-        float dx = inv[c] * (dy - coef[c * 2]) - x * coef[c * 2 + 1];
-        __half* d = p.din + b * p.in_bs + r;
-        if (p.din_acc) dx = rh(dx) + __half2float(*d);
-        *d = __float2half_rn(dx);
+    for (int i = 0; i < EW_PER_THREAD; ++i, q += EW_THREADS) {
+        if (q >= total) break;
+        const long long r = q / nq; const int c0 = (int)(q - r * nq) * cw;
+        const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = r * Cs + c0;
+        if (cw == 8) {
+            const Half8 x = ld8(in + io), dy = ld8(p.gout + oo);
+            Half8 d;
+            if (p.din_acc) d = ld8(p.din + io);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int c = c0 + j;
+                float dx = inv[c] * (__half2float(dy.v[j]) - coef[c * 2]) - (__half2float(x.v[j]) - mean16[c]) * coef[c * 2 + 1];
+                if (c >= p.C) dx = 0.f;
+                if (p.din_acc) dx = rh(dx) + __half2float(d.v[j]);
+                d.v[j] = __float2half_rn(dx);
+            }
+            st8(p.din + io, d);
+        } else {
+            float dx = inv[c0] * (__half2float(p.gout[oo]) - coef[c0 * 2]) - (__half2float(in[io]) - mean16[c0]) * coef[c0 * 2 + 1];
+            if (p.din_acc) dx = rh(dx) + __half2float(p.din[io]);
+            p.din[io] = __float2half_rn(dx);
+        }
     }
 }
 
-// ------------------------------------------------------------------ max pooling
+// ------------------------------------------------------------------ max pooling (C == F, Cs == Fs)
+__device__ __forceinline__ bool better_max(float v, float best) { return v > best || (v != v && best == best); }
+
 static __global__ void __launch_bounds__(EW_THREADS)
 k_maxpool_fwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, Inputs I) {
     const int pi = find_prob(prefix, nprob, blockIdx.x);
     const Prob p = probs[pi];
     const int blk = blockIdx.x - prefix[pi];
-    const int C = p.C, per = p.Ho * p.Wo * C;
-    const long long total = (long long)nb * per;
+    const int Cs = p.Cs, HoWo = p.Ho * p.Wo;
+    const int cw = (Cs % 8 == 0) ? 8 : 1, nq = Cs / cw;
+    const long long total = (long long)nb * HoWo * nq;
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
-    long long e = (long long)blk * EW_PER_CTA + threadIdx.x;
+    long long q = (long long)blk * EW_PER_CTA + threadIdx.x;
+#pragma unroll 1
+    for (int it = 0; it < EW_PER_THREAD; ++it, q += EW_THREADS) {
+        if (q >= total) break;
+        const long long pix = q / nq; const int c0 = (int)(q - pix * nq) * cw;
+        const long long b = pix / HoWo; const int rem = (int)(pix - b * HoWo);
+        const int ho = rem / p.Wo, wo = rem - ho * p.Wo;
+        const __half* base = in + b * in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * Cs + c0;
+        float best[8];
 #pragma unroll
-    for (int it = 0; it < EW_PER_THREAD; ++it, e += EW_THREADS) {
-        if (e >= total) break;
-        long long b = e / per; int r = (int)(e - b * per);
-        int c = r % C; int t = r / C; int wo = t % p.Wo, ho = t / p.Wo;
-        const __half* base = in + b * in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * C + c;
-        float best = -INFINITY;
+        for (int j = 0; j < 8; ++j) best[j] = -INFINITY;
         for (int i = 0; i < p.kh; ++i)
-            for (int j = 0; j < p.kw; ++j) {
-                float v = __half2float(base[((long long)i * p.W + j) * C]);
-                if (v > best || (v != v && best == best)) best = v;
+            for (int jj = 0; jj < p.kw; ++jj) {
+                const __half* s = base + ((long long)i * p.W + jj) * Cs;
+                if (cw == 8) {
+                    const Half8 x = ld8(s);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { const float v = __half2float(x.v[j]); if (better_max(v, best[j])) best[j] = v; }
+                } else {
+                    const float v = __half2float(*s);
+                    if (better_max(v, best[0])) best[0] = v;
+                }
             }
-        p.out[b * p.out_bs + r] = __float2half_rn(best);
+        __half* o = p.out + pix * Cs + c0;
+        if (cw == 8) {
+            Half8 y;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) y.v[j] = __float2half_rn(best[j]);
+            st8(o, y);
+        } else {
+            *o = __float2half_rn(best[0]);
+        }
     }
 }
 
@@ -273,73 +394,105 @@ k_maxpool_bwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
     const Prob p = probs[pi];
     if (p.din == nullptr) return;
     const int blk = blockIdx.x - prefix[pi];
-    const int C = p.C, per = p.H * p.W * C;
-    const long long total = (long long)nb * per;
+    const int Cs = p.Cs, HW = p.H * p.W, HoWo = p.Ho * p.Wo;
+    const int cw = (Cs % 8 == 0) ? 8 : 1, nq = Cs / cw;
+    const long long total = (long long)nb * HW * nq;
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
-    long long e = (long long)blk * EW_PER_CTA + threadIdx.x;
+    long long q = (long long)blk * EW_PER_CTA + threadIdx.x;
 #pragma unroll 1
-    for (int it = 0; it < EW_PER_THREAD; ++it, e += EW_THREADS) {
-        if (e >= total) break;
-        long long b = e / per; int r = (int)(e - b * per);
-        int c = r % C; int t = r / C; int w = t % p.W, h = t / p.W;
-        const __half* ib = in + b * in_bs + c;
-        const float xv = __half2float(ib[((long long)h * p.W + w) * C]);
-        float g = 0.f;
+    for (int it = 0; it < EW_PER_THREAD; ++it, q += EW_THREADS) {
+        if (q >= total) break;
+        const long long pix = q / nq; const int c0 = (int)(q - pix * nq) * cw;
+        const long long b = pix / HW; const int rem = (int)(pix - b * HW);
+        const int h = rem / p.W, w = rem - h * p.W;
+        const __half* ib = in + b * in_bs + c0;
+        float xv[8], g[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { xv[j] = 0.f; g[j] = 0.f; }
+        if (cw == 8) { const Half8 x = ld8(ib + ((long long)h * p.W + w) * Cs);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) xv[j] = __half2float(x.v[j]);
+        } else xv[0] = __half2float(ib[((long long)h * p.W + w) * Cs]);
         // windows (ho, wo) that contain (h, w)
         int ho_lo = h - p.kh + 1; ho_lo = ho_lo <= 0 ? 0 : (ho_lo + p.sh - 1) / p.sh;
         int wo_lo = w - p.kw + 1; wo_lo = wo_lo <= 0 ? 0 : (wo_lo + p.sw - 1) / p.sw;
-        int ho_hi = min(p.Ho - 1, h / p.sh), wo_hi = min(p.Wo - 1, w / p.sw);
+        const int ho_hi = min(p.Ho - 1, h / p.sh), wo_hi = min(p.Wo - 1, w / p.sw);
         for (int ho = ho_lo; ho <= ho_hi; ++ho)
             for (int wo = wo_lo; wo <= wo_hi; ++wo) {
-                long long oo = b * p.out_bs + ((long long)ho * p.Wo + wo) * C + c;
-                float mx = __half2float(p.out[oo]);
-                bool is_max = (xv == mx) || (xv != xv && mx != mx);
-                if (!is_max) continue;
-                // first maximum wins: no earlier element of the window may equal the maximum
-                bool first = true;
-                int hi0 = ho * p.sh, wi0 = wo * p.sw;
-                for (int i = 0; i < p.kh && first; ++i)
-                    for (int j = 0; j < p.kw; ++j) {
-                        int hh = hi0 + i, ww = wi0 + j;
+                const long long oo = (b * HoWo + (long long)ho * p.Wo + wo) * Cs + c0;
+                float mx[8], go[8];
+                if (cw == 8) { const Half8 m8 = ld8(p.out + oo), g8 = ld8(p.gout + oo);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { mx[j] = __half2float(m8.v[j]); go[j] = __half2float(g8.v[j]); }
+                } else { mx[0] = __half2float(p.out[oo]); go[0] = __half2float(p.gout[oo]); }
+                unsigned cand = 0;          // lanes where this element equals the window maximum
+                for (int j = 0; j < cw; ++j) if (xv[j] == mx[j] || (xv[j] != xv[j] && mx[j] != mx[j])) cand |= 1u << j;
+                if (!cand) continue;
+                // first maximum wins: drop lanes where an earlier element of the window equals the maximum
+                const int hi0 = ho * p.sh, wi0 = wo * p.sw;
+                for (int i = 0; i < p.kh && cand; ++i)
+                    for (int jj = 0; jj < p.kw && cand; ++jj) {
+                        const int hh = hi0 + i, ww = wi0 + jj;
                         if (hh == h && ww == w) { i = p.kh; break; }
-                        float v = __half2float(ib[((long long)hh * p.W + ww) * C]);
-                        if (v == mx || (v != v && mx != mx)) { first = false; break; }
+                        const __half* s = ib + ((long long)hh * p.W + ww) * Cs;
+                        if (cw == 8) { const Half8 e = ld8(s);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) { const float v = __half2float(e.v[j]); if (v == mx[j] || (v != v && mx[j] != mx[j])) cand &= ~(1u << j); }
+                        } else { const float v = __half2float(*s); if (v == mx[0] || (v != v && mx[0] != mx[0])) cand = 0; }
                     }
-                if (first) g += __half2float(p.gout[oo]);
+                for (int j = 0; j < cw; ++j) if (cand & (1u << j)) g[j] += go[j];
             }
-        __half* d = p.din + b * p.in_bs + r;
-        if (p.din_acc) g = rh(g) + __half2float(*d);
-        *d = __float2half_rn(g);
+        __half* d = p.din + b * p.in_bs + (long long)rem * Cs + c0;
+        if (cw == 8) {
+            Half8 o;
+            if (p.din_acc) o = ld8(d);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float v = g[j];
+                if (c0 + j >= p.C) v = 0.f;
+                if (p.din_acc) v = rh(v) + __half2float(o.v[j]);
+                o.v[j] = __float2half_rn(v);
+            }
+            st8(d, o);
+        } else {
+            float v = g[0];
+            if (p.din_acc) v = rh(v) + __half2float(*d);
+            *d = __float2half_rn(v);
+        }
     }
 }
 
-// ------------------------------------------------------------------ concat (last axis)
-// fwd: out[b][r][coff + c] = in[b][r][c];  bwd: din[b][r][c] (+)= gout[b][r][coff + c]
+// ------------------------------------------------------------------ copy: concatenate (last axis) and non-view reshape
+// The source's n_el real elements per sample, in row-major (row, channel) order, fill rows of Cj channels at
+// channel offset coff of the destination.  fwd: out <- in;  bwd: din (+)= gout.
+__host__ __device__ inline int copy_blocks(long long elems) { return (int)((elems + EW_PER_CTA * 2 - 1) / (EW_PER_CTA * 2)); }
+
 static __global__ void __launch_bounds__(EW_THREADS)
-k_concat(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, Inputs I, int bwd) {
+k_copy(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, Inputs I, int bwd) {
     const int pi = find_prob(prefix, nprob, blockIdx.x);
     const Prob p = probs[pi];
     if (bwd && p.din == nullptr) return;
     const int blk = blockIdx.x - prefix[pi];
-    const int C = p.C, per = p.H * p.W * C;
-    const long long total = (long long)nb * per;
+    const long long total = (long long)nb * p.n_el;
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
-    long long e = (long long)blk * EW_PER_CTA + threadIdx.x;
+    long long e = (long long)blk * (EW_PER_CTA * 2) + threadIdx.x;
 #pragma unroll
-    for (int i = 0; i < EW_PER_THREAD; ++i, e += EW_THREADS) {
+    for (int i = 0; i < EW_PER_THREAD * 2; ++i, e += EW_THREADS) {
         if (e >= total) break;
-        long long b = e / per; int r = (int)(e - b * per);
-        int c = r % C; int row = r / C;
-        long long oo = b * p.out_bs + (long long)row * p.F + p.coff + c;
+        const long long b = e / p.n_el; const int ee = (int)(e - b * p.n_el);
+        const int sr = ee / p.C, sc = ee - sr * p.C;
+        const int dr = ee / p.Cj, dc = ee - dr * p.Cj;
+        const long long so = b * in_bs + (long long)sr * p.Cs + sc;
+        const long long dd = b * p.out_bs + (long long)dr * p.Fs + p.coff + dc;
         if (!bwd) {
-            p.out[oo] = in[b * in_bs + r];
+            p.out[dd] = in[so];
         } else {
-            __half* d = p.din + b * p.in_bs + r;
-            float g = __half2float(p.gout[oo]);
-            if (p.din_acc) g += __half2float(*d);
-            *d = __float2half_rn(g);
+            const long long go = b * p.in_bs + (long long)sr * p.Cs + sc;
+            float g = __half2float(p.gout[dd]);
+            if (p.din_acc) g += __half2float(p.din[go]);
+            p.din[go] = __float2half_rn(g);
         }
     }
 }

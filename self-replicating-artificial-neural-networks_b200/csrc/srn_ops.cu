@@ -222,7 +222,7 @@ extern "C" int srn_bn_train_forward(int32_t device, const uint16_t* x, int64_t r
     if (rows * (int64_t)C > 0x7fffffffLL) return fail(SRN_ERR_LIMIT, "srn_bn_train_forward: more than 2^31 elements");
     int rc = check_device(device);
     if (rc) return rc;
-    const int chunks = col_chunks(rows);
+    const int chunks = col_chunks(rows, C);
     __half *d_x = nullptr, *d_y = nullptr, *d_par = nullptr; float* d_save = nullptr; Prob* d_prob = nullptr; int* d_prefix = nullptr;
     auto cleanup = [&]() { cudaFree(d_x); cudaFree(d_y); cudaFree(d_par); cudaFree(d_save); cudaFree(d_prob); cudaFree(d_prefix); };
 #define CKR(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); return fail(SRN_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); } } while (0)
@@ -240,9 +240,9 @@ extern "C" int srn_bn_train_forward(int32_t device, const uint16_t* x, int64_t r
     CKR(cudaMemcpy(d_par + 3 * C, moving_variance, C * sizeof(__half), cudaMemcpyHostToDevice));
     Prob p{};
     p.in = d_x; p.out = d_y; p.w = d_par; p.bias = d_par + C; p.mov = d_par + 2 * C; p.save = d_save;
-    p.H = 1; p.W = 1; p.C = C; p.Ho = 1; p.Wo = 1; p.F = C; p.in_bs = C; p.out_bs = C;    // nb = rows samples of one row each
+    p.H = 1; p.W = 1; p.C = C; p.Cs = C; p.Ho = 1; p.Wo = 1; p.F = C; p.Fs = C; p.in_bs = C; p.out_bs = C;    // nb = rows samples of one row each
     const int nb = (int)rows;
-    const int pre[4] = {0, chunks, 0, ew_blocks((long long)ne)};
+    const int pre[4] = {0, chunks, 0, ew_blocks(rows, C)};
     CKR(cudaMemcpy(d_prob, &p, sizeof(Prob), cudaMemcpyHostToDevice));
     CKR(cudaMemcpy(d_prefix, pre, sizeof pre, cudaMemcpyHostToDevice));
     Inputs I{};
@@ -282,12 +282,12 @@ extern "C" int srn_bn_train_forward_noalloc(int32_t device, void* stream, const 
     if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(SRN_ERR_ARG, "srn_bn_train_forward_noalloc: device %d", device);
     if (d_moving_variance != d_moving_mean + C)
         return fail(SRN_ERR_ARG, "srn_bn_train_forward_noalloc: moving_variance must directly follow moving_mean (one [2][C] array)");
-    const int chunks = col_chunks(rows);
+    const int chunks = col_chunks(rows, C);
     const size_t need = 4 * (size_t)C + 2 * (size_t)C * chunks;
     if (need > NOALLOC_FLOATS)
         return fail(SRN_ERR_LIMIT, "srn_bn_train_forward_noalloc: C * (4 + 2 * ceil(rows / %d)) = %zu floats exceeds the built-in "
-                    "scratch of %zu floats (%zu bytes); use srn_bn_train_forward for this size", COL_ROWS, need, NOALLOC_FLOATS,
-                    (size_t)SRN_NOALLOC_SCRATCH_BYTES);
+                    "scratch of %zu floats (%zu bytes); use srn_bn_train_forward for this size", col_geom(C).rows_per_cta, need,
+                    NOALLOC_FLOATS, (size_t)SRN_NOALLOC_SCRATCH_BYTES);
     int rc = check_device(device);
     if (rc) return rc;
     if (!g_noalloc_ptr[device]) {
@@ -308,9 +308,9 @@ extern "C" int srn_bn_train_forward_noalloc(int32_t device, void* stream, const 
     p.in = reinterpret_cast<const __half*>(d_x); p.out = reinterpret_cast<__half*>(d_y);
     p.w = reinterpret_cast<const __half*>(d_gamma); p.bias = reinterpret_cast<const __half*>(d_beta);
     p.mov = reinterpret_cast<__half*>(d_moving_mean); p.save = d_save;
-    p.H = 1; p.W = 1; p.C = C; p.Ho = 1; p.Wo = 1; p.F = C; p.in_bs = C; p.out_bs = C;
+    p.H = 1; p.W = 1; p.C = C; p.Cs = C; p.Ho = 1; p.Wo = 1; p.F = C; p.Fs = C; p.in_bs = C; p.out_bs = C;
     const int nb = (int)rows;
-    const int blocks = ew_blocks(rows * (long long)C);
+    const int blocks = ew_blocks(rows, C);
     hdr.pre[0] = 0; hdr.pre[1] = chunks; hdr.pre[2] = 0; hdr.pre[3] = blocks;
     static_assert(offsetof(decltype(hdr), pre) == sizeof(Prob), "descriptor layout");
     CK(cudaMemcpyAsync(d_prob, &hdr, sizeof hdr, cudaMemcpyHostToDevice, st));

@@ -146,7 +146,8 @@ def activation_bytes_estimate(ir: SerannIR, max_batch: int) -> int:
     total = 0
     for l in ir.layers:
         if l.kind != KIND_RESHAPE:
-            total += 2 * l.out_elems
+            c = l.out_shape[-1]
+            total += 2 * (l.out_elems // c) * (-(-c // 8) * 8)      # channel stride padded to 8
     return total * 2 * max_batch
 
 
