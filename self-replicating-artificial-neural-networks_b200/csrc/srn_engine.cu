@@ -76,10 +76,12 @@ struct Indiv {
 struct Cached {
     int* prefix[P_COUNT] = {};
     int total[P_COUNT] = {};
+    TcTile* tiles[P_COUNT] = {};   // tensor-core passes: one 256-byte descriptor per tile, heaviest first
 };
 
 struct Group {
     int depth, kind, cfgF, cfgC, ordinal, tc;
+    int mode = 3;                  // bit 0: runs when the inputs are a shared batch, bit 1: when they are per individual
     std::vector<Prob> h;
     Prob* d = nullptr;
     std::map<int, Cached> cache;
@@ -96,6 +98,9 @@ struct srn_engine {
     std::vector<ProfRec*> prof;
     srn_config cfg{};
     cudaStream_t stream = 0;
+    int num_sms = 148;
+    std::vector<Im2colGeo> geos;         // shared im2col buffers of the first layers (one per window geometry)
+    __half* im2col = nullptr;
     int xe = 0, G = 0, ncls = 0, NL = 0;
     // dataset
     __half* x[2] = {nullptr, nullptr};
@@ -174,6 +179,7 @@ static void free_population(srn_engine* h) {
     h->inds.clear();
     cudaFree(h->d_loss); h->d_loss = nullptr;
     cudaFree(h->d_lb); h->d_lb = nullptr;
+    cudaFree(h->im2col); h->im2col = nullptr; h->geos.clear();
     cudaFree(h->P); cudaFree(h->M); cudaFree(h->V); cudaFree(h->S); cudaFree(h->act); cudaFree(h->Gr); cudaFree(h->save);
     h->P = h->M = h->V = h->S = h->act = nullptr; h->Gr = h->save = nullptr;
     cudaFree(h->met_correct); cudaFree(h->met_ce); cudaFree(h->met_mse);
@@ -202,6 +208,7 @@ extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
     }
     srn_engine* h = new srn_engine();
     h->cfg = *cfg;
+    CK(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
     h->xe = cfg->image_h * cfg->image_w;
     h->G = cfg->genotype_size;
     h->ncls = cfg->n_classes;
@@ -428,6 +435,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
     CK(cudaMemsetAsync(h->act, 0, (size_t)h->act_elems * sizeof(__half), h->stream));
     // ---- pass 2: pointers, consumer ordinals, problem groups
     std::map<std::tuple<int, int, int, int, int>, Group> gmap;
+    long long geo_elems = 0;
     h->h_loss.clear();
     for (int i = 0; i < n; ++i) {
         Indiv& ind = h->inds[i];
@@ -475,8 +483,8 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                     if (g_tensor_cores) {
                         // 1: operands in 16-byte chunks (channel stride padded to 8); 2: first layers on a one-channel
                         // model input, im2col gathered element by element
-                        if (p.Cs % 8 == 0 && p.Fs % 8 == 0 && tc_k_fwd(p) >= 32) tc = 1;
-                        else if (p.in_sel != 0 && p.Cs == 1 && p.C == 1 && p.Fs % 8 == 0 && p.kh * p.kw >= 9) tc = 2;
+                        if (p.Cs % 8 == 0 && p.Fs % 8 == 0) tc = 1;
+                        else if (p.in_sel != 0 && p.Cs == 1 && p.C == 1 && p.Fs % 8 == 0) tc = 2;
                         if (tc) { cfgF = tc_cfg_for(p.F); cfgC = tc_cfg_for(p.C); }
                     }
                 } else if (d.kind == SRN_KIND_MAXPOOL) {
@@ -493,9 +501,43 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                     p.coff = coff;
                     coff += p.Cj;
                 }
-                auto key = std::make_tuple(to.depth, kind, cfgF + 16 * tc, cfgC, ordinal);
+                int mode = 3;
+                if (tc == 2) {
+                    // first layer on a model input: with a shared batch it runs as a Dense over the shared im2col
+                    // matrix of its window geometry (vector path); the element-wise gather variant below is kept
+                    // for per-individual inputs (replication)
+                    int gi = -1;
+                    for (size_t q = 0; q < h->geos.size(); ++q) {
+                        const Im2colGeo& e = h->geos[q];
+                        if (e.in_bs == -p.in_sel && e.kh == p.kh && e.kw == p.kw && e.sh == p.sh && e.sw == p.sw) { gi = (int)q; break; }
+                    }
+                    if (gi < 0) {
+                        Im2colGeo e{};
+                        e.in_bs = -p.in_sel;                 // placeholder: which input (resolved per launch)
+                        e.H = p.H; e.W = p.W; e.kh = p.kh; e.kw = p.kw; e.sh = p.sh; e.sw = p.sw; e.Ho = p.Ho; e.Wo = p.Wo;
+                        e.KK = p.kh * p.kw; e.Kp = (int)align_up(e.KK, 8);
+                        e.out = (__half*)nullptr + geo_elems;    // offset for now, fixed up after allocation
+                        geo_elems += align_up((long long)MB * e.Ho * e.Wo * e.Kp, 64);
+                        h->geos.push_back(e);
+                        gi = (int)h->geos.size() - 1;
+                    }
+                    Prob s2 = p;
+                    const Im2colGeo& e = h->geos[gi];
+                    s2.in_sel = 0; s2.in = (const __half*)nullptr + (e.out - (__half*)nullptr);   // fixed up below
+                    s2.in_bs = e.Ho * e.Wo * e.Kp;
+                    s2.H = e.Ho * e.Wo; s2.W = 1; s2.C = e.KK; s2.Cs = e.Kp; s2.Ho = s2.H; s2.Wo = 1;
+                    s2.kh = s2.kw = s2.sh = s2.sw = 1;
+                    s2.coff = gi;                            // geometry index, used for the fix-up
+                    const int cF = tc_cfg_for(s2.F), cC = tc_cfg_for(s2.C);
+                    auto key2 = std::make_tuple(to.depth, kind, cF + 16 * 1 + 64 * 1, cC, ordinal);
+                    Group& g2 = gmap[key2];
+                    g2.depth = to.depth; g2.kind = kind; g2.cfgF = cF; g2.cfgC = cC; g2.ordinal = ordinal; g2.tc = 1; g2.mode = 1;
+                    g2.h.push_back(s2);
+                    mode = 2;
+                }
+                auto key = std::make_tuple(to.depth, kind, cfgF + 16 * tc + 64 * mode, cfgC, ordinal);
                 Group& g = gmap[key];
-                g.depth = to.depth; g.kind = kind; g.cfgF = cfgF; g.cfgC = cfgC; g.ordinal = ordinal; g.tc = tc;
+                g.depth = to.depth; g.kind = kind; g.cfgF = cfgF; g.cfgC = cfgC; g.ordinal = ordinal; g.tc = tc; g.mode = mode;
                 g.h.push_back(p);
             }
         }
@@ -506,6 +548,15 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
     }
     h->groups.clear();
     for (auto& kv : gmap) h->groups.push_back(std::move(kv.second));   // std::map iterates in key order
+    if (geo_elems > 0) {
+        CK(cudaMalloc(&h->im2col, (size_t)geo_elems * sizeof(__half)));
+        CK(cudaMemsetAsync(h->im2col, 0, (size_t)geo_elems * sizeof(__half), h->stream));
+        h->device_bytes += geo_elems * 2;
+        for (auto& e : h->geos) e.out = h->im2col + (e.out - (__half*)nullptr);
+        for (auto& g : h->groups)
+            if (g.mode == 1)
+                for (auto& q : g.h) { q.in = h->geos[q.coff].out; q.coff = 0; }
+    }
     // backward runs the groups in reverse: the first writer of each input gradient overwrites, later ones add
     {
         std::map<const __half*, bool> written;
@@ -647,8 +698,8 @@ static int pass_items(const Group& g, const Prob& p, int pass, int nb) {
             if (pass == P_BWD_EW) return p.din ? ew_blocks(in_rows, p.Cs) : 0;
             return 0;
         case SRN_KIND_CONCAT:
-            if (pass == P_FWD) return copy_blocks((long long)nb * p.n_el);
-            if (pass == P_BWD_EW) return p.din ? copy_blocks((long long)nb * p.n_el) : 0;
+            if (pass == P_FWD) return copy_blocks(p, nb);
+            if (pass == P_BWD_EW) return p.din ? copy_blocks(p, nb) : 0;
             return 0;
     }
     return 0;
@@ -674,10 +725,40 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
     CK(cudaStreamSynchronize(h->stream));      // host vector goes out of scope
     h->scratch_prefix.push_back(dev);
     for (int pass = 0; pass < P_COUNT; ++pass) c.prefix[pass] = dev + (size_t)pass * (np + 1);
+    if (g.tc) {
+        for (int pass : {P_FWD, P_DGRAD, P_WGRAD}) {
+            if (!c.total[pass]) continue;
+            const int* pre = host.data() + (size_t)pass * (np + 1);
+            const int mode = pass == P_FWD ? TC_FWD : (pass == P_DGRAD ? TC_DGRAD : TC_WGRAD);
+            const int BN = TC_BN[pass == P_DGRAD ? g.cfgC : g.cfgF];
+            std::vector<TcTile> tt((size_t)c.total[pass]);
+            for (int i = 0; i < np; ++i)
+                for (int t = pre[i]; t < pre[i + 1]; ++t) {
+                    memset(&tt[t], 0, sizeof(TcTile));
+                    tt[t].p = g.h[i];
+                    tc_describe_tile(tt[t], t - pre[i], nb, BN, mode, g.tc == 2);
+                }
+            std::stable_sort(tt.begin(), tt.end(), [](const TcTile& a, const TcTile& b) { return a.nk > b.nk; });
+            TcTile* dt = nullptr;
+            CK(cudaMalloc(&dt, tt.size() * sizeof(TcTile)));
+            CK(cudaMemcpy(dt, tt.data(), tt.size() * sizeof(TcTile), cudaMemcpyHostToDevice));
+            h->scratch_prefix.push_back(reinterpret_cast<int*>(dt));
+            c.tiles[pass] = dt;
+        }
+    }
     g.cache[nb] = c;
     *out = &g.cache[nb];
     return SRN_OK;
 }
+
+// persistent tensor-core launch: as many CTAs as fit the machine (shared memory bound), each walking the tile table
+static int tc_grid(srn_engine* h, int total, int BN) {
+    const int per_sm = std::max(1, std::min(4, (227 * 1024) / (tc_smem_bytes(BN) + 1024)));
+    return std::min(total, h->num_sms * per_sm);
+}
+#define LAUNCH_TC(cat, MODE, SCALAR, pass, BN_)                                                    \
+    LAUNCH_SMEM(cat, (k_gemm_tc<MODE, SCALAR>), tc_grid(h, c->total[pass], BN_), TC_THREADS, tc_smem_bytes(BN_), \
+                c->tiles[pass], c->total[pass], nb, BN_, I)
 
 template <int CFG>
 static void launch_fwd_cfg(srn_engine* h, Group& g, Cached* c, int nb, const Inputs& I) {
@@ -691,7 +772,18 @@ static void launch_dgrad_cfg(srn_engine* h, Group& g, Cached* c, int nb) {
 }
 
 static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
+    const int mode = (I.x_istride == 0 && I.g_istride == 0) ? 1 : 2;
+    if (mode == 1) {
+        for (const Im2colGeo& e0 : h->geos) {
+            Im2colGeo e = e0;
+            const bool img = e0.in_bs == -1;
+            e.in = img ? I.x : I.g; e.in_bs = img ? I.x_bs : I.g_bs;
+            const long long total = (long long)nb * e.Ho * e.Wo * (e.Kp >> 3);
+            LAUNCH(SRN_CAT_GATHER, k_im2col, (unsigned)((total + 255) / 256), 256, e, nb);
+        }
+    }
     for (auto& g : h->groups) {
+        if (!(g.mode & mode)) continue;
         Cached* c;
         int rc = plan_for(h, g, nb, &c);
         if (rc) return rc;
@@ -701,8 +793,8 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
             case SRN_KIND_CONV:
                 if (g.tc) {
                     const int BN = TC_BN[g.cfgF];
-                    if (g.tc == 1) LAUNCH_SMEM(SRN_CAT_GEMM_FWD, (k_gemm_tc<TC_FWD, false>), c->total[P_FWD], TC_THREADS, tc_smem_bytes(BN), g.d, c->prefix[P_FWD], np, nb, BN, I);
-                    else LAUNCH_SMEM(SRN_CAT_GEMM_FWD, (k_gemm_tc<TC_FWD, true>), c->total[P_FWD], TC_THREADS, tc_smem_bytes(BN), g.d, c->prefix[P_FWD], np, nb, BN, I);
+                    if (g.tc == 1) LAUNCH_TC(SRN_CAT_GEMM_FWD, TC_FWD, false, P_FWD, BN);
+                    else LAUNCH_TC(SRN_CAT_GEMM_FWD, TC_FWD, true, P_FWD, BN);
                     break;
                 }
                 if (g.cfgF == 0) launch_fwd_cfg<0>(h, g, c, nb, I);
@@ -730,8 +822,10 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
 }
 
 static int backward_pass(srn_engine* h, int nb, const Inputs& I) {
+    const int mode = (I.x_istride == 0 && I.g_istride == 0) ? 1 : 2;
     for (int gi = (int)h->groups.size() - 1; gi >= 0; --gi) {
         Group& g = h->groups[gi];
+        if (!(g.mode & mode)) continue;
         Cached* c;
         int rc = plan_for(h, g, nb, &c);
         if (rc) return rc;
@@ -742,9 +836,9 @@ static int backward_pass(srn_engine* h, int nb, const Inputs& I) {
                 LAUNCH(SRN_CAT_ACT_BWD, k_act_bwd_bias, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb);
                 if (g.tc) {
                     const int BNf = TC_BN[g.cfgF], BNc = TC_BN[g.cfgC];
-                    if (g.tc == 1) LAUNCH_SMEM(SRN_CAT_GEMM_WGRAD, (k_gemm_tc<TC_WGRAD, false>), c->total[P_WGRAD], TC_THREADS, tc_smem_bytes(BNf), g.d, c->prefix[P_WGRAD], np, nb, BNf, I);
-                    else LAUNCH_SMEM(SRN_CAT_GEMM_WGRAD, (k_gemm_tc<TC_WGRAD, true>), c->total[P_WGRAD], TC_THREADS, tc_smem_bytes(BNf), g.d, c->prefix[P_WGRAD], np, nb, BNf, I);
-                    LAUNCH_SMEM(SRN_CAT_GEMM_DGRAD, (k_gemm_tc<TC_DGRAD, false>), c->total[P_DGRAD], TC_THREADS, tc_smem_bytes(BNc), g.d, c->prefix[P_DGRAD], np, nb, BNc, I);
+                    if (g.tc == 1) LAUNCH_TC(SRN_CAT_GEMM_WGRAD, TC_WGRAD, false, P_WGRAD, BNf);
+                    else LAUNCH_TC(SRN_CAT_GEMM_WGRAD, TC_WGRAD, true, P_WGRAD, BNf);
+                    LAUNCH_TC(SRN_CAT_GEMM_DGRAD, TC_DGRAD, false, P_DGRAD, BNc);
                     break;
                 }
                 LAUNCH(SRN_CAT_GEMM_WGRAD, k_conv_wgrad, c->total[P_WGRAD], SIMT_THREADS, g.d, c->prefix[P_WGRAD], np, nb, I);

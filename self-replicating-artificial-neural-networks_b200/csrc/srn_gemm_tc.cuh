@@ -9,9 +9,16 @@
 //   forward  Out = A(K-major, im2col rows) x W(MN-major, [k][n] rows)
 //   dgrad    dIn = dOut'(K-major)         x W(K-major, rows (ij, c), contiguous f)
 //   wgrad    dW  = A(MN-major, [row][kk]) x dOut(MN-major, [row][f])      (reduction over rows)
-// A 4-stage ring of (A, B) tiles is filled two k-blocks ahead; one thread issues four K=16 tcgen05.mma per
-// k-block and commits to the ring's mbarriers; the fp32 accumulator lives in TMEM and is read back with
-// tcgen05.ld by the four warps (warp w owns TMEM lanes 32w..32w+31) for the same epilogues as the SIMT kernels.
+// The kernel is persistent and warp-specialised.  A CTA walks its share of a host-built table of 256-byte tile
+// descriptors (sorted by cost, dealt out in snake order, prefetched four tiles ahead) and treats the k-blocks
+// of its tiles as one stream:
+//   warps 0-7  loaders: gather k-block p into ring stage p % 4 (cp.async), and once their own copies of
+//              k-block p - 3 have landed (wait_group + fence.proxy.async) arrive on that stage's "full" barrier;
+//   warp 8     one thread waits "full", issues four K=16 tcgen05.mma into one of two TMEM accumulators and
+//              commits to the stage's "empty" barrier (and to "tmem_full" after a tile's last k-block);
+//   warps 9-12 epilogue: wait "tmem_full", read the accumulator with tcgen05.ld (warp w owns TMEM lanes
+//              32 (w % 4) ..), apply the same epilogues as the SIMT kernels, arrive on "tmem_empty".
+// Loads, MMAs and epilogues of neighbouring tiles therefore overlap; nothing in the loop is a CTA-wide barrier.
 //
 // Every activation tensor has its channel stride padded to 8 with zero pad (srn_common.cuh), so a 16-byte
 // chunk is always aligned and inside one pixel; the k index of a pass runs over the padded (pixel, channel)
@@ -25,16 +32,25 @@ namespace srn {
 
 constexpr int TC_BM = 128;            // UMMA M
 constexpr int TC_BK = 64;             // k elements per stage (4 MMAs of K = 16)
-constexpr int TC_STAGES = 4;
-constexpr int TC_PF = 3;              // prefetch distance in k-blocks
-constexpr int TC_THREADS = 128;
+constexpr int TC_MAX_STAGES = 8;
+constexpr int TC_LW = 8;               // loader warps
+constexpr int TC_LOADERS = TC_LW * 32;
+constexpr int TC_THREADS = TC_LOADERS + 32 + 128;   // loaders + 1 MMA warp + 4 epilogue warps
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;
 constexpr int TC_WGRAD_ROWS = 4096;   // reduction rows per wgrad CTA (64 k-blocks)
 
 enum { TC_FWD = 0, TC_DGRAD = 1, TC_WGRAD = 2 };
 
-__host__ __device__ inline int tc_smem_bytes(int BN) { return TC_STAGES * (TC_A_BYTES + BN * TC_BK * 2) + 256; }
-__host__ __device__ inline int tc_tmem_cols(int BN) { return BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256)); }
+constexpr int TC_RING = 16;           // tile descriptors in shared memory: epilogue <= 6 tiles behind the loader, prefetch 4 ahead
+constexpr int TC_DESC_AHEAD = 4;
+// Pipeline depth per N tile: BN <= 64 keeps two CTAs per SM (4 stages each), wider tiles take the SM alone with as
+// many stages as fit.  A loader publishes k-block p - lag after issuing k-block p (lag + 1 k-blocks of loads in
+// flight per thread); stages - lag - 1 >= 1 further stages decouple the loaders from the MMA completion latency.
+__host__ __device__ inline int tc_stages(int BN) { return BN <= 64 ? 4 : (BN <= 128 ? 6 : 4); }
+__host__ __device__ inline int tc_lag(int BN) { return BN <= 64 ? 2 : (BN <= 128 ? 4 : 2); }
+__host__ __device__ inline int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + BN * TC_BK * 2) + 256 + TC_RING * 256; }
+__host__ __device__ inline int tc_acc_cols(int BN) { return BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256)); }
+__host__ __device__ inline int tc_tmem_cols(int BN) { return 2 * tc_acc_cols(BN); }     // two accumulators
 __host__ __device__ inline int round_up8(int v) { return (v + 7) & ~7; }
 
 // reduction length of each pass as the kernel sees it: over padded channels
@@ -70,6 +86,10 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(count) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void loaders_sync() { asm volatile("bar.sync 1, 256;\n" ::: "memory"); }   // the loader warps only
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n"
@@ -80,6 +100,21 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         "bra WAIT_LOOP;\n"
         "WAIT_DONE:\n"
         "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+// same, for waits that last a whole tile (epilogue, accumulator hand-back): back off so that the spinning warps
+// do not take issue slots from the loaders
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    while (true) {
+        asm volatile(
+            "{\n"
+            ".reg .pred P1;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, P1;\n"
+            "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (done) break;
+        __nanosleep(200);
+    }
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
@@ -131,9 +166,75 @@ __device__ __forceinline__ uint32_t core_off(int mn_group, int k_group, int r8) 
 }
 
 // ------------------------------------------------------------------ the kernel
+// what the loader, the MMA issuer and the epilogue need to know about one tile (lives in a shared-memory ring)
+// division by a runtime constant as multiply-high + shift (valid for numerators < 2^31); the loaders do
+// several index decompositions per 16-byte chunk and a hardware-less integer division costs ~20 dependent instructions
+struct FastDiv {
+    uint32_t mul, shr;
+    int d;
+};
+inline FastDiv make_fastdiv(int d) {
+    FastDiv f; f.d = d; f.mul = 0; f.shr = 0;
+    if (d > 1) {
+        int lg = 31 - __builtin_clz((unsigned)d);
+        if (d & (d - 1)) ++lg;
+        const int p = 31 + lg;
+        f.mul = (uint32_t)((((unsigned long long)1 << p) + (unsigned)d - 1) / (unsigned)d);
+        f.shr = (uint32_t)(p - 32);
+    }
+    return f;
+}
+__device__ __forceinline__ int fdiv(int n, const FastDiv& f) { return f.d == 1 ? n : (int)(__umulhi((uint32_t)n, f.mul) >> f.shr); }
+
+struct __align__(16) TcTile {
+    Prob p;
+    int m0, n0, nk, n_umma, r0, r1, Mrows, Ncols;
+    FastDiv fd_rows;   // rows per sample of the M index: Ho*Wo (fwd, wgrad) or H*W (dgrad)
+    FastDiv fd_w;      // Wo (fwd, wgrad) or W (dgrad)
+    FastDiv fd_c;      // channel stride of the k index: Cs (fwd, wgrad) or Fs (dgrad)
+    FastDiv fd_kw;
+    unsigned char pad[256 - sizeof(Prob) - 8 * sizeof(int) - 4 * sizeof(FastDiv)];
+};
+static_assert(sizeof(TcTile) == 256, "TcTile is one 256-byte table entry / ring slot");
+
+// index in the table of the j-th tile of CTA c (G CTAs): rounds alternate direction so that costs even out
+__host__ __device__ inline int tc_tile_index(int c, int j, int G) { return j * G + ((j & 1) ? G - 1 - c : c); }
+
+inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool SCALAR_A) {
+    const Prob& p = t.p;
+    const int HoWo = p.Ho * p.Wo;
+    const int KK = p.kh * p.kw;
+    const int Kf = SCALAR_A ? KK : KK * p.Cs;
+    t.r0 = 0; t.r1 = 0;
+    if (MODE == TC_FWD) {
+        t.Mrows = nb * HoWo; t.Ncols = p.F;
+        const int tn = (t.Ncols + BN - 1) / BN;
+        t.m0 = (tile / tn) * TC_BM; t.n0 = (tile % tn) * BN;
+        t.nk = (Kf + TC_BK - 1) / TC_BK;
+    } else if (MODE == TC_DGRAD) {
+        t.Mrows = nb * p.H * p.W; t.Ncols = p.C;
+        const int tn = (t.Ncols + BN - 1) / BN;
+        t.m0 = (tile / tn) * TC_BM; t.n0 = (tile % tn) * BN;
+        t.nk = (KK * p.Fs + TC_BK - 1) / TC_BK;
+    } else {
+        t.Mrows = Kf; t.Ncols = p.F;                      // output rows are kk = (i, j, padded c)
+        const int tm = (t.Mrows + TC_BM - 1) / TC_BM, tn = (t.Ncols + BN - 1) / BN;
+        const int split = tile / (tm * tn);
+        tile -= split * tm * tn;
+        t.m0 = (tile / tn) * TC_BM; t.n0 = (tile % tn) * BN;
+        t.r0 = split * TC_WGRAD_ROWS; t.r1 = min(nb * HoWo, t.r0 + TC_WGRAD_ROWS);
+        t.nk = (t.r1 - t.r0 + TC_BK - 1) / TC_BK;
+    }
+    t.n_umma = min(BN, ((t.Ncols - t.n0 + 15) / 16) * 16);
+    t.fd_rows = make_fastdiv(MODE == TC_DGRAD ? p.H * p.W : HoWo);
+    t.fd_w = make_fastdiv(MODE == TC_DGRAD ? p.W : p.Wo);
+    t.fd_c = make_fastdiv(MODE == TC_DGRAD ? p.Fs : p.Cs);
+    t.fd_kw = make_fastdiv(p.kw);
+}
+
 template <int MODE, bool SCALAR_A>
 static __global__ void __launch_bounds__(TC_THREADS)
-k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, int BN, Inputs I) {
+k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int l8 = lane & 7, lq = lane >> 3;              // row inside a core matrix, chunk inside a quad
@@ -141,316 +242,378 @@ k_gemm_tc(const Prob* __restrict__ probs, const int* __restrict__ prefix, int np
     const uint32_t sbase = (sraw + 127u) & ~127u;
     unsigned char* sgen = smem_raw + (sbase - sraw);      // generic pointer to the same place as sbase
     const uint32_t B_BYTES = (uint32_t)BN * TC_BK * 2;
-    const uint32_t sA = sbase, sB = sbase + TC_STAGES * TC_A_BYTES;
-    const uint32_t sBar = sB + TC_STAGES * B_BYTES;      // TC_STAGES "empty" barriers + 1 "done" barrier
-    const uint32_t sSlot = sBar + (TC_STAGES + 1) * 8;
+    const int STAGES = tc_stages(BN), LAG = tc_lag(BN);
+    const uint32_t sA = sbase, sB = sbase + STAGES * TC_A_BYTES;
+    const uint32_t sRing = sB + STAGES * B_BYTES;         // TC_RING tile descriptors of 256 bytes
+    const uint32_t sFull = sRing + TC_RING * 256;         // barriers: full[S], empty[S], tmem_full[2], tmem_empty[2]
+    const uint32_t sEmpty = sFull + TC_MAX_STAGES * 8;
+    const uint32_t sTFull = sEmpty + TC_MAX_STAGES * 8;
+    const uint32_t sTEmpty = sTFull + 2 * 8;
+    const uint32_t sSlot = sTEmpty + 2 * 8;
+    TcTile* ring = reinterpret_cast<TcTile*>(sgen + (sRing - sbase));
     volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(sgen + (sSlot - sbase));
+    const int acc_cols = tc_acc_cols(BN), tmem_cols = tc_tmem_cols(BN);
 
-    const int pi = find_prob(prefix, nprob, blockIdx.x);
-    const Prob p = probs[pi];
-    int tile = blockIdx.x - prefix[pi];
-    const int tmem_cols = tc_tmem_cols(BN);
+    const int G = gridDim.x, cta = blockIdx.x;
+    int my_tiles = ntiles / G;                                      // full rounds, plus maybe one of the last round
+    if (tc_tile_index(cta, my_tiles, G) < ntiles) ++my_tiles;
+    // 256-byte descriptor of this CTA's j-th tile -> ring slot j % TC_RING (16 loader threads x 16 bytes)
+    auto fetch_desc = [&](int j) {
+        if (j < my_tiles && tid < 16)
+            cp_async16(sRing + (j % TC_RING) * 256 + tid * 16,
+                       reinterpret_cast<const unsigned char*>(table + tc_tile_index(cta, j, G)) + tid * 16, true);
+    };
 
     if (tid == 0) {
-        for (int i = 0; i <= TC_STAGES; ++i) mbar_init(sBar + i * 8, 1);
+        for (int i = 0; i < STAGES; ++i) { mbar_init(sFull + i * 8, TC_LOADERS); mbar_init(sEmpty + i * 8, 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(sTFull + i * 8, 1); mbar_init(sTEmpty + i * 8, 128); }
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
     }
-    if (warp == 0) tmem_alloc(sSlot, (uint32_t)tmem_cols);
+    if (warp == TC_LW) tmem_alloc(sSlot, (uint32_t)tmem_cols);
+    if (warp < TC_LW) {
+        for (int j = 0; j < TC_DESC_AHEAD; ++j) fetch_desc(j);
+        cp_async_commit();
+        cp_async_wait<0>();
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *slot_ptr;
 
-    // ---- problem geometry
-    int in_bs;
-    const __half* in = resolve_in(p, I, in_bs);
-    const int HoWo = p.Ho * p.Wo, HW = p.H * p.W;
-    const int Cs = p.Cs, Fs = p.Fs;
-    const int KK = p.kh * p.kw;
-    const int Kf = SCALAR_A ? KK : KK * Cs;               // forward reduction length (padded channels)
-    const int Kd = KK * Fs;
-    int m0 = 0, n0 = 0, Mrows = 0, Ncols = 0, nk = 0, r0 = 0, r1 = 0;
-    if (MODE == TC_FWD) {
-        Mrows = nb * HoWo; Ncols = p.F;
-        const int tn = (Ncols + BN - 1) / BN;
-        m0 = (tile / tn) * TC_BM; n0 = (tile % tn) * BN;
-        nk = (Kf + TC_BK - 1) / TC_BK;
-    } else if (MODE == TC_DGRAD) {
-        Mrows = nb * HW; Ncols = p.C;
-        const int tn = (Ncols + BN - 1) / BN;
-        m0 = (tile / tn) * TC_BM; n0 = (tile % tn) * BN;
-        nk = (Kd + TC_BK - 1) / TC_BK;
-    } else {
-        Mrows = Kf; Ncols = p.F;                          // output rows are kk = (i, j, padded c)
-        const int tm = (Mrows + TC_BM - 1) / TC_BM, tn = (Ncols + BN - 1) / BN;
-        const int split = tile / (tm * tn);
-        tile -= split * tm * tn;
-        m0 = (tile / tn) * TC_BM; n0 = (tile % tn) * BN;
-        r0 = split * TC_WGRAD_ROWS; r1 = min(nb * HoWo, r0 + TC_WGRAD_ROWS);
-        nk = (r1 - r0 + TC_BK - 1) / TC_BK;
-    }
-    const int n_umma = min(BN, ((Ncols - n0 + 15) / 16) * 16);
-
-    // ---- per-thread loader state that does not change over the k loop
-    const __half* a_row[4];          // FWD: base of the im2col row; null = out of range
-    int a_b[4], a_h[4], a_w[4];      // DGRAD: input position of the row
-    long long w_koff[4]; bool w_kok[4];   // WGRAD (vector): offset of this thread's four kk chunks inside the window
-    if (MODE == TC_FWD) {
+    if (warp < TC_LW) {
+        // =================================================================== loaders (8 warps)
+        // A tile: 128 (m or kk) x 64 k in 16-byte chunks = 1024 chunks, 4 per thread; B tile: BN x 64, BN/32 per
+        // thread.  A warp covers 8 rows x 4 consecutive chunks per item (64 contiguous bytes per row).
+        const __half* l_in = nullptr; int l_in_bs = 0;
+        const __half* a_row[2];          // FWD: base of this thread's two im2col rows; null = out of range
+        int a_b[2], a_h[2], a_w[2];      // DGRAD: input position of this thread's two rows
+        int w_koff[4]; bool w_kok[4];    // WGRAD (vector): offsets of this thread's four kk chunks inside the window
+        int lj = 0, lnk = 0;
+        auto loader_enter_tile = [&]() {
+            loaders_sync();                 // the 16 fetching threads have completed this descriptor's copy long ago
+            const TcTile& T = ring[lj % TC_RING];
+            fetch_desc(lj + TC_DESC_AHEAD);
+            const Prob& p = T.p;
+            l_in = resolve_in(p, I, l_in_bs);
+            lnk = T.nk;
+            const int HoWo = p.Ho * p.Wo, HW = p.H * p.W, Cs = p.Cs;
+            if (MODE == TC_FWD) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int m = m0 + (warp * 4 + j) * 8 + l8;
-            a_row[j] = nullptr;
-            if (m < Mrows) {
-                const int b = m / HoWo, rem = m - b * HoWo;
-                const int ho = rem / p.Wo, wo = rem - ho * p.Wo;
-                a_row[j] = in + (long long)b * in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * Cs;
-            }
-        }
-    } else if (MODE == TC_DGRAD) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int m = m0 + (warp * 4 + j) * 8 + l8;
-            a_b[j] = -1; a_h[j] = 0; a_w[j] = 0;
-            if (m < Mrows) {
-                a_b[j] = m / HW;
-                const int rem = m - a_b[j] * HW;
-                a_h[j] = rem / p.W; a_w[j] = rem - a_h[j] * p.W;
-            }
-        }
-    } else if (!SCALAR_A) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const int kk = m0 + (q * 4 + lq) * 8;
-            w_kok[q] = kk < Kf;
-            const int ij = kk / Cs, cp = kk - ij * Cs;
-            const int i = ij / p.kw, j = ij - i * p.kw;
-            w_koff[q] = ((long long)i * p.W + j) * Cs + cp;
-        }
-    }
-
-    auto load_stage = [&](int stage, int kb) {
-        const uint32_t aS = sA + stage * TC_A_BYTES, bS = sB + stage * B_BYTES;
-        const int items_b = BN >> 4;                     // B items per warp
-        if (MODE == TC_FWD) {
-            // A, K-major: 16 row blocks x 2 quads of k chunks
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int q = warp * 8 + i, blk = q >> 1, ch = (q & 1) * 4 + lq;
-                const int k = kb * TC_BK + ch * 8;
-                const __half* row = a_row[i >> 1];
-                if (SCALAR_A) {
-                    Half8 v;
-                    int ki = k / p.kw, kj = k - ki * p.kw;
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        v.v[e] = (row != nullptr && k + e < Kf) ? row[ki * p.W + kj] : __float2half_rn(0.f);
-                        if (++kj == p.kw) { kj = 0; ++ki; }
+                for (int j = 0; j < 2; ++j) {
+                    const int m = T.m0 + (warp * 2 + j) * 8 + l8;
+                    a_row[j] = nullptr;
+                    if (m < T.Mrows) {
+                        const int b = fdiv(m, T.fd_rows), rem = m - b * HoWo;
+                        const int ho = fdiv(rem, T.fd_w), wo = rem - ho * p.Wo;
+                        a_row[j] = l_in + (long long)b * l_in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * Cs;
                     }
-                    *reinterpret_cast<Half8*>(sgen + (aS - sbase) + core_off(blk, ch, l8)) = v;
+                }
+            } else if (MODE == TC_DGRAD) {
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const int m = T.m0 + (warp * 2 + j) * 8 + l8;
+                    a_b[j] = -1; a_h[j] = 0; a_w[j] = 0;
+                    if (m < T.Mrows) {
+                        a_b[j] = fdiv(m, T.fd_rows);
+                        const int rem = m - a_b[j] * HW;
+                        a_h[j] = fdiv(rem, T.fd_w); a_w[j] = rem - a_h[j] * p.W;
+                    }
+                }
+            } else if (!SCALAR_A) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int kk = T.m0 + (q * 4 + lq) * 8;
+                    w_kok[q] = kk < T.Mrows;
+                    const int ij = fdiv(kk, T.fd_c), cp = kk - ij * Cs;
+                    const int i = fdiv(ij, T.fd_kw), j = ij - i * p.kw;
+                    w_koff[q] = (i * p.W + j) * Cs + cp;
+                }
+            }
+        };
+        auto load_stage = [&](int stage, int kb) {
+            const TcTile& T = ring[lj % TC_RING];
+            const Prob& p = T.p;
+            const int Cs = p.Cs, Fs = p.Fs, HoWo = p.Ho * p.Wo;
+            const int KK = p.kh * p.kw;
+            const int Kf = SCALAR_A ? KK : KK * Cs, Kd = KK * Fs;
+            const bool dense = KK == 1;
+            const int n0 = T.n0;
+            const uint32_t aS = sA + stage * TC_A_BYTES, bS = sB + stage * B_BYTES;
+            const int Q = BN >> 5;                           // B items per thread = quads of 4 chunks along the major axis
+            if (MODE == TC_FWD) {
+                // A, K-major.  Items (row block 2*warp + j, k chunk h*4 + lq): two rows x two chunks.
+                if (!SCALAR_A) {
+                    int koff[2]; bool kok[2];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int k = kb * TC_BK + (h * 4 + lq) * 8;
+                        kok[h] = k < Kf;
+                        koff[h] = k;
+                        if (!dense) {
+                            const int ij = fdiv(k, T.fd_c), cp = k - ij * Cs;
+                            const int ki = fdiv(ij, T.fd_kw), kj = ij - ki * p.kw;
+                            koff[h] = (ki * p.W + kj) * Cs + cp;
+                        }
+                    }
+#pragma unroll
+                    for (int j = 0; j < 2; ++j)
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            const bool ok = a_row[j] != nullptr && kok[h];
+                            cp_async16_ca(aS + core_off(warp * 2 + j, h * 4 + lq, l8),
+                                          ok ? (const void*)(a_row[j] + koff[h]) : (const void*)p.w, ok);
+                        }
                 } else {
-                    const bool ok = row != nullptr && k < Kf;
-                    const int ij = k / Cs, cp = k - ij * Cs;
-                    const int ki = ij / p.kw, kj = ij - ki * p.kw;
-                    cp_async16_ca(aS + core_off(blk, ch, l8),
-                                  ok ? (const void*)(row + ((long long)ki * p.W + kj) * Cs + cp) : (const void*)p.w, ok);
-                }
-            }
-            // B, MN-major: 8 k blocks x BN/32 quads of n chunks; W rows are [(ij, c)][ldw], pad channels have no row
-            const int Q = BN >> 5;
-            for (int i = 0; i < items_b; ++i) {
-                const int q = warp * items_b + i, blk = q / Q, nch = (q - blk * Q) * 4 + lq;
-                const int k = kb * TC_BK + blk * 8 + l8, n = n0 + nch * 8;
-                long long wrow = k;
-                bool ok = k < Kf && n < p.ldw;
-                if (!SCALAR_A) { const int ij = k / Cs, cp = k - ij * Cs; ok = ok && cp < p.C; wrow = (long long)ij * p.C + cp; }
-                cp_async16(bS + core_off(nch, blk, l8), ok ? (const void*)(p.w + wrow * p.ldw + n) : (const void*)p.w, ok);
-            }
-        } else if (MODE == TC_DGRAD) {
+                    // first layer on a one-channel model input with per-individual inputs: element-wise gather
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int q = warp * 8 + i, blk = q >> 1, ch = (q & 1) * 4 + lq;
-                const int k = kb * TC_BK + ch * 8;
-                const int j = i >> 1;
-                bool ok = a_b[j] >= 0 && k < Kd;
-                const __half* src = p.gout;
-                if (ok) {
-                    const int ij = k / Fs, f = k - ij * Fs;
-                    const int ki = ij / p.kw, kj = ij - ki * p.kw;
-                    const int hh = a_h[j] - ki, ww = a_w[j] - kj;
-                    ok = hh >= 0 && ww >= 0;
-                    if (ok) {
-                        const int ho = hh / p.sh, wo = ww / p.sw;
-                        ok = ho * p.sh == hh && wo * p.sw == ww && ho < p.Ho && wo < p.Wo;
-                        if (ok) src = p.gout + (long long)a_b[j] * p.out_bs + ((long long)ho * p.Wo + wo) * Fs + f;
+                    for (int j = 0; j < 2; ++j)
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            const int k = kb * TC_BK + (h * 4 + lq) * 8;
+                            Half8 v;
+                            int ki = fdiv(k, T.fd_kw), kj = k - ki * p.kw;
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                v.v[e] = (a_row[j] != nullptr && k + e < Kf) ? a_row[j][ki * p.W + kj] : __float2half_rn(0.f);
+                                if (++kj == p.kw) { kj = 0; ++ki; }
+                            }
+                            *reinterpret_cast<Half8*>(sgen + (aS - sbase) + core_off(warp * 2 + j, h * 4 + lq, l8)) = v;
+                        }
+                }
+                // B, MN-major: this warp owns k rows kb*64 + warp*8 .. +7 (one per l8), Q quads of n chunks.
+                // W rows are [(ij, c)][ldw]; pad channels have no row.
+                {
+                    const int k = kb * TC_BK + warp * 8 + l8;
+                    long long wrow = k;
+                    bool kok = k < Kf;
+                    if (SCALAR_A) {}
+                    else if (dense) kok = kok && k < p.C;
+                    else { const int ij = fdiv(k, T.fd_c), cp = k - ij * Cs; kok = kok && cp < p.C; wrow = (long long)ij * p.C + cp; }
+                    const __half* wr = p.w + wrow * p.ldw + n0;
+#pragma unroll 4
+                    for (int i = 0; i < Q; ++i) {
+                        const int nch = i * 4 + lq;
+                        const bool ok = kok && n0 + nch * 8 < p.ldw;
+                        cp_async16(bS + core_off(nch, warp, l8), ok ? (const void*)(wr + nch * 8) : (const void*)p.w, ok);
                     }
                 }
-                cp_async16_ca(aS + core_off(blk, ch, l8), src, ok);
-            }
-            // B, K-major: rows n = input channel c, k = (ij, f) contiguous in f
-            for (int i = 0; i < items_b; ++i) {
-                const int q = warp * items_b + i, blk = q >> 1, ch = (q & 1) * 4 + lq;
-                const int c = n0 + blk * 8 + l8, k = kb * TC_BK + ch * 8;
-                const bool ok = c < p.C && k < Kd;
-                const int ij = k / Fs, f = k - ij * Fs;
-                cp_async16(bS + core_off(blk, ch, l8),
-                           ok ? (const void*)(p.w + ((long long)ij * p.C + c) * p.ldw + f) : (const void*)p.w, ok);
-            }
-        } else {
-            // rows of this k-block: r = r0 + kb*64 + blk*8 + l8, two blocks per thread
-            const __half* in_row[2]; const __half* go_row[2];
+            } else if (MODE == TC_DGRAD) {
+                // k = (ij, f) over the padded filters: two chunks per thread and k-block, decomposed once
+                int kki[2], kkj[2], kf[2]; long long wbase[2]; bool kok[2];
 #pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                const int r = r0 + kb * TC_BK + (warp * 2 + j) * 8 + l8;
-                in_row[j] = nullptr; go_row[j] = nullptr;
-                if (r < r1) {
-                    const int b = r / HoWo, rem = r - b * HoWo;
-                    const int ho = rem / p.Wo, wo = rem - ho * p.Wo;
-                    in_row[j] = in + (long long)b * in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * Cs;
-                    go_row[j] = p.gout + (long long)b * p.out_bs + (long long)rem * Fs;
+                for (int h = 0; h < 2; ++h) {
+                    const int k = kb * TC_BK + (h * 4 + lq) * 8;
+                    kok[h] = k < Kd;
+                    int ij = 0; kf[h] = k; kki[h] = 0; kkj[h] = 0;
+                    if (!dense) { ij = fdiv(k, T.fd_c); kf[h] = k - ij * Fs; kki[h] = fdiv(ij, T.fd_kw); kkj[h] = ij - kki[h] * p.kw; }
+                    wbase[h] = (long long)ij * p.C * p.ldw + kf[h];
                 }
-            }
-            // A, MN-major: 8 row blocks x 4 quads of kk chunks
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int q = warp * 8 + i, blk = q >> 2, qd = q & 3, cc = qd * 4 + lq;
-                const __half* row = (i < 4) ? in_row[0] : in_row[1];
-                if (SCALAR_A) {
-                    Half8 v;
-                    const int kk = m0 + cc * 8;
-                    int ki = kk / p.kw, kj = kk - ki * p.kw;
+                for (int j = 0; j < 2; ++j)
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        v.v[e] = (row != nullptr && kk + e < Kf) ? row[ki * p.W + kj] : __float2half_rn(0.f);
-                        if (++kj == p.kw) { kj = 0; ++ki; }
+                    for (int h = 0; h < 2; ++h) {
+                        bool ok = a_b[j] >= 0 && kok[h];
+                        const __half* src = p.gout;
+                        if (ok) {
+                            const int hh = a_h[j] - kki[h], ww = a_w[j] - kkj[h];
+                            ok = hh >= 0 && ww >= 0;
+                            if (ok) {
+                                // strides are 1 or 2 in practice: shifts for those, a real division otherwise
+                                const int ho = p.sh == 1 ? hh : (p.sh == 2 ? hh >> 1 : hh / p.sh);
+                                const int wo = p.sw == 1 ? ww : (p.sw == 2 ? ww >> 1 : ww / p.sw);
+                                ok = ho * p.sh == hh && wo * p.sw == ww && ho < p.Ho && wo < p.Wo;
+                                if (ok) src = p.gout + (long long)a_b[j] * p.out_bs + (ho * p.Wo + wo) * Fs + kf[h];
+                            }
+                        }
+                        cp_async16_ca(aS + core_off(warp * 2 + j, h * 4 + lq, l8), src, ok);
                     }
-                    *reinterpret_cast<Half8*>(sgen + (aS - sbase) + core_off(cc, blk, l8)) = v;
-                } else {
-                    const bool ok = row != nullptr && w_kok[qd];
-                    cp_async16_ca(aS + core_off(cc, blk, l8), ok ? (const void*)(row + w_koff[qd]) : (const void*)p.w, ok);
+                // B, K-major: rows n = input channel c, k = (ij, f) contiguous in f; items q = warp*Q + i -> (row block q/2, chunk half q%2)
+#pragma unroll 4
+                for (int i = 0; i < Q; ++i) {
+                    const int q = warp * Q + i, blk = q >> 1, h = q & 1;
+                    const int c = n0 + blk * 8 + l8;
+                    const bool ok = c < p.C && kok[h];
+                    cp_async16(bS + core_off(blk, h * 4 + lq, l8),
+                               ok ? (const void*)(p.w + wbase[h] + (long long)c * p.ldw) : (const void*)p.w, ok);
+                }
+            } else {
+                // this warp owns reduction rows r0 + kb*64 + warp*8 .. +7 (one per l8)
+                const int r = T.r0 + kb * TC_BK + warp * 8 + l8;
+                const __half* in_row = nullptr; const __half* go_row = nullptr;
+                if (r < T.r1) {
+                    const int b = fdiv(r, T.fd_rows), rem = r - b * HoWo;
+                    const int ho = fdiv(rem, T.fd_w), wo = rem - ho * p.Wo;
+                    in_row = l_in + (long long)b * l_in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * Cs;
+                    go_row = p.gout + (long long)b * p.out_bs + (long long)rem * Fs;
+                }
+                // A, MN-major: 4 quads of kk chunks
+#pragma unroll
+                for (int qd = 0; qd < 4; ++qd) {
+                    const int cc = qd * 4 + lq;
+                    if (SCALAR_A) {
+                        Half8 v;
+                        const int kk = T.m0 + cc * 8;
+                        int ki = fdiv(kk, T.fd_kw), kj = kk - ki * p.kw;
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            v.v[e] = (in_row != nullptr && kk + e < Kf) ? in_row[ki * p.W + kj] : __float2half_rn(0.f);
+                            if (++kj == p.kw) { kj = 0; ++ki; }
+                        }
+                        *reinterpret_cast<Half8*>(sgen + (aS - sbase) + core_off(cc, warp, l8)) = v;
+                    } else {
+                        const bool ok = in_row != nullptr && w_kok[qd];
+                        cp_async16_ca(aS + core_off(cc, warp, l8), ok ? (const void*)(in_row + w_koff[qd]) : (const void*)p.w, ok);
+                    }
+                }
+                // B, MN-major: Q quads of f chunks
+#pragma unroll 4
+                for (int i = 0; i < Q; ++i) {
+                    const int nch = i * 4 + lq, f = n0 + nch * 8;
+                    const bool ok = go_row != nullptr && f < Fs;
+                    cp_async16(bS + core_off(nch, warp, l8), ok ? (const void*)(go_row + f) : (const void*)p.w, ok);
                 }
             }
-            // B, MN-major: 8 row blocks x BN/32 quads of f chunks
-            const int Q = BN >> 5;
-            for (int i = 0; i < items_b; ++i) {
-                const int q = warp * items_b + i, blk = q / Q, nch = (q - blk * Q) * 4 + lq;
-                const __half* row = (blk - warp * 2) ? go_row[1] : go_row[0];
-                const int f = n0 + nch * 8;
-                const bool ok = row != nullptr && f < Fs;
-                cp_async16(bS + core_off(nch, blk, l8), ok ? (const void*)(row + f) : (const void*)p.w, ok);
+        };
+
+        int p = 0;                       // stream position: k-blocks issued so far
+        for (lj = 0; lj < my_tiles; ++lj) {
+            loader_enter_tile();
+            for (int kb = 0; kb < lnk; ++kb, ++p) {
+                const int sb = p % STAGES;
+                if (p >= STAGES) mbar_wait(sEmpty + sb * 8, (uint32_t)((p / STAGES - 1) & 1));
+                load_stage(sb, kb);
+                cp_async_commit();
+                if (p >= LAG) {          // my copies of k-block p - LAG have landed: publish them to the async proxy
+                    if (LAG == 2) cp_async_wait<2>(); else cp_async_wait<4>();
+                    fence_proxy_async();
+                    mbar_arrive(sFull + ((p - LAG) % STAGES) * 8);
+                }
             }
         }
-    };
-
-    const uint32_t idesc = umma_idesc(MODE == TC_WGRAD ? 1 : 0, MODE == TC_DGRAD ? 0 : 1, n_umma);
-
-    // ---- main loop: fill TC_PF k-blocks ahead, one thread issues the MMAs
-    for (int s = 0; s < TC_PF; ++s) {
-        if (s < nk) load_stage(s, s);
-        cp_async_commit();
-    }
-    for (int kb = 0; kb < nk; ++kb) {
-        const int nxt = kb + TC_PF;
-        if (nxt < nk) {
-            const int sb = nxt % TC_STAGES;
-            if (nxt >= TC_STAGES) mbar_wait(sBar + sb * 8, (uint32_t)((nxt / TC_STAGES - 1) & 1));
-            load_stage(sb, nxt);
-        }
-        cp_async_commit();
-        cp_async_wait<TC_PF>();
+        cp_async_wait<0>();
         fence_proxy_async();
-        __syncthreads();
-        if (tid == 0) {
-            tc_fence_after();
-            const int st = kb % TC_STAGES;
-            const uint32_t aS = sA + st * TC_A_BYTES, bS = sB + st * B_BYTES;
+        for (int q = (p > LAG ? p - LAG : 0); q < p; ++q) mbar_arrive(sFull + (q % STAGES) * 8);
+    } else if (warp == TC_LW) {
+        // =================================================================== MMA issuer
+        if (lane == 0) {
+            int p = 0;
+            for (int j = 0; j < my_tiles; ++j) {
+                const int acc = j & 1;
+                if (j >= 2) mbar_wait_relaxed(sTEmpty + acc * 8, (uint32_t)((j / 2 - 1) & 1));   // epilogue drained this accumulator
+                const uint32_t tacc = tmem + (uint32_t)(acc * acc_cols);
+                int nk = 1; uint32_t idesc = 0;
+                for (int kb = 0; kb < nk; ++kb, ++p) {
+                    const int st = p % STAGES;
+                    mbar_wait(sFull + st * 8, (uint32_t)((p / STAGES) & 1));
+                    tc_fence_after();
+                    if (kb == 0) {       // the descriptor was fetched by the loaders long before this stage was published
+                        const TcTile& T = ring[j % TC_RING];
+                        nk = T.nk;
+                        idesc = umma_idesc(MODE == TC_WGRAD ? 1 : 0, MODE == TC_DGRAD ? 0 : 1, T.n_umma);
+                    }
+                    const uint32_t aS = sA + st * TC_A_BYTES, bS = sB + st * B_BYTES;
 #pragma unroll
-            for (int ks = 0; ks < TC_BK / 16; ++ks)
-                umma_f16(tmem, umma_desc(aS + ks * 256), umma_desc(bS + ks * 256), idesc, (kb | ks) ? 1u : 0u);
-            umma_commit(sBar + st * 8);
-            if (kb == nk - 1) umma_commit(sBar + TC_STAGES * 8);
-        }
-    }
-    mbar_wait(sBar + TC_STAGES * 8, 0);
-    tc_fence_after();
-
-    // ---- epilogue: this thread owns accumulator row (warp * 32 + lane); whole 8-channel chunks are written,
-    //      pad channels as zero
-    const int mrow = m0 + warp * 32 + lane;
-    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
-    if (MODE == TC_FWD) {
-        __half* orow = nullptr;
-        if (mrow < Mrows) {
-            const int b = mrow / HoWo, rem = mrow - b * HoWo;
-            orow = p.out + (long long)b * p.out_bs + (long long)rem * Fs;
-        }
-        for (int cb = 0; cb < n_umma; cb += 16) {
-            float v[16];
-            tmem_ld16(trow + cb, v);
-            if (!orow) continue;
-#pragma unroll
-            for (int h8 = 0; h8 < 2; ++h8) {
-                const int n = n0 + cb + h8 * 8;
-                if (n >= Ncols) break;
-                Half8 o;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    float z = 0.f;
-                    if (n + j < Ncols) z = act_forward(rh(rh(v[h8 * 8 + j]) + __half2float(p.bias[n + j])), p.act);
-                    o.v[j] = __float2half_rn(z);
+                    for (int ks = 0; ks < TC_BK / 16; ++ks)
+                        umma_f16(tacc, umma_desc(aS + ks * 256), umma_desc(bS + ks * 256), idesc, (kb | ks) ? 1u : 0u);
+                    umma_commit(sEmpty + st * 8);
                 }
-                st8(orow + n, o);
-            }
-        }
-    } else if (MODE == TC_DGRAD) {
-        __half* drow = nullptr;
-        if (mrow < Mrows) {
-            const int b = mrow / HW, rem = mrow - b * HW;
-            drow = p.din + (long long)b * p.in_bs + (long long)rem * Cs;
-        }
-        for (int cb = 0; cb < n_umma; cb += 16) {
-            float v[16];
-            tmem_ld16(trow + cb, v);
-            if (!drow) continue;
-#pragma unroll
-            for (int h8 = 0; h8 < 2; ++h8) {
-                const int c = n0 + cb + h8 * 8;
-                if (c >= Ncols) break;
-                Half8 o;
-                if (p.din_acc) o = ld8(drow + c);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    float x = (c + j < Ncols) ? v[h8 * 8 + j] : 0.f;
-                    if (p.din_acc) x = rh(x) + __half2float(o.v[j]);
-                    o.v[j] = __float2half_rn(x);
-                }
-                st8(drow + c, o);
+                umma_commit(sTFull + acc * 8);
             }
         }
     } else {
-        // accumulator row = kk = (ij, padded c): rows of pad channels have no weight row
-        float* grow = nullptr;
-        if (mrow < Kf) {
-            if (SCALAR_A) grow = p.gw + (long long)mrow * p.ldw;
-            else { const int ij = mrow / Cs, cp = mrow - ij * Cs; if (cp < p.C) grow = p.gw + ((long long)ij * p.C + cp) * p.ldw; }
-        }
-        const bool single = (nb * HoWo) <= TC_WGRAD_ROWS;     // one split: plain stores, else fp32 atomics
-        for (int cb = 0; cb < n_umma; cb += 16) {
-            float v[16];
-            tmem_ld16(trow + cb, v);
-            if (!grow) continue;
+        // =================================================================== epilogue (4 warps)
+        const int ewarp = warp & 3;      // TMEM lanes 32 * ewarp .. + 31
+        auto epilogue = [&](const TcTile& T, uint32_t tacc, int ewarp) {
+            const Prob& p = T.p;
+            const int Cs = p.Cs, Fs = p.Fs;
+            const int mrow = T.m0 + ewarp * 32 + lane, n0 = T.n0, Ncols = T.Ncols;
+            const uint32_t trow = tacc + ((uint32_t)(ewarp * 32) << 16);
+            if (MODE == TC_FWD) {
+                const int HoWo = p.Ho * p.Wo;
+                __half* orow = nullptr;
+                if (mrow < T.Mrows) {
+                    const int b = fdiv(mrow, T.fd_rows), rem = mrow - b * HoWo;
+                    orow = p.out + (long long)b * p.out_bs + (long long)rem * Fs;
+                }
+                for (int cb = 0; cb < T.n_umma; cb += 16) {
+                    float v[16];
+                    tmem_ld16(trow + cb, v);
+                    if (!orow) continue;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const int f = n0 + cb + j;
-                if (f < Ncols) {
-                    if (single) grow[f] = v[j];
-                    else if (v[j] != 0.f) atomicAdd(&grow[f], v[j]);
+                    for (int h8 = 0; h8 < 2; ++h8) {
+                        const int n = n0 + cb + h8 * 8;
+                        if (n >= Ncols) break;
+                        Half8 o;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            float z = 0.f;
+                            if (n + j < Ncols) z = act_forward(rh(rh(v[h8 * 8 + j]) + __half2float(p.bias[n + j])), p.act);
+                            o.v[j] = __float2half_rn(z);
+                        }
+                        st8(orow + n, o);
+                    }
+                }
+            } else if (MODE == TC_DGRAD) {
+                const int HW = p.H * p.W;
+                __half* drow = nullptr;
+                if (mrow < T.Mrows) {
+                    const int b = fdiv(mrow, T.fd_rows), rem = mrow - b * HW;
+                    drow = p.din + (long long)b * p.in_bs + (long long)rem * Cs;
+                }
+                for (int cb = 0; cb < T.n_umma; cb += 16) {
+                    float v[16];
+                    tmem_ld16(trow + cb, v);
+                    if (!drow) continue;
+#pragma unroll
+                    for (int h8 = 0; h8 < 2; ++h8) {
+                        const int c = n0 + cb + h8 * 8;
+                        if (c >= Ncols) break;
+                        Half8 o;
+                        if (p.din_acc) o = ld8(drow + c);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            float x = (c + j < Ncols) ? v[h8 * 8 + j] : 0.f;
+                            if (p.din_acc) x = rh(x) + __half2float(o.v[j]);
+                            o.v[j] = __float2half_rn(x);
+                        }
+                        st8(drow + c, o);
+                    }
+                }
+            } else {
+                // accumulator row = kk = (ij, padded c): rows of pad channels have no weight row
+                float* grow = nullptr;
+                if (mrow < T.Mrows) {
+                    if (SCALAR_A) grow = p.gw + (long long)mrow * p.ldw;
+                    else { const int ij = fdiv(mrow, T.fd_c), cp = mrow - ij * Cs; if (cp < p.C) grow = p.gw + ((long long)ij * p.C + cp) * p.ldw; }
+                }
+                const bool single = (nb * p.Ho * p.Wo) <= TC_WGRAD_ROWS;     // one split: plain stores, else fp32 atomics
+                for (int cb = 0; cb < T.n_umma; cb += 16) {
+                    float v[16];
+                    tmem_ld16(trow + cb, v);
+                    if (!grow) continue;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const int f = n0 + cb + j;
+                        if (f < Ncols) {
+                            if (single) grow[f] = v[j];
+                            else if (v[j] != 0.f) atomicAdd(&grow[f], v[j]);
+                        }
+                    }
                 }
             }
+        };
+        for (int j = 0; j < my_tiles; ++j) {
+            const int acc = j & 1;
+            mbar_wait_relaxed(sTFull + acc * 8, (uint32_t)((j / 2) & 1));
+            tc_fence_after();
+            epilogue(ring[j % TC_RING], tmem + (uint32_t)(acc * acc_cols), ewarp);
+            tc_fence_before();
+            mbar_arrive(sTEmpty + acc * 8);
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, (uint32_t)tmem_cols);
+    if (warp == TC_LW) tmem_dealloc(tmem, (uint32_t)tmem_cols);
 }
 
 }  // namespace srn

@@ -466,7 +466,12 @@ k_maxpool_bwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
 // ------------------------------------------------------------------ copy: concatenate (last axis) and non-view reshape
 // The source's n_el real elements per sample, in row-major (row, channel) order, fill rows of Cj channels at
 // channel offset coff of the destination.  fwd: out <- in;  bwd: din (+)= gout.
-__host__ __device__ inline int copy_blocks(long long elems) { return (int)((elems + EW_PER_CTA * 2 - 1) / (EW_PER_CTA * 2)); }
+// 16-byte path when source rows, destination rows and the channel offset are all multiples of 8 channels
+__host__ __device__ inline bool copy_vec(const Prob& p) { return p.C % 8 == 0 && p.Cj % 8 == 0 && p.coff % 8 == 0 && p.Cs % 8 == 0 && p.Fs % 8 == 0; }
+__host__ __device__ inline int copy_blocks(const Prob& p, int nb) {
+    const long long units = (long long)nb * (copy_vec(p) ? p.n_el / 8 : p.n_el);
+    return (int)((units + EW_PER_CTA - 1) / EW_PER_CTA);
+}
 
 static __global__ void __launch_bounds__(EW_THREADS)
 k_copy(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, Inputs I, int bwd) {
@@ -474,27 +479,71 @@ k_copy(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob
     const Prob p = probs[pi];
     if (bwd && p.din == nullptr) return;
     const int blk = blockIdx.x - prefix[pi];
-    const long long total = (long long)nb * p.n_el;
+    const bool vec = copy_vec(p);
+    const int cw = vec ? 8 : 1;
+    const int per = p.n_el / cw;                       // units per sample
+    const long long total = (long long)nb * per;
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
-    long long e = (long long)blk * (EW_PER_CTA * 2) + threadIdx.x;
+    long long u = (long long)blk * EW_PER_CTA + threadIdx.x;
 #pragma unroll
-    for (int i = 0; i < EW_PER_THREAD * 2; ++i, e += EW_THREADS) {
-        if (e >= total) break;
-        const long long b = e / p.n_el; const int ee = (int)(e - b * p.n_el);
+    for (int i = 0; i < EW_PER_THREAD; ++i, u += EW_THREADS) {
+        if (u >= total) break;
+        const long long b = u / per; const int ee = (int)(u - b * per) * cw;
         const int sr = ee / p.C, sc = ee - sr * p.C;
         const int dr = ee / p.Cj, dc = ee - dr * p.Cj;
         const long long so = b * in_bs + (long long)sr * p.Cs + sc;
         const long long dd = b * p.out_bs + (long long)dr * p.Fs + p.coff + dc;
         if (!bwd) {
-            p.out[dd] = in[so];
+            if (vec) st8(p.out + dd, ld8(in + so));
+            else p.out[dd] = in[so];
         } else {
             const long long go = b * p.in_bs + (long long)sr * p.Cs + sc;
-            float g = __half2float(p.gout[dd]);
-            if (p.din_acc) g += __half2float(p.din[go]);
-            p.din[go] = __float2half_rn(g);
+            if (vec) {
+                Half8 g = ld8(p.gout + dd);
+                if (p.din_acc) {
+                    const Half8 o = ld8(p.din + go);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) g.v[j] = __float2half_rn(__half2float(g.v[j]) + __half2float(o.v[j]));
+                }
+                st8(p.din + go, g);
+            } else {
+                float g = __half2float(p.gout[dd]);
+                if (p.din_acc) g += __half2float(p.din[go]);
+                p.din[go] = __float2half_rn(g);
+            }
         }
     }
+}
+
+// ------------------------------------------------------------------ shared im2col of a one-channel model input
+// In training and evaluation every individual sees the same image / genotype batch, so the patch matrix of a
+// first layer depends only on its window geometry: it is written once per batch and geometry as
+// [sample][position][Kp] (Kp = kh*kw rounded up to 8, pad zero) and every first layer with that geometry becomes a
+// plain Dense over it on the vectorised tensor-core path.
+struct Im2colGeo {
+    const __half* in; __half* out;
+    int in_bs, H, W, kh, kw, sh, sw, Ho, Wo, KK, Kp;
+};
+
+static __global__ void __launch_bounds__(256)
+k_im2col(Im2colGeo g, int nb) {
+    const int nq = g.Kp >> 3, HoWo = g.Ho * g.Wo;
+    const long long total = (long long)nb * HoWo * nq;
+    long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= total) return;
+    const long long pos = q / nq; const int k0 = (int)(q - pos * nq) * 8;
+    const long long b = pos / HoWo; const int rem = (int)(pos - b * HoWo);
+    const int ho = rem / g.Wo, wo = rem - ho * g.Wo;
+    const __half* src = g.in + b * g.in_bs + (long long)(ho * g.sh) * g.W + wo * g.sw;
+    Half8 v;
+    int ki = k0 / g.kw, kj = k0 - ki * g.kw;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        v.v[e] = (k0 + e < g.KK) ? src[ki * g.W + kj] : __float2half_rn(0.f);
+        if (++kj == g.kw) { kj = 0; ++ki; }
+    }
+    st8(g.out + pos * g.Kp + k0, v);
 }
 
 // ------------------------------------------------------------------ fused losses
