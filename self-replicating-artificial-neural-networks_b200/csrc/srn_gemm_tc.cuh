@@ -12,8 +12,8 @@
 // The kernel is persistent and warp-specialised.  A CTA walks its share of a host-built table of 256-byte tile
 // descriptors (sorted by cost, dealt out in snake order, prefetched four tiles ahead) and treats the k-blocks
 // of its tiles as one stream:
-//   warps 0-7  loaders: gather k-block p into ring stage p % 4 (cp.async), and once their own copies of
-//              k-block p - 3 have landed (wait_group + fence.proxy.async) arrive on that stage's "full" barrier;
+//   warps 0-7  loaders: gather k-block p into ring stage p % S with cp.async; each thread's copies arrive on the
+//              stage's "full" barrier by themselves when they land (cp.async.mbarrier.arrive.noinc);
 //   warp 8     one thread waits "full", issues four K=16 tcgen05.mma into one of two TMEM accumulators and
 //              commits to the stage's "empty" barrier (and to "tmem_full" after a tile's last k-block);
 //   warps 9-12 epilogue: wait "tmem_full", read the accumulator with tcgen05.ld (warp w owns TMEM lanes
@@ -41,13 +41,12 @@ constexpr int TC_WGRAD_ROWS = 4096;   // reduction rows per wgrad CTA (64 k-bloc
 
 enum { TC_FWD = 0, TC_DGRAD = 1, TC_WGRAD = 2 };
 
-constexpr int TC_RING = 16;           // tile descriptors in shared memory: epilogue <= 6 tiles behind the loader, prefetch 4 ahead
+constexpr int TC_RING = 32;           // tile descriptors in shared memory: epilogue <= 10 tiles behind the loader, 4 ahead
 constexpr int TC_DESC_AHEAD = 4;
 // Pipeline depth per N tile: BN <= 64 keeps two CTAs per SM (4 stages each), wider tiles take the SM alone with as
-// many stages as fit.  A loader publishes k-block p - lag after issuing k-block p (lag + 1 k-blocks of loads in
-// flight per thread); stages - lag - 1 >= 1 further stages decouple the loaders from the MMA completion latency.
-__host__ __device__ inline int tc_stages(int BN) { return BN <= 64 ? 4 : (BN <= 128 ? 6 : 4); }
-__host__ __device__ inline int tc_lag(int BN) { return BN <= 64 ? 2 : (BN <= 128 ? 4 : 2); }
+// many stages as fit.  Loaders never wait for their own copies: completion is signalled to the stage's "full"
+// barrier by the copy engine itself (cp.async.mbarrier.arrive.noinc), so up to `stages` k-blocks are in flight.
+__host__ __device__ inline int tc_stages(int BN) { return BN <= 64 ? 4 : (BN <= 128 ? 3 : 4); }
 __host__ __device__ inline int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + BN * TC_BK * 2) + 256 + TC_RING * 256; }
 __host__ __device__ inline int tc_acc_cols(int BN) { return BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256)); }
 __host__ __device__ inline int tc_tmem_cols(int BN) { return 2 * tc_acc_cols(BN); }     // two accumulators
@@ -78,7 +77,12 @@ __device__ __forceinline__ void cp_async16_ca(uint32_t dst, const void* src, boo
     const int sz = valid ? 16 : 0;
     asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(src), "r"(sz) : "memory");
 }
+// arrive on an mbarrier once all cp.async issued so far by this thread have landed (no wait in the thread)
+__device__ __forceinline__ void cp_async_arrive_noinc(uint32_t bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];\n" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
@@ -242,7 +246,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
     const uint32_t sbase = (sraw + 127u) & ~127u;
     unsigned char* sgen = smem_raw + (sbase - sraw);      // generic pointer to the same place as sbase
     const uint32_t B_BYTES = (uint32_t)BN * TC_BK * 2;
-    const int STAGES = tc_stages(BN), LAG = tc_lag(BN);
+    const int STAGES = tc_stages(BN);
     const uint32_t sA = sbase, sB = sbase + STAGES * TC_A_BYTES;
     const uint32_t sRing = sB + STAGES * B_BYTES;         // TC_RING tile descriptors of 256 bytes
     const uint32_t sFull = sRing + TC_RING * 256;         // barriers: full[S], empty[S], tmem_full[2], tmem_empty[2]
@@ -257,11 +261,15 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
     const int G = gridDim.x, cta = blockIdx.x;
     int my_tiles = ntiles / G;                                      // full rounds, plus maybe one of the last round
     if (tc_tile_index(cta, my_tiles, G) < ntiles) ++my_tiles;
-    // 256-byte descriptor of this CTA's j-th tile -> ring slot j % TC_RING (16 loader threads x 16 bytes)
-    auto fetch_desc = [&](int j) {
+    // 256-byte descriptors travel global -> registers (one tile early) -> ring slot j % TC_RING, 16 bytes per thread
+    // of the first half-warp; the load of the next one is in flight while the current tile is being gathered
+    uint4 dreg = make_uint4(0, 0, 0, 0);
+    auto desc_load = [&](int j) {
         if (j < my_tiles && tid < 16)
-            cp_async16(sRing + (j % TC_RING) * 256 + tid * 16,
-                       reinterpret_cast<const unsigned char*>(table + tc_tile_index(cta, j, G)) + tid * 16, true);
+            dreg = __ldg(reinterpret_cast<const uint4*>(table + tc_tile_index(cta, j, G)) + tid);
+    };
+    auto desc_store = [&](int j) {
+        if (j < my_tiles && tid < 16) reinterpret_cast<uint4*>(ring + (j % TC_RING))[tid] = dreg;
     };
 
     if (tid == 0) {
@@ -270,11 +278,8 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
     }
     if (warp == TC_LW) tmem_alloc(sSlot, (uint32_t)tmem_cols);
-    if (warp < TC_LW) {
-        for (int j = 0; j < TC_DESC_AHEAD; ++j) fetch_desc(j);
-        cp_async_commit();
-        cp_async_wait<0>();
-    }
+    for (int j = 0; j < TC_DESC_AHEAD; ++j) { desc_load(j); desc_store(j); }
+    desc_load(TC_DESC_AHEAD);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -290,9 +295,10 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
         int w_koff[4]; bool w_kok[4];    // WGRAD (vector): offsets of this thread's four kk chunks inside the window
         int lj = 0, lnk = 0;
         auto loader_enter_tile = [&]() {
-            loaders_sync();                 // the 16 fetching threads have completed this descriptor's copy long ago
+            loaders_sync();                 // descriptor lj was stored before the previous loaders_sync
             const TcTile& T = ring[lj % TC_RING];
-            fetch_desc(lj + TC_DESC_AHEAD);
+            desc_store(lj + TC_DESC_AHEAD);
+            desc_load(lj + TC_DESC_AHEAD + 1);
             const Prob& p = T.p;
             l_in = resolve_in(p, I, l_in_bs);
             lnk = T.nk;
@@ -482,17 +488,11 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                 const int sb = p % STAGES;
                 if (p >= STAGES) mbar_wait(sEmpty + sb * 8, (uint32_t)((p / STAGES - 1) & 1));
                 load_stage(sb, kb);
-                cp_async_commit();
-                if (p >= LAG) {          // my copies of k-block p - LAG have landed: publish them to the async proxy
-                    if (LAG == 2) cp_async_wait<2>(); else cp_async_wait<4>();
-                    fence_proxy_async();
-                    mbar_arrive(sFull + ((p - LAG) % STAGES) * 8);
-                }
+                if (SCALAR_A) fence_proxy_async();       // the element-wise gather used ordinary shared-memory stores
+                cp_async_arrive_noinc(sFull + sb * 8);   // fires when this thread's copies for the stage have landed
             }
         }
-        cp_async_wait<0>();
-        fence_proxy_async();
-        for (int q = (p > LAG ? p - LAG : 0); q < p; ++q) mbar_arrive(sFull + (q % STAGES) * 8);
+        cp_async_wait_all();
     } else if (warp == TC_LW) {
         // =================================================================== MMA issuer
         if (lane == 0) {
@@ -505,6 +505,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                 for (int kb = 0; kb < nk; ++kb, ++p) {
                     const int st = p % STAGES;
                     mbar_wait(sFull + st * 8, (uint32_t)((p / STAGES) & 1));
+                    fence_proxy_async();     // the stage was written through the generic proxy (cp.async), UMMA reads it through the async proxy
                     tc_fence_after();
                     if (kb == 0) {       // the descriptor was fetched by the loaders long before this stage was published
                         const TcTile& T = ring[j % TC_RING];
