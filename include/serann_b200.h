@@ -177,6 +177,10 @@ int srn_decoder_decode(srn_decoder* d, const uint8_t* bits, int32_t n, int32_t* 
 int srn_readout(int32_t device, const uint16_t* probs, const uint8_t* parent_bits, int32_t rows,
                 int32_t rows_per_parent, int32_t G, uint32_t* packed_bits, int32_t* mutations);
 
+/* Levenshtein distance of two byte strings (host code; replaces edlib.align(a, b)['editDistance'],
+ * evolutionary_experiment/logic/experiment.py:16-17).  Returns -1 on a bad argument. */
+int32_t srn_levenshtein(const char* a, int32_t la, const char* b, int32_t lb);
+
 /* Stand-alone BatchNormalizationF16 training-mode forward on a channel-last fp16 tensor [rows][C]
  * (common/BatchNormalizationF16.py:130-153).  params = gamma, beta, moving_mean, moving_variance
  * (each [C], fp16); moving statistics are updated in place; y [rows][C]. */

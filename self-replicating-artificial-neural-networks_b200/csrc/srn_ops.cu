@@ -185,6 +185,27 @@ extern "C" int srn_decoder_decode(srn_decoder* d, const uint8_t* bits, int32_t n
     return SRN_OK;
 }
 
+// ------------------------------------------------------------------ edit distance (host)
+// Levenshtein distance between two byte strings, two-row dynamic programme.  Replaces edlib.align(a, b)['editDistance']
+// (reference evolutionary_experiment/logic/experiment.py:16-17), which is not installable here.
+extern "C" int32_t srn_levenshtein(const char* a, int32_t la, const char* b, int32_t lb) {
+    if (la < 0 || lb < 0 || (!a && la) || (!b && lb)) return -1;
+    if (la < lb) { std::swap(a, b); std::swap(la, lb); }
+    if (lb == 0) return la;
+    std::vector<int32_t> prev(lb + 1), cur(lb + 1);
+    for (int j = 0; j <= lb; ++j) prev[j] = j;
+    for (int i = 1; i <= la; ++i) {
+        cur[0] = i;
+        const char ca = a[i - 1];
+        for (int j = 1; j <= lb; ++j) {
+            const int32_t sub = prev[j - 1] + (ca != b[j - 1]);
+            cur[j] = std::min(sub, std::min(prev[j], cur[j - 1]) + 1);
+        }
+        prev.swap(cur);
+    }
+    return prev[lb];
+}
+
 // ------------------------------------------------------------------ stand-alone readout
 extern "C" int srn_readout(int32_t device, const uint16_t* probs, const uint8_t* parent_bits, int32_t rows,
                            int32_t rows_per_parent, int32_t G, uint32_t* packed_bits, int32_t* mutations) {

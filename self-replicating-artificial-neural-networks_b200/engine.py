@@ -80,6 +80,8 @@ def load_library(rebuild: bool = False) -> C.CDLL:
     lib.srn_readout.argtypes = [i32, vp, vp, i32, i32, i32, vp, vp]
     lib.srn_bn_train_forward.argtypes = [i32, vp, i64, i32, vp, vp, vp, vp, vp]
     lib.srn_bn_train_forward_noalloc.argtypes = [i32, vp, vp, i64, i32, vp, vp, vp, vp, vp]
+    lib.srn_levenshtein.argtypes = [C.c_char_p, i32, C.c_char_p, i32]
+    lib.srn_levenshtein.restype = i32
     lib.srn_set_tensor_cores.argtypes = [i32]
     lib.srn_profile.argtypes = [vp, i32]
     lib.srn_profile_read.argtypes = [vp, vp, vp]
@@ -313,6 +315,12 @@ class Engine:
 
     def launch_groups(self) -> int:
         return int(self._lib.srn_debug_launch_groups(self._h))
+
+
+def levenshtein(a: str, b: str) -> int:
+    """Edit distance of two strings (reference ``experiment.py:16-17`` via edlib)."""
+    ab, bb = a.encode(), b.encode()
+    return int(load_library().srn_levenshtein(ab, len(ab), bb, len(bb)))
 
 
 def unpack_bits(packed: np.ndarray, G: int) -> np.ndarray:

@@ -1,0 +1,282 @@
+"""Evolution loop around the B200 worker: one generation = evaluate -> fertility -> offspring counts ->
+statistics -> store -> select -> decode.
+
+Host-side restatement of the reference driver ``Experiment``
+(``evolutionary_experiment/logic/experiment.py``) on current pandas / NumPy (the reference uses
+``DataFrame.append``, ``Series.iteritems`` and ``np.NaN``, which are gone).  The random draws keep the
+reference's order on the legacy ``np.random`` stream seeded by the CLI (``run_experiment.py:55``):
+first-generation sampling, one multinomial per generation, then per parent one permutation for the
+offspring choice and one for proof-reading.
+"""
+from __future__ import annotations
+
+from datetime import datetime
+from typing import Dict, Optional
+from uuid import uuid4
+
+import numpy as np
+import pandas as pd
+
+from .engine import levenshtein
+from .frontend import extract_layer_counts
+from .parallel import reference_batches
+
+MAX_SERANN_PER_GPU = 112        # reference evolutionary_experiment/config.py:8
+
+
+def hamming(a, b, *args, **kwargs):
+    return np.not_equal(a, b).sum(axis=-1) / np.shape(a)[-1]
+
+
+def pairwise_genotype_distances(genotypes: np.ndarray):
+    """Mean pairwise Euclidean / Hamming distance and the cdist Hamming sum ("nucleotide diversity").
+
+    The reference calls ``pdist`` / ``cdist`` with a Python metric, ~1.5 M interpreter calls per generation at
+    population 1000 (``experiment.py:246-251``).  For 0/1 genotypes both metrics are functions of the number
+    of differing loci, which one Gram matrix gives for all pairs at once; non-binary or NaN genotypes fall
+    back to broadcasting.
+    """
+    g = np.asarray(genotypes, dtype=np.float64)
+    n, L = g.shape
+    if n < 2:
+        return float('nan'), float('nan'), 0.0
+    if np.isin(g, (0.0, 1.0)).all():
+        ones = g.sum(axis=1)
+        diff = ones[:, None] + ones[None, :] - 2.0 * (g @ g.T)          # differing loci per pair
+        iu = np.triu_indices(n, 1)
+        return float(np.sqrt(diff[iu]).mean()), float((diff[iu] / L).mean()), float(diff.sum() / L)
+    d2 = ((g[:, None, :] - g[None, :, :]) ** 2).sum(-1)
+    ne = (g[:, None, :] != g[None, :, :]).sum(-1) / L
+    iu = np.triu_indices(n, 1)
+    return float(np.sqrt(d2[iu]).mean()), float(ne[iu].mean()), float(ne.sum())
+
+
+class Experiment:
+    def __init__(self, experiment_id, serann_dataset, workers_pool, experiment_db, parameters, genetic_encoder,
+                 start_generation: int = 0, population_source=None):
+        """``genetic_encoder``: a ``RibosomalAutoencoder`` (reference builds it itself from config paths,
+        ``experiment.py:36``).  ``population_source``: optional callable ``(n) -> list of source strings``; when
+        given, the next generation's *source codes* come from it instead of from the decoder - needed with a
+        random-init autoencoder, whose decodes are not valid programs.  The offspring
+        genotypes are still produced, selected and decoded."""
+        self._experiment_db = experiment_db
+        self._parameters = parameters
+        self._serann_dataset = serann_dataset
+        self._id = experiment_id
+        self._start_generation = start_generation
+        self._genetic_encoder = genetic_encoder
+        self._population_source = population_source
+        self._experiment_db.save_execution_info(datetime.now(), self._parameters)
+        self._workers_pool = workers_pool
+        self.generation_seconds = []
+
+    # ------------------------------------------------------------------ main loop (experiment.py:43-108)
+    def execute(self):
+        p = self._parameters
+        print(f'Experiment {self._id} has started')
+        print(f'Using {self._workers_pool.get_workers_count()} GPU workers')
+        current = self._get_first_generation()
+        offspring_pool_size = p['initial_offspring_pool_size']
+        print('Initial offspring pool size:', offspring_pool_size)
+        for generation in range(self._start_generation, p['num_generations']):
+            t0 = datetime.now()
+            print(f'### Generation {generation} execution has started ###')
+            current['experiment_id'] = self._id
+            current['generation'] = generation
+            current['num_offspring'] = 0
+            print('Starting training and replication')
+            models_info, offspring_by_id, times = self._learn_and_replicate(current, offspring_pool_size)
+            current = current.join(models_info)
+            print('Calculating fecundity scores')
+            current['absolute_fertility'], current['relative_fertility'] = \
+                self._get_fertility(current['classification_validation_accuracy'])
+            print('Sampling offspring counts')
+            if current['is_valid'].sum() > 0:
+                current['num_offspring'] = np.random.multinomial(p['num_seranns'], current['relative_fertility'])
+            survived = current['is_valid'].astype(bool) & ~current['is_overweight'].astype(bool)
+            valid = current[survived]
+            print('Extracting source codes statistics')
+            counts = pd.DataFrame([extract_layer_counts(s) for s in valid['source_code']], index=valid.index)
+            current = current.join(counts, how='left')
+            print('Saving generation information to the experiment DB')
+            self._report_generation_statistics(current, generation, times, t0)
+            print('Saving SeRANN records to the experiment DB')
+            self._experiment_db.save_seranns_info(current)
+            if len(valid) == 0:
+                print('No valid SeRANNs left! stopping...')
+                break
+            print('Applying offspring selection')
+            nxt = self._select_offspring(current, offspring_by_id)
+            print(f'Generation {generation} execution is done')
+            offspring_pool_size = int(current['num_offspring'].max() * p['offspring_pool_size_factor'])
+            print('Offspring pool size was updated to:', offspring_pool_size)
+            current = nxt
+            dt = datetime.now() - t0
+            self.generation_seconds.append(dt.total_seconds())
+            s = int(dt.total_seconds())
+            print(f'\033[1mGeneration execution time: {s // 3600:02d}:{(s // 60) % 60:02d}:{s % 60:02d}\033[0m')
+        return current
+
+    # ------------------------------------------------------------------ fertility (experiment.py:110-117)
+    def _get_fertility(self, accuracy: pd.Series):
+        absolute = accuracy ** self._parameters['selection_pressure']
+        with np.errstate(all='ignore'):
+            relative = np.nan_to_num(absolute / np.sum(absolute))
+            relative = relative / relative.sum()
+        return absolute, relative
+
+    # ------------------------------------------------------------------ generations (experiment.py:119-160)
+    def _load_last_generation_from_db(self):
+        last = self._experiment_db.get_serann_by_generation(self._start_generation - 1)
+        print('Replicating the last generation')
+        ok = (last['is_valid'] == True) & (last['is_overweight'] == False)   # noqa: E712
+        if ok.sum() == 0 or last[ok]['num_offspring'].sum() == 0:
+            raise Exception('No valid SeRANNs left in the last generation!')
+        print('Retraining and replicating the last generation')
+        pool = self._parameters['initial_offspring_pool_size']
+        _, offspring_by_id, _ = self._learn_and_replicate(last, pool)
+        return self._select_offspring(last, offspring_by_id)
+
+    def _get_first_generation(self):
+        if self._start_generation > 0:
+            return self._load_last_generation_from_db()
+        p = self._parameters
+        ancestor = p.get('ancestor_genotype')
+        if ancestor is None:
+            sample = np.random.randint(0, len(self._serann_dataset), p['num_seranns'])
+            by_id = {str(uuid4()): self._serann_dataset[s] for s in sample}
+        else:
+            ancestor = np.array(ancestor)
+            by_id = {str(uuid4()): ancestor for _ in range(p['num_seranns'])}
+        gen = pd.Series(by_id).rename('genotype').rename_axis('id').to_frame()
+        genotypes = np.array(gen['genotype'].values.tolist())
+        gen['source_code'] = self._sources_for(genotypes)
+        gen['parent_id'] = None
+        for c in ('genotype_euclidean_distance_from_parent', 'genotype_hamming_distance_from_parent',
+                  'source_code_levenshtein_distance_from_parent'):
+            gen[c] = np.nan
+        return gen
+
+    def _sources_for(self, genotypes: np.ndarray):
+        decoded = self._genetic_encoder.decode_to_string(genotypes)
+        if self._population_source is None:
+            return decoded
+        return list(self._population_source(len(genotypes)))
+
+    # ------------------------------------------------------------------ evaluation (experiment.py:162-190)
+    def _learn_and_replicate(self, generation: pd.DataFrame, num_offspring):
+        times: Dict[str, list] = {}
+        infos, offspring_by_id = [], {}
+        workers = self._workers_pool.get_workers_count()
+        batch_index = reference_batches(len(generation), workers, MAX_SERANN_PER_GPU)
+        batch_by_id = pd.Series(batch_index, index=generation.index).astype(int)
+        total = batch_by_id.nunique()
+        jobs = [{'args': [data, num_offspring]} for _, data in generation.groupby(batch_by_id)]
+        for i, result in enumerate(self._workers_pool.imap_unordered(jobs), 1):
+            print(f'{i} of {total} batches completed')
+            infos.append(result['models_info'])
+            offspring_by_id.update(result.get('offspring_by_id', {}))
+            times.setdefault('learning_times', []).append(result['learning_time'])
+            times.setdefault('replication_times', []).append(result['replication_time'])
+        return pd.concat(infos), offspring_by_id, times
+
+    # ------------------------------------------------------------------ selection (experiment.py:192-238, 305-321)
+    def _select_offspring(self, generation: pd.DataFrame, offspring_by_id: dict):
+        p = self._parameters
+        strategy = {'random': self._random_offspring_selection, 'best': self._best_offspring_selection} \
+            .get(p['offspring_selection_strategy'])
+        if strategy is None:
+            raise Exception('Unknown offspring selection strategy')
+        ids, parents, genotypes = [], [], []
+        for parent_id, probs in offspring_by_id.items():
+            parent_genotype = np.asarray(generation.loc[parent_id, 'genotype'])
+            n = int(generation.loc[parent_id, 'num_offspring'])
+            bits = np.round(np.clip(probs, 0, 1))                     # experiment.py:210
+            chosen = strategy(parent_genotype, n, bits)
+            chosen = self._probabilistic_proofreading(parent_genotype, chosen)
+            ids += [str(uuid4()) for _ in range(n)]
+            parents += [parent_id] * n
+            genotypes += list(chosen)
+        offspring = np.array(genotypes)
+        sources = self._sources_for(offspring) if len(offspring) else []
+        nxt = pd.DataFrame({'genotype': genotypes, 'parent_id': parents, 'source_code': sources}, index=ids).rename_axis('id')
+        if len(nxt) == 0:
+            return nxt
+        parent_genotypes = np.array(generation.loc[parents, 'genotype'].values.tolist())
+        nxt['genotype_euclidean_distance_from_parent'] = np.sqrt(np.sum(np.power(offspring.astype(np.float64) - parent_genotypes, 2), axis=1))
+        nxt['genotype_hamming_distance_from_parent'] = (parent_genotypes != offspring).sum(axis=1) / p['genotype_size']
+        parent_sources = generation.loc[parents, 'source_code'].values
+        cache: Dict[tuple, int] = {}
+
+        def lev(a, b):
+            if a == b:
+                return 0
+            k = (a, b)
+            if k not in cache:
+                cache[k] = levenshtein(a, b)
+            return cache[k]
+        nxt['source_code_levenshtein_distance_from_parent'] = [lev(s, ps) for s, ps in zip(nxt['source_code'].values, parent_sources)]
+        return nxt
+
+    def _random_offspring_selection(self, _, num_offspring, offspring):
+        return offspring[np.random.permutation(len(offspring))[:num_offspring]]
+
+    def _best_offspring_selection(self, parent_genotype, num_offspring, offspring):
+        return offspring[np.argsort(hamming(parent_genotype, offspring))[:num_offspring]]
+
+    def _probabilistic_proofreading(self, parent_genotype, offspring):
+        ec = self._parameters['error_correction_probability']
+        out = offspring.copy()
+        rows, cols = np.where(out != parent_genotype)
+        fixed = np.random.permutation(len(rows))[:int(ec * len(rows))]     # consumes the stream even when ec == 0
+        rows, cols = rows[fixed], cols[fixed]
+        out[rows, cols] = parent_genotype[cols]
+        return out
+
+    # ------------------------------------------------------------------ statistics (experiment.py:240-303)
+    def get_genotype_stats(self, info: pd.DataFrame) -> dict:
+        genotypes = np.array(info['genotype'].values.tolist())
+        as_str = info['genotype'].map(lambda g: str(np.asarray(g).tolist()))
+        dist = as_str.value_counts(normalize=True)
+        mean_euclid, mean_hamming, diversity = pairwise_genotype_distances(genotypes)
+        return {'mean_pairwise_euclidean_distance': mean_euclid,
+                'mean_pairwise_hamming_distance': mean_hamming,
+                'mean_euclidean_distance_from_parent': info['genotype_euclidean_distance_from_parent'].mean(),
+                'mean_hamming_distance_from_parent': info['genotype_hamming_distance_from_parent'].mean(),
+                'shannon_index': float(-np.sum(dist * np.log(dist))),
+                'nucleotide_diversity': diversity,
+                'species_richness': int(as_str.nunique())}
+
+    def get_source_code_stats(self, info: pd.DataFrame) -> dict:
+        dist = info['source_code'].value_counts(normalize=True)
+        return {'median_levenshtein_distance_from_parent': info['source_code_levenshtein_distance_from_parent'].median(),
+                'shannon_index': float(-np.sum(dist * np.log(dist))),
+                'species_richness': int(info['source_code'].nunique())}
+
+    def _report_generation_statistics(self, info: pd.DataFrame, generation, times, start_time):
+        survived = info['is_valid'].astype(bool) & ~info['is_overweight'].astype(bool)
+        mean = lambda c: float(pd.to_numeric(info[c], errors='coerce').mean()) if c in info else float('nan')
+        row = {
+            'experiment_id': self._id, 'generation': generation, 'start_time': start_time,
+            'survival_rate': float(survived.mean()),
+            'overweight_rate': float(info['is_overweight'].astype(float).mean()),
+            'invalid_rate': float(1 - info['is_valid'].astype(float).mean()),
+            'mean_parameters_count': mean('parameters_count'),
+            'mean_absolute_fertility': mean('absolute_fertility'),
+            'absolute_fertility_std': float(pd.to_numeric(info['absolute_fertility'], errors='coerce').std()),
+            'mean_loss_balance': mean('loss_balance'),
+            'mean_classification_validation_accuracy': mean('classification_validation_accuracy'),
+            'mean_classification_training_accuracy': mean('classification_training_accuracy'),
+            'mean_classification_test_accuracy': mean('classification_test_accuracy'),
+            'max_classification_test_accuracy': float(pd.to_numeric(info['classification_test_accuracy'], errors='coerce').max()),
+            'mean_replication_mse': mean('replication_mse'),
+            'learning_time_seconds': float(np.mean(times['learning_times'])),
+            'replication_time_seconds': float(np.mean(times['replication_times'])),
+            'total_time_seconds': (datetime.now() - start_time).total_seconds(),
+            'mean_classification_layers': mean('classification_layers'),
+            'mean_replication_layers': mean('replication_layers'),
+            'mean_merged_layers': mean('merged_layers'),
+        }
+        row.update({f'genotype_{k}': v for k, v in self.get_genotype_stats(info).items()})
+        row.update({f'source_code_{k}': v for k, v in self.get_source_code_stats(info).items()})
+        self._experiment_db.save_generation_info(row)
