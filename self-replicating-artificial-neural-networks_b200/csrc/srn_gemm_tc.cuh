@@ -69,13 +69,25 @@ __host__ __device__ inline int tc_tiles_wgrad(const Prob& p, int nb, int BN) {
 // ------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// 16-byte asynchronous copy; when !valid the destination is zero-filled (src-size 0) and src is not read, but it
+// must still be a mapped address: callers pass clamped, always-valid pointers instead of selecting a dummy
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
-    const int sz = valid ? 16 : 0;                      // src-size 0: the 16 bytes are zero-filled
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(src), "r"(sz) : "memory");
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %2, 0;\n"
+        "@p cp.async.cg.shared.global [%0], [%1], 16;\n"
+        "@!p cp.async.cg.shared.global [%0], [%1], 16, 0;\n"
+        "}\n" ::"r"(dst), "l"(src), "r"((int)valid) : "memory");
 }
 __device__ __forceinline__ void cp_async16_ca(uint32_t dst, const void* src, bool valid) {   // keeps the line in L1 (im2col reuse)
-    const int sz = valid ? 16 : 0;
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(src), "r"(sz) : "memory");
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %2, 0;\n"
+        "@p cp.async.ca.shared.global [%0], [%1], 16;\n"
+        "@!p cp.async.ca.shared.global [%0], [%1], 16, 0;\n"
+        "}\n" ::"r"(dst), "l"(src), "r"((int)valid) : "memory");
 }
 // arrive on an mbarrier once all cp.async issued so far by this thread have landed (no wait in the thread)
 __device__ __forceinline__ void cp_async_arrive_noinc(uint32_t bar) {
@@ -289,10 +301,18 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
         // =================================================================== loaders (8 warps)
         // A tile: 128 (m or kk) x 64 k in 16-byte chunks = 1024 chunks, 4 per thread; B tile: BN x 64, BN/32 per
         // thread.  A warp covers 8 rows x 4 consecutive chunks per item (64 contiguous bytes per row).
+        // Per-tile loader state lives in registers: everything the k loop needs is copied out of the descriptor
+        // once per tile, and gather pointers are clamped to mapped addresses so that an out-of-range chunk only
+        // changes the copy's predicate (zero fill), never its address computation.
         const __half* l_in = nullptr; int l_in_bs = 0;
-        const __half* a_row[2];          // FWD: base of this thread's two im2col rows; null = out of range
-        int a_b[2], a_h[2], a_w[2];      // DGRAD: input position of this thread's two rows
+        const __half* a_row[2] = {nullptr, nullptr}; bool a_ok[2] = {false, false};   // FWD: this thread's two im2col rows
+        int a_b[2], a_h[2], a_w[2];      // DGRAD: input position of this thread's two rows (a_b < 0: out of range)
         int w_koff[4]; bool w_kok[4];    // WGRAD (vector): offsets of this thread's four kk chunks inside the window
+        const __half* t_w = nullptr; const __half* t_gout = nullptr;
+        int t_ldw = 0, t_C = 0, t_Cs = 1, t_Fs = 1, t_kw = 1, t_W = 1, t_Wo = 1, t_Ho = 1, t_sh = 1, t_sw = 1;
+        int t_Kf = 0, t_Kd = 0, t_n0 = 0, t_out_bs = 0, t_HoWo = 1, t_r0 = 0, t_r1 = 0, t_m0 = 0;
+        bool t_dense = true;
+        FastDiv t_fdc{}, t_fdkw{}, t_fdrows{}, t_fdw{};
         int lj = 0, lnk = 0;
         auto loader_enter_tile = [&]() {
             loaders_sync();                 // descriptor lj was stored before the previous loaders_sync
@@ -302,17 +322,23 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             const Prob& p = T.p;
             l_in = resolve_in(p, I, l_in_bs);
             lnk = T.nk;
-            const int HoWo = p.Ho * p.Wo, HW = p.H * p.W, Cs = p.Cs;
+            t_w = p.w; t_gout = p.gout; t_ldw = p.ldw; t_C = p.C; t_Cs = p.Cs; t_Fs = p.Fs; t_kw = p.kw; t_W = p.W;
+            t_Wo = p.Wo; t_Ho = p.Ho; t_sh = p.sh; t_sw = p.sw; t_n0 = T.n0; t_out_bs = p.out_bs; t_HoWo = p.Ho * p.Wo;
+            t_r0 = T.r0; t_r1 = T.r1; t_m0 = T.m0;
+            const int KK = p.kh * p.kw;
+            t_dense = KK == 1;
+            t_Kf = SCALAR_A ? KK : KK * p.Cs; t_Kd = KK * p.Fs;
+            t_fdc = T.fd_c; t_fdkw = T.fd_kw; t_fdrows = T.fd_rows; t_fdw = T.fd_w;
+            const int HW = p.H * p.W;
             if (MODE == TC_FWD) {
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
                     const int m = T.m0 + (warp * 2 + j) * 8 + l8;
-                    a_row[j] = nullptr;
-                    if (m < T.Mrows) {
-                        const int b = fdiv(m, T.fd_rows), rem = m - b * HoWo;
-                        const int ho = fdiv(rem, T.fd_w), wo = rem - ho * p.Wo;
-                        a_row[j] = l_in + (long long)b * l_in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * Cs;
-                    }
+                    a_ok[j] = m < T.Mrows;
+                    const int mc = a_ok[j] ? m : 0;
+                    const int b = fdiv(mc, t_fdrows), rem = mc - b * t_HoWo;
+                    const int ho = fdiv(rem, t_fdw), wo = rem - ho * t_Wo;
+                    a_row[j] = l_in + (long long)b * l_in_bs + ((long long)(ho * t_sh) * t_W + wo * t_sw) * t_Cs;
                 }
             } else if (MODE == TC_DGRAD) {
 #pragma unroll
@@ -320,9 +346,9 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                     const int m = T.m0 + (warp * 2 + j) * 8 + l8;
                     a_b[j] = -1; a_h[j] = 0; a_w[j] = 0;
                     if (m < T.Mrows) {
-                        a_b[j] = fdiv(m, T.fd_rows);
+                        a_b[j] = fdiv(m, t_fdrows);
                         const int rem = m - a_b[j] * HW;
-                        a_h[j] = fdiv(rem, T.fd_w); a_w[j] = rem - a_h[j] * p.W;
+                        a_h[j] = fdiv(rem, t_fdw); a_w[j] = rem - a_h[j] * t_W;
                     }
                 }
             } else if (!SCALAR_A) {
@@ -330,20 +356,14 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                 for (int q = 0; q < 4; ++q) {
                     const int kk = T.m0 + (q * 4 + lq) * 8;
                     w_kok[q] = kk < T.Mrows;
-                    const int ij = fdiv(kk, T.fd_c), cp = kk - ij * Cs;
-                    const int i = fdiv(ij, T.fd_kw), j = ij - i * p.kw;
-                    w_koff[q] = (i * p.W + j) * Cs + cp;
+                    const int kc = w_kok[q] ? kk : 0;
+                    const int ij = fdiv(kc, t_fdc), cp = kc - ij * t_Cs;
+                    const int i = fdiv(ij, t_fdkw), j = ij - i * t_kw;
+                    w_koff[q] = (i * t_W + j) * t_Cs + cp;
                 }
             }
         };
         auto load_stage = [&](int stage, int kb) {
-            const TcTile& T = ring[lj % TC_RING];
-            const Prob& p = T.p;
-            const int Cs = p.Cs, Fs = p.Fs, HoWo = p.Ho * p.Wo;
-            const int KK = p.kh * p.kw;
-            const int Kf = SCALAR_A ? KK : KK * Cs, Kd = KK * Fs;
-            const bool dense = KK == 1;
-            const int n0 = T.n0;
             const uint32_t aS = sA + stage * TC_A_BYTES, bS = sB + stage * B_BYTES;
             const int Q = BN >> 5;                           // B items per thread = quads of 4 chunks along the major axis
             if (MODE == TC_FWD) {
@@ -353,22 +373,20 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
                         const int k = kb * TC_BK + (h * 4 + lq) * 8;
-                        kok[h] = k < Kf;
-                        koff[h] = k;
-                        if (!dense) {
-                            const int ij = fdiv(k, T.fd_c), cp = k - ij * Cs;
-                            const int ki = fdiv(ij, T.fd_kw), kj = ij - ki * p.kw;
-                            koff[h] = (ki * p.W + kj) * Cs + cp;
+                        kok[h] = k < t_Kf;
+                        const int kc = kok[h] ? k : 0;
+                        koff[h] = kc;
+                        if (!t_dense) {
+                            const int ij = fdiv(kc, t_fdc), cp = kc - ij * t_Cs;
+                            const int ki = fdiv(ij, t_fdkw), kj = ij - ki * t_kw;
+                            koff[h] = (ki * t_W + kj) * t_Cs + cp;
                         }
                     }
 #pragma unroll
                     for (int j = 0; j < 2; ++j)
 #pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            const bool ok = a_row[j] != nullptr && kok[h];
-                            cp_async16_ca(aS + core_off(warp * 2 + j, h * 4 + lq, l8),
-                                          ok ? (const void*)(a_row[j] + koff[h]) : (const void*)p.w, ok);
-                        }
+                        for (int h = 0; h < 2; ++h)
+                            cp_async16_ca(aS + core_off(warp * 2 + j, h * 4 + lq, l8), a_row[j] + koff[h], a_ok[j] && kok[h]);
                 } else {
                     // first layer on a one-channel model input with per-individual inputs: element-wise gather
 #pragma unroll
@@ -377,11 +395,11 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                         for (int h = 0; h < 2; ++h) {
                             const int k = kb * TC_BK + (h * 4 + lq) * 8;
                             Half8 v;
-                            int ki = fdiv(k, T.fd_kw), kj = k - ki * p.kw;
+                            int ki = fdiv(k, t_fdkw), kj = k - ki * t_kw;
 #pragma unroll
                             for (int e = 0; e < 8; ++e) {
-                                v.v[e] = (a_row[j] != nullptr && k + e < Kf) ? a_row[j][ki * p.W + kj] : __float2half_rn(0.f);
-                                if (++kj == p.kw) { kj = 0; ++ki; }
+                                v.v[e] = (a_ok[j] && k + e < t_Kf) ? a_row[j][ki * t_W + kj] : __float2half_rn(0.f);
+                                if (++kj == t_kw) { kj = 0; ++ki; }
                             }
                             *reinterpret_cast<Half8*>(sgen + (aS - sbase) + core_off(warp * 2 + j, h * 4 + lq, l8)) = v;
                         }
@@ -390,17 +408,19 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                 // W rows are [(ij, c)][ldw]; pad channels have no row.
                 {
                     const int k = kb * TC_BK + warp * 8 + l8;
-                    long long wrow = k;
-                    bool kok = k < Kf;
+                    bool kok = k < t_Kf;
+                    const int kc = kok ? k : 0;
+                    int wrow = kc;
                     if (SCALAR_A) {}
-                    else if (dense) kok = kok && k < p.C;
-                    else { const int ij = fdiv(k, T.fd_c), cp = k - ij * Cs; kok = kok && cp < p.C; wrow = (long long)ij * p.C + cp; }
-                    const __half* wr = p.w + wrow * p.ldw + n0;
+                    else if (t_dense) kok = kok && kc < t_C;
+                    else { const int ij = fdiv(kc, t_fdc), cp = kc - ij * t_Cs; kok = kok && cp < t_C; wrow = ij * t_C + cp; }
+                    if (!kok) wrow = 0;
+                    const __half* wr = t_w + (long long)wrow * t_ldw;
 #pragma unroll 4
                     for (int i = 0; i < Q; ++i) {
-                        const int nch = i * 4 + lq;
-                        const bool ok = kok && n0 + nch * 8 < p.ldw;
-                        cp_async16(bS + core_off(nch, warp, l8), ok ? (const void*)(wr + nch * 8) : (const void*)p.w, ok);
+                        const int nch = i * 4 + lq, n = t_n0 + nch * 8;
+                        const bool ok = kok && n < t_ldw;
+                        cp_async16(bS + core_off(nch, warp, l8), wr + (ok ? n : 0), ok);
                     }
                 }
             } else if (MODE == TC_DGRAD) {
@@ -409,74 +429,66 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     const int k = kb * TC_BK + (h * 4 + lq) * 8;
-                    kok[h] = k < Kd;
-                    int ij = 0; kf[h] = k; kki[h] = 0; kkj[h] = 0;
-                    if (!dense) { ij = fdiv(k, T.fd_c); kf[h] = k - ij * Fs; kki[h] = fdiv(ij, T.fd_kw); kkj[h] = ij - kki[h] * p.kw; }
-                    wbase[h] = (long long)ij * p.C * p.ldw + kf[h];
+                    kok[h] = k < t_Kd;
+                    const int kc = kok[h] ? k : 0;
+                    int ij = 0; kf[h] = kc; kki[h] = 0; kkj[h] = 0;
+                    if (!t_dense) { ij = fdiv(kc, t_fdc); kf[h] = kc - ij * t_Fs; kki[h] = fdiv(ij, t_fdkw); kkj[h] = ij - kki[h] * t_kw; }
+                    wbase[h] = (long long)ij * t_C * t_ldw + kf[h];
                 }
 #pragma unroll
                 for (int j = 0; j < 2; ++j)
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
                         bool ok = a_b[j] >= 0 && kok[h];
-                        const __half* src = p.gout;
-                        if (ok) {
-                            const int hh = a_h[j] - kki[h], ww = a_w[j] - kkj[h];
-                            ok = hh >= 0 && ww >= 0;
-                            if (ok) {
-                                // strides are 1 or 2 in practice: shifts for those, a real division otherwise
-                                const int ho = p.sh == 1 ? hh : (p.sh == 2 ? hh >> 1 : hh / p.sh);
-                                const int wo = p.sw == 1 ? ww : (p.sw == 2 ? ww >> 1 : ww / p.sw);
-                                ok = ho * p.sh == hh && wo * p.sw == ww && ho < p.Ho && wo < p.Wo;
-                                if (ok) src = p.gout + (long long)a_b[j] * p.out_bs + (ho * p.Wo + wo) * Fs + kf[h];
-                            }
-                        }
-                        cp_async16_ca(aS + core_off(warp * 2 + j, h * 4 + lq, l8), src, ok);
+                        const int hh = a_h[j] - kki[h], ww = a_w[j] - kkj[h];
+                        // strides are 1 or 2 in practice: shifts for those, a real division otherwise
+                        const int ho = t_sh == 1 ? hh : (t_sh == 2 ? hh >> 1 : hh / t_sh);
+                        const int wo = t_sw == 1 ? ww : (t_sw == 2 ? ww >> 1 : ww / t_sw);
+                        ok = ok && hh >= 0 && ww >= 0 && ho * t_sh == hh && wo * t_sw == ww && ho < t_Ho && wo < t_Wo;
+                        const long long off = ok ? (long long)a_b[j] * t_out_bs + (ho * t_Wo + wo) * t_Fs + kf[h] : 0;
+                        cp_async16_ca(aS + core_off(warp * 2 + j, h * 4 + lq, l8), t_gout + off, ok);
                     }
                 // B, K-major: rows n = input channel c, k = (ij, f) contiguous in f; items q = warp*Q + i -> (row block q/2, chunk half q%2)
 #pragma unroll 4
                 for (int i = 0; i < Q; ++i) {
                     const int q = warp * Q + i, blk = q >> 1, h = q & 1;
-                    const int c = n0 + blk * 8 + l8;
-                    const bool ok = c < p.C && kok[h];
-                    cp_async16(bS + core_off(blk, h * 4 + lq, l8),
-                               ok ? (const void*)(p.w + wbase[h] + (long long)c * p.ldw) : (const void*)p.w, ok);
+                    const int c = t_n0 + blk * 8 + l8;
+                    const bool ok = c < t_C && kok[h];
+                    cp_async16(bS + core_off(blk, h * 4 + lq, l8), t_w + (ok ? wbase[h] + (long long)c * t_ldw : 0), ok);
                 }
             } else {
                 // this warp owns reduction rows r0 + kb*64 + warp*8 .. +7 (one per l8)
-                const int r = T.r0 + kb * TC_BK + warp * 8 + l8;
-                const __half* in_row = nullptr; const __half* go_row = nullptr;
-                if (r < T.r1) {
-                    const int b = fdiv(r, T.fd_rows), rem = r - b * HoWo;
-                    const int ho = fdiv(rem, T.fd_w), wo = rem - ho * p.Wo;
-                    in_row = l_in + (long long)b * l_in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * Cs;
-                    go_row = p.gout + (long long)b * p.out_bs + (long long)rem * Fs;
-                }
+                const int r = t_r0 + kb * TC_BK + warp * 8 + l8;
+                const bool rok = r < t_r1;
+                const int rc = rok ? r : t_r0;
+                const int b = fdiv(rc, t_fdrows), rem = rc - b * t_HoWo;
+                const int ho = fdiv(rem, t_fdw), wo = rem - ho * t_Wo;
+                const __half* in_row = l_in + (long long)b * l_in_bs + ((long long)(ho * t_sh) * t_W + wo * t_sw) * t_Cs;
+                const __half* go_row = t_gout + (long long)b * t_out_bs + (long long)rem * t_Fs;
                 // A, MN-major: 4 quads of kk chunks
 #pragma unroll
                 for (int qd = 0; qd < 4; ++qd) {
                     const int cc = qd * 4 + lq;
                     if (SCALAR_A) {
                         Half8 v;
-                        const int kk = T.m0 + cc * 8;
-                        int ki = fdiv(kk, T.fd_kw), kj = kk - ki * p.kw;
+                        const int kk = t_m0 + cc * 8;
+                        int ki = fdiv(kk, t_fdkw), kj = kk - ki * t_kw;
 #pragma unroll
                         for (int e = 0; e < 8; ++e) {
-                            v.v[e] = (in_row != nullptr && kk + e < Kf) ? in_row[ki * p.W + kj] : __float2half_rn(0.f);
-                            if (++kj == p.kw) { kj = 0; ++ki; }
+                            v.v[e] = (rok && kk + e < t_Kf) ? in_row[ki * t_W + kj] : __float2half_rn(0.f);
+                            if (++kj == t_kw) { kj = 0; ++ki; }
                         }
                         *reinterpret_cast<Half8*>(sgen + (aS - sbase) + core_off(cc, warp, l8)) = v;
                     } else {
-                        const bool ok = in_row != nullptr && w_kok[qd];
-                        cp_async16_ca(aS + core_off(cc, warp, l8), ok ? (const void*)(in_row + w_koff[qd]) : (const void*)p.w, ok);
+                        cp_async16_ca(aS + core_off(cc, warp, l8), in_row + w_koff[qd], rok && w_kok[qd]);
                     }
                 }
                 // B, MN-major: Q quads of f chunks
 #pragma unroll 4
                 for (int i = 0; i < Q; ++i) {
-                    const int nch = i * 4 + lq, f = n0 + nch * 8;
-                    const bool ok = go_row != nullptr && f < Fs;
-                    cp_async16(bS + core_off(nch, warp, l8), ok ? (const void*)(go_row + f) : (const void*)p.w, ok);
+                    const int nch = i * 4 + lq, f = t_n0 + nch * 8;
+                    const bool ok = rok && f < t_Fs;
+                    cp_async16(bS + core_off(nch, warp, l8), go_row + (ok ? f : 0), ok);
                 }
             }
         };
