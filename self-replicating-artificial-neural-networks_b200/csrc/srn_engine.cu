@@ -372,7 +372,6 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
             to.needs_grad = ng;
             to.root = 2 + l; to.depth = depth + 1;
             to.Cs = (int)align_up(to.C, 8);
-            if (d.kind == SRN_KIND_BN || d.kind == SRN_KIND_MAXPOOL) to.Cs = ti.Cs;     // same channels in and out
             if (d.kind == SRN_KIND_RESHAPE) {
                 const bool src_flat = ti.Cs == ti.C || ti.rows == 1;
                 if (src_flat && (to.rows == 1 || to.C % 8 == 0)) {       // pure view of the source's storage
@@ -484,7 +483,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                         // 1: operands in 16-byte chunks (channel stride padded to 8); 2: first layers on a one-channel
                         // model input, im2col gathered element by element
                         if (p.Cs % 8 == 0 && p.Fs % 8 == 0) tc = 1;
-                        else if (p.in_sel != 0 && p.Cs == 1 && p.C == 1 && p.Fs % 8 == 0) tc = 2;
+                        else if (p.in_sel != 0 && p.Cs == 1 && p.C == 1 && p.Fs % 8 == 0) tc = 2;   // only the model inputs have Cs == 1
                         if (tc) { cfgF = tc_cfg_for(p.F); cfgC = tc_cfg_for(p.C); }
                     }
                 } else if (d.kind == SRN_KIND_MAXPOOL) {

@@ -139,7 +139,7 @@ k_bn_partial(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
                 if (g.cw == 8) {
                     const Half8 x = ld8(in + io);
                     if (bwd) {
-                        const Half8 dy = ld8(p.gout + r * Cs + (long long)cq * 8);
+                        const Half8 dy = ld8(p.gout + r * p.Fs + (long long)cq * 8);
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
                             const float d = __half2float(dy.v[j]);
@@ -156,7 +156,7 @@ k_bn_partial(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
                     }
                 } else {
                     const float xv = __half2float(in[io]) - pivot[0];
-                    if (bwd) { const float d = __half2float(p.gout[r * Cs + cq]); s1[0] += d; s2[0] += d * xv; }
+                    if (bwd) { const float d = __half2float(p.gout[r * p.Fs + cq]); s1[0] += d; s2[0] += d * xv; }
                     else { s1[0] += xv; s2[0] += xv * xv; }
                 }
             }
@@ -262,7 +262,7 @@ k_bn_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, int n
     for (int i = 0; i < EW_PER_THREAD; ++i, q += EW_THREADS) {
         if (q >= total) break;
         const long long r = q / nq; const int c0 = (int)(q - r * nq) * cw;
-        const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = r * Cs + c0;
+        const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = r * p.Fs + c0;
         if (cw == 8) {
             const Half8 x = ld8(in + io);
             Half8 y;
@@ -317,7 +317,7 @@ k_bn_bwd_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
     for (int i = 0; i < EW_PER_THREAD; ++i, q += EW_THREADS) {
         if (q >= total) break;
         const long long r = q / nq; const int c0 = (int)(q - r * nq) * cw;
-        const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = r * Cs + c0;
+        const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = r * p.Fs + c0;
         if (cw == 8) {
             const Half8 x = ld8(in + io), dy = ld8(p.gout + oo);
             Half8 d;
@@ -375,7 +375,7 @@ k_maxpool_fwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
                     if (better_max(v, best[0])) best[0] = v;
                 }
             }
-        __half* o = p.out + pix * Cs + c0;
+        __half* o = p.out + pix * p.Fs + c0;
         if (cw == 8) {
             Half8 y;
 #pragma unroll
@@ -400,6 +400,58 @@ k_maxpool_bwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
     long long q = (long long)blk * EW_PER_CTA + threadIdx.x;
+    if (p.sh == p.kh && p.sw == p.kw) {
+        // windows do not overlap (Keras' default stride): one thread per window and channel chunk finds the first
+        // maximum and writes the whole window's gradients; the threads of the last window column / row also clear
+        // the input pixels that no window covers
+        const long long wtotal = (long long)nb * HoWo * nq;
+#pragma unroll 1
+        for (int it = 0; it < EW_PER_THREAD; ++it, q += EW_THREADS) {
+            if (q >= wtotal) break;
+            const long long pix = q / nq; const int c0 = (int)(q - pix * nq) * cw;
+            const long long b = pix / HoWo; const int rem = (int)(pix - b * HoWo);
+            const int ho = rem / p.Wo, wo = rem - ho * p.Wo;
+            const long long oo = pix * p.Fs + c0;
+            float mx[8], go[8]; int arg[8];
+            if (cw == 8) { const Half8 m8 = ld8(p.out + oo), g8 = ld8(p.gout + oo);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { mx[j] = __half2float(m8.v[j]); go[j] = __half2float(g8.v[j]); arg[j] = -1; }
+            } else { mx[0] = __half2float(p.out[oo]); go[0] = __half2float(p.gout[oo]); arg[0] = -1; }
+            const __half* ib = in + b * in_bs + ((long long)(ho * p.kh) * p.W + wo * p.kw) * Cs + c0;
+            for (int i = 0; i < p.kh; ++i)
+                for (int jj = 0; jj < p.kw; ++jj) {
+                    const __half* s = ib + ((long long)i * p.W + jj) * Cs;
+                    if (cw == 8) { const Half8 e = ld8(s);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) { const float v = __half2float(e.v[j]); if (arg[j] < 0 && (v == mx[j] || (v != v && mx[j] != mx[j]))) arg[j] = i * p.kw + jj; }
+                    } else { const float v = __half2float(*s); if (arg[0] < 0 && (v == mx[0] || (v != v && mx[0] != mx[0]))) arg[0] = i * p.kw + jj; }
+                }
+            const int h_end = (ho == p.Ho - 1) ? p.H - ho * p.kh : p.kh;      // also the uncovered rows / columns
+            const int w_end = (wo == p.Wo - 1) ? p.W - wo * p.kw : p.kw;
+            __half* db = p.din + b * p.in_bs + ((long long)(ho * p.kh) * p.W + wo * p.kw) * Cs + c0;
+            for (int i = 0; i < h_end; ++i)
+                for (int jj = 0; jj < w_end; ++jj) {
+                    __half* d = db + ((long long)i * p.W + jj) * Cs;
+                    const int id = (i < p.kh && jj < p.kw) ? i * p.kw + jj : -2;
+                    if (cw == 8) {
+                        Half8 o;
+                        if (p.din_acc) o = ld8(d);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            float v = (arg[j] == id && c0 + j < p.C) ? go[j] : 0.f;
+                            if (p.din_acc) v = rh(v) + __half2float(o.v[j]);
+                            o.v[j] = __float2half_rn(v);
+                        }
+                        st8(d, o);
+                    } else {
+                        float v = (arg[0] == id) ? go[0] : 0.f;
+                        if (p.din_acc) v = rh(v) + __half2float(*d);
+                        *d = __float2half_rn(v);
+                    }
+                }
+        }
+        return;
+    }
 #pragma unroll 1
     for (int it = 0; it < EW_PER_THREAD; ++it, q += EW_THREADS) {
         if (q >= total) break;
@@ -420,7 +472,7 @@ k_maxpool_bwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
         const int ho_hi = min(p.Ho - 1, h / p.sh), wo_hi = min(p.Wo - 1, w / p.sw);
         for (int ho = ho_lo; ho <= ho_hi; ++ho)
             for (int wo = wo_lo; wo <= wo_hi; ++wo) {
-                const long long oo = (b * HoWo + (long long)ho * p.Wo + wo) * Cs + c0;
+                const long long oo = (b * HoWo + (long long)ho * p.Wo + wo) * p.Fs + c0;
                 float mx[8], go[8];
                 if (cw == 8) { const Half8 m8 = ld8(p.out + oo), g8 = ld8(p.gout + oo);
 #pragma unroll

@@ -125,3 +125,15 @@ def make_engine_and_oracle(irs, data, max_batch=64, weight_seed=5):
         eng.set_weights(i, w)
         inds.append(O.Individual(ir, w))
     return eng, inds
+
+# pooling / BatchNormalization applied directly to the one-channel model inputs, overlapping and uneven pooling windows
+NET_F = """X_layer = MaxPool2D(pool_size=2)(X_layer)
+X_layer = Conv2D(filters=8, kernel_size=3, strides=1)(X_layer)
+X_layer = MaxPool2D(pool_size=5)(X_layer)
+g_layer = BatchNormalization()(g_layer)
+g_layer = Conv1D(filters=8, kernel_size=5, strides=2)(g_layer)
+con = concatenate([Reshape((1, -1))(X_layer), Reshape((1, -1))(g_layer)])
+con = Dense(units=50, activation='relu')(con)
+
+loss_balance = 0.35"""
+HANDCRAFTED.append(NET_F)
