@@ -49,6 +49,8 @@ struct Tensor {
     long long bs = 0;          // batch stride in elements = rows * Cs
     int root = -1;             // tensor whose storage this one views
     bool view = false;
+    int inplace_of = -1;       // concat tensor whose buffer this tensor is written into directly (no copy)
+    long long inplace_off = 0;
     bool needs_grad = false;
     int depth = 0;
     int consumers = 0;         // consumers needing din (counted on the root)
@@ -343,16 +345,19 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
         Tensor& tg = ind.tensors[1]; tg.rows = h->G; tg.C = tg.Cs = 1; tg.elems = h->G; tg.bs = h->G; tg.root = 1;
         // a concatenate reads through reshapes (flat order is preserved), so a reshape that would need a
         // compacting copy is only materialised when something else consumes it
-        std::vector<int> used(2 + nl, 0);
+        std::vector<int> used(2 + nl, 0);       // direct readers of a tensor (a concatenate counts on the chased source)
+        std::vector<int> used_src(2 + nl, 0);   // readers of a tensor through any chain of reshapes
         auto chase = [&](int t) { while (t >= 2 && layers[off[i] + t - 2].kind == SRN_KIND_RESHAPE) t = layers[off[i] + t - 2].in[0]; return t; };
         for (int l = 0; l < nl; ++l) {
             const srn_layer_desc& d = layers[off[i] + l];
             for (int j = 0; j < d.n_in && j < SRN_MAX_CONCAT_INPUTS; ++j) {
                 if (d.in[j] < 0 || d.in[j] >= 2 + l) return fail(SRN_ERR_ARG, "individual %d layer %d: input id %d out of range", i, l, d.in[j]);
                 used[d.kind == SRN_KIND_CONCAT ? chase(d.in[j]) : d.in[j]] += 1;
+                if (d.kind != SRN_KIND_RESHAPE) used_src[chase(d.in[j])] += 1;
             }
         }
         used[1 + nl] += 1;
+        used_src[chase(1 + nl)] += 1;
         for (int l = 0; l < nl; ++l) {
             LayerRt& L = ind.layers[l];
             L.d = layers[off[i] + l];
@@ -402,10 +407,28 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
         }
         if (ind.tensors.back().elems != h->NL || ind.tensors.back().rows != 1)
             return fail(SRN_ERR_ARG, "individual %d: last layer must emit one row of n_classes + genotype_size = %d values", i, h->NL);
+        // in-place concatenation: an input that is the dense (C % 8 == 0) output of a layer, read by nothing else,
+        // is produced straight into its slice of the (1, F) concatenation buffer - forward copy and backward
+        // slice copy disappear; the producers and gradient readers honour the buffer's batch stride
+        for (int l = 0; l < nl; ++l) {
+            const srn_layer_desc& d = ind.layers[l].d;
+            if (d.kind != SRN_KIND_CONCAT || ind.tensors[2 + l].rows != 1) continue;
+            long long coff = 0;
+            for (int j = 0; j < d.n_in; ++j) {
+                const int si = chase(d.in[j]);
+                Tensor& S = ind.tensors[si];
+                if (si >= 2 && !S.view && S.inplace_of < 0 && S.Cs == S.C && coff % 8 == 0 && used_src[si] == 1 &&
+                    ind.layers[si - 2].d.kind != SRN_KIND_CONCAT && ind.layers[si - 2].d.kind != SRN_KIND_RESHAPE) {
+                    S.inplace_of = 2 + l; S.inplace_off = coff;
+                    S.bs = ind.tensors[2 + l].bs;
+                }
+                coff += S.elems;
+            }
+        }
         // storage: every tensor that owns memory gets activations; gradients where needed
         for (size_t t = 2; t < ind.tensors.size(); ++t) {
             Tensor& T = ind.tensors[t];
-            if (T.view || ind.layers[t - 2].dead) continue;
+            if (T.view || ind.layers[t - 2].dead || T.inplace_of >= 0) continue;
             a_off = align_up(a_off, 64);
             T.act_off = a_off; a_off += T.bs * MB;
             if (T.needs_grad) { a_off = align_up(a_off, 64); T.grad_off = a_off; a_off += T.bs * MB; }
@@ -443,6 +466,12 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
             if (T.grad_off >= 0) T.grad = h->act + T.grad_off;
             T.consumers = 0;
         }
+        for (auto& T : ind.tensors)              // tensors produced in place inside a concatenation buffer
+            if (T.inplace_of >= 0) {
+                const Tensor& Cn = ind.tensors[T.inplace_of];
+                T.act = Cn.act + T.inplace_off;
+                T.grad = (T.needs_grad && Cn.grad) ? Cn.grad + T.inplace_off : nullptr;
+            }
         for (auto& T : ind.tensors)              // views share the root's storage (roots precede their views)
             if (T.view) { T.act = ind.tensors[T.root].act; T.grad = ind.tensors[T.root].grad; }
         auto chase = [&](int t) { while (t >= 2 && ind.layers[t - 2].d.kind == SRN_KIND_RESHAPE) t = ind.layers[t - 2].d.in[0]; return t; };
@@ -456,6 +485,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
             for (int j = 0; j < d.n_in; ++j) {
                 const int tin = d.kind == SRN_KIND_CONCAT ? chase(d.in[j]) : d.in[j];
                 Tensor& ti = ind.tensors[tin];
+                if (d.kind == SRN_KIND_CONCAT && ti.inplace_of == (int)(2 + l)) { coff += (int)ti.elems; continue; }   // already in place
                 Tensor& troot = ind.tensors[ti.root];
                 Prob p{};
                 p.indiv = i;
@@ -1178,7 +1208,10 @@ extern "C" int srn_debug_get_tensor(srn_engine* h, int32_t ind, int32_t tensor, 
     if (!src) return fail(SRN_ERR_ARG, "srn_debug_get_tensor: tensor %d has no %s buffer", tensor, grad ? "gradient" : "activation");
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
-    CK(cudaMemcpy2D(buf, (size_t)T.C * sizeof(__half), src, (size_t)T.Cs * sizeof(__half), (size_t)T.C * sizeof(__half), (size_t)nb * T.rows, cudaMemcpyDeviceToHost));
+    if (T.bs == T.rows * T.Cs)
+        CK(cudaMemcpy2D(buf, (size_t)T.C * sizeof(__half), src, (size_t)T.Cs * sizeof(__half), (size_t)T.C * sizeof(__half), (size_t)nb * T.rows, cudaMemcpyDeviceToHost));
+    else        // produced in place inside a concatenation buffer: dense rows (Cs == C), the buffer's batch stride
+        CK(cudaMemcpy2D(buf, (size_t)T.elems * sizeof(__half), src, (size_t)T.bs * sizeof(__half), (size_t)T.elems * sizeof(__half), (size_t)nb, cudaMemcpyDeviceToHost));
     return SRN_OK;
 }
 

@@ -32,6 +32,14 @@ __device__ __forceinline__ long long in_row_off(long long r, int rps, int bs, in
     return b * bs + (r - b * rps) * (long long)Cs;
 }
 
+// offset of row r (over all samples) of an output / output-gradient tensor.  Normally samples are contiguous
+// (bs == rps * Fs); a tensor written in place into a concatenation buffer has the buffer's batch stride instead
+__device__ __forceinline__ long long out_row_off(long long r, int rps, int bs, int Fs) {
+    if (bs == rps * Fs) return r * Fs;
+    const long long b = r / rps;
+    return b * bs + (r - b * rps) * (long long)Fs;
+}
+
 // sums over the row lanes of a CTA: sm holds one value per (thread, j); thread `ch` (< nq * cw) gets channel ch
 __device__ __forceinline__ float col_block_sum(const float* sm, const ColGeom& g, int ch) {
     const int cq = ch / g.cw, j = ch - cq * g.cw;
@@ -60,7 +68,7 @@ k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
         float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (active) {
             for (long long r = r0 + rl; r < r1; r += g.RL) {
-                const long long o = r * Fs + (long long)cq * g.cw;
+                const long long o = out_row_off(r, p.Ho * p.Wo, p.out_bs, Fs) + (long long)cq * g.cw;
                 if (g.cw == 8) {
                     Half8 gv = ld8(p.gout + o);
                     if (p.act == 1) {
@@ -139,7 +147,7 @@ k_bn_partial(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
                 if (g.cw == 8) {
                     const Half8 x = ld8(in + io);
                     if (bwd) {
-                        const Half8 dy = ld8(p.gout + r * p.Fs + (long long)cq * 8);
+                        const Half8 dy = ld8(p.gout + out_row_off(r, rps, p.out_bs, p.Fs) + (long long)cq * 8);
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
                             const float d = __half2float(dy.v[j]);
@@ -156,7 +164,7 @@ k_bn_partial(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
                     }
                 } else {
                     const float xv = __half2float(in[io]) - pivot[0];
-                    if (bwd) { const float d = __half2float(p.gout[r * p.Fs + cq]); s1[0] += d; s2[0] += d * xv; }
+                    if (bwd) { const float d = __half2float(p.gout[out_row_off(r, rps, p.out_bs, p.Fs) + cq]); s1[0] += d; s2[0] += d * xv; }
                     else { s1[0] += xv; s2[0] += xv * xv; }
                 }
             }
@@ -262,7 +270,7 @@ k_bn_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, int n
     for (int i = 0; i < EW_PER_THREAD; ++i, q += EW_THREADS) {
         if (q >= total) break;
         const long long r = q / nq; const int c0 = (int)(q - r * nq) * cw;
-        const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = r * p.Fs + c0;
+        const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = out_row_off(r, rps, p.out_bs, p.Fs) + c0;
         if (cw == 8) {
             const Half8 x = ld8(in + io);
             Half8 y;
@@ -317,7 +325,7 @@ k_bn_bwd_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
     for (int i = 0; i < EW_PER_THREAD; ++i, q += EW_THREADS) {
         if (q >= total) break;
         const long long r = q / nq; const int c0 = (int)(q - r * nq) * cw;
-        const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = r * p.Fs + c0;
+        const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = out_row_off(r, rps, p.out_bs, p.Fs) + c0;
         if (cw == 8) {
             const Half8 x = ld8(in + io), dy = ld8(p.gout + oo);
             Half8 d;
@@ -375,7 +383,7 @@ k_maxpool_fwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
                     if (better_max(v, best[0])) best[0] = v;
                 }
             }
-        __half* o = p.out + pix * p.Fs + c0;
+        __half* o = p.out + out_row_off(pix, HoWo, p.out_bs, p.Fs) + c0;
         if (cw == 8) {
             Half8 y;
 #pragma unroll
@@ -411,7 +419,7 @@ k_maxpool_bwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
             const long long pix = q / nq; const int c0 = (int)(q - pix * nq) * cw;
             const long long b = pix / HoWo; const int rem = (int)(pix - b * HoWo);
             const int ho = rem / p.Wo, wo = rem - ho * p.Wo;
-            const long long oo = pix * p.Fs + c0;
+            const long long oo = out_row_off(pix, HoWo, p.out_bs, p.Fs) + c0;
             float mx[8], go[8]; int arg[8];
             if (cw == 8) { const Half8 m8 = ld8(p.out + oo), g8 = ld8(p.gout + oo);
 #pragma unroll
@@ -472,7 +480,7 @@ k_maxpool_bwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
         const int ho_hi = min(p.Ho - 1, h / p.sh), wo_hi = min(p.Wo - 1, w / p.sw);
         for (int ho = ho_lo; ho <= ho_hi; ++ho)
             for (int wo = wo_lo; wo <= wo_hi; ++wo) {
-                const long long oo = (b * HoWo + (long long)ho * p.Wo + wo) * p.Fs + c0;
+                const long long oo = b * p.out_bs + ((long long)ho * p.Wo + wo) * p.Fs + c0;
                 float mx[8], go[8];
                 if (cw == 8) { const Half8 m8 = ld8(p.out + oo), g8 = ld8(p.gout + oo);
 #pragma unroll
@@ -518,11 +526,17 @@ k_maxpool_bwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
 // ------------------------------------------------------------------ copy: concatenate (last axis) and non-view reshape
 // The source's n_el real elements per sample, in row-major (row, channel) order, fill rows of Cj channels at
 // channel offset coff of the destination.  fwd: out <- in;  bwd: din (+)= gout.
-// 16-byte path when source rows, destination rows and the channel offset are all multiples of 8 channels
-__host__ __device__ inline bool copy_vec(const Prob& p) { return p.C % 8 == 0 && p.Cj % 8 == 0 && p.coff % 8 == 0 && p.Cs % 8 == 0 && p.Fs % 8 == 0; }
+// Work unit = one 16-byte chunk of 8 source channels when the source has a padded channel stride (every tensor but
+// the model inputs), else one element.  mode 2: source and destination chunks are both aligned (C, Cj, coff
+// multiples of 8): 16-byte load and store.  mode 1: aligned source chunk, compacted (unaligned) destination:
+// 16-byte access on the source side, 2-byte accesses on the destination side.  mode 0: element by element.
+__host__ __device__ inline int copy_mode(const Prob& p) {
+    if (p.Cs % 8 != 0) return 0;
+    return (p.C % 8 == 0 && p.Cj % 8 == 0 && p.coff % 8 == 0 && p.Fs % 8 == 0) ? 2 : 1;
+}
 __host__ __device__ inline int copy_blocks(const Prob& p, int nb) {
-    const long long units = (long long)nb * (copy_vec(p) ? p.n_el / 8 : p.n_el);
-    return (int)((units + EW_PER_CTA - 1) / EW_PER_CTA);
+    const long long per = copy_mode(p) ? (long long)(p.n_el / p.C) * (p.Cs / 8) : p.n_el;
+    return (int)(((long long)nb * per + EW_PER_CTA - 1) / EW_PER_CTA);
 }
 
 static __global__ void __launch_bounds__(EW_THREADS)
@@ -531,27 +545,28 @@ k_copy(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob
     const Prob p = probs[pi];
     if (bwd && p.din == nullptr) return;
     const int blk = blockIdx.x - prefix[pi];
-    const bool vec = copy_vec(p);
-    const int cw = vec ? 8 : 1;
-    const int per = p.n_el / cw;                       // units per sample
+    const int mode = copy_mode(p);
+    const int nq = mode ? p.Cs / 8 : 1;
+    const int per = mode ? (p.n_el / p.C) * nq : p.n_el;      // units per sample
     const long long total = (long long)nb * per;
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
     long long u = (long long)blk * EW_PER_CTA + threadIdx.x;
-#pragma unroll
+#pragma unroll 1
     for (int i = 0; i < EW_PER_THREAD; ++i, u += EW_THREADS) {
         if (u >= total) break;
-        const long long b = u / per; const int ee = (int)(u - b * per) * cw;
-        const int sr = ee / p.C, sc = ee - sr * p.C;
-        const int dr = ee / p.Cj, dc = ee - dr * p.Cj;
+        const long long b = u / per; const int uu = (int)(u - b * per);
+        int sr, sc;
+        if (mode) { sr = uu / nq; sc = (uu - sr * nq) * 8; } else { sr = uu / p.C; sc = uu - sr * p.C; }
+        if (sc >= p.C) continue;                                // a chunk that is pad only
         const long long so = b * in_bs + (long long)sr * p.Cs + sc;
-        const long long dd = b * p.out_bs + (long long)dr * p.Fs + p.coff + dc;
-        if (!bwd) {
-            if (vec) st8(p.out + dd, ld8(in + so));
-            else p.out[dd] = in[so];
-        } else {
-            const long long go = b * p.in_bs + (long long)sr * p.Cs + sc;
-            if (vec) {
+        const int ee = sr * p.C + sc;                           // flat index of the first element of the unit
+        int dr = ee / p.Cj, dc = ee - dr * p.Cj;
+        if (mode == 2) {
+            const long long dd = b * p.out_bs + (long long)dr * p.Fs + p.coff + dc;
+            if (!bwd) st8(p.out + dd, ld8(in + so));
+            else {
+                const long long go = b * p.in_bs + (long long)sr * p.Cs + sc;
                 Half8 g = ld8(p.gout + dd);
                 if (p.din_acc) {
                     const Half8 o = ld8(p.din + go);
@@ -559,11 +574,29 @@ k_copy(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob
                     for (int j = 0; j < 8; ++j) g.v[j] = __float2half_rn(__half2float(g.v[j]) + __half2float(o.v[j]));
                 }
                 st8(p.din + go, g);
-            } else {
-                float g = __half2float(p.gout[dd]);
-                if (p.din_acc) g += __half2float(p.din[go]);
-                p.din[go] = __float2half_rn(g);
             }
+        } else {
+            const int n = mode ? min(8, p.C - sc) : 1;          // real channels in this unit
+            Half8 v;
+            const long long go = b * p.in_bs + (long long)sr * p.Cs + sc;
+            if (!bwd) { if (mode) v = ld8(in + so); else v.v[0] = in[so]; }
+            else if (p.din_acc) { if (mode) v = ld8(p.din + go); else v.v[0] = p.din[go]; }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (j < n) {
+                    const long long dd = b * p.out_bs + (long long)dr * p.Fs + p.coff + dc;
+                    if (!bwd) p.out[dd] = v.v[j];
+                    else {
+                        float g = __half2float(p.gout[dd]);
+                        if (p.din_acc) g += __half2float(v.v[j]);
+                        v.v[j] = __float2half_rn(g);
+                    }
+                    if (++dc == p.Cj) { dc = 0; ++dr; }
+                } else if (bwd) {
+                    v.v[j] = __float2half_rn(0.f);                 // pad channels of the source gradient stay zero
+                }
+            }
+            if (bwd) { if (mode) st8(p.din + go, v); else p.din[go] = v.v[0]; }
         }
     }
 }
