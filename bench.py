@@ -194,7 +194,7 @@ def run_reference(args):
 
 
 def workload_config(args, n_ind):
-    return {'workload': f'configs[1]: population {args.pop} SeRANNs per GPU ({args.mix} generator mix, seed 0), '
+    return {'workload': f'configs[1]: population {args.pop} SeRANNs per GPU ({args.mix} generator mix, seed 0, the same mix on every GPU), '
                         f'batch {BATCH}, 60000/10000 synthetic rows of 28x28 + 100-bit genotypes',
             'population_per_gpu': n_ind, 'batch': BATCH, 'mix': args.mix,
             'l2_policy': 'working set per step (activation arena, GBs) is far larger than the 126 MB L2',
@@ -240,8 +240,10 @@ def main():
     from serann_b200.synthetic import synthetic_dataset
     from serann_b200.worker import B200PopulationWorker
 
-    pop = population(args.pop * world, args.mix)
-    mine = shard(pop, world, rank)
+    # weak scaling: every GPU evaluates its own args.pop individuals drawn from the same architecture mix (independent
+    # initialisations), so the per-GPU work is the same at every N; the job's population is args.pop * world
+    pop = population(args.pop, args.mix)
+    mine = list(range(len(pop)))
     irs = [pop[i][1] for i in mine]
     data = synthetic_dataset()
     n_val = 3000
@@ -275,8 +277,12 @@ def main():
     top = max((k for k in flops), key=lambda k: prof[k][0])
     top_ms, top_launches = prof[top][0] / 2.0, prof[top][1] // 2
     achieved = flops[top] / (top_ms / 1000.0) / 1e12
+    traffic = None
+    tpath = ROOT / 'profiles' / 'r01_dram_traffic_per_step.json'
+    if tpath.exists():      # dram__bytes_read + write per step of each kernel category, from the committed ncu capture
+        traffic = json.loads(tpath.read_text()).get(top)
     roofline = {'bound': 'tensor', 'kernel': top, 'achieved': achieved, 'peak': tf_sust, 'unit': 'TFLOP/s',
-                'frac': achieved / tf_sust, 'traffic': None, 'peak_source': f'{peak_kind} sustained bf16/fp16 dense',
+                'frac': achieved / tf_sust, 'traffic': traffic, 'peak_source': f'{peak_kind} sustained bf16/fp16 dense',
                 'launches_per_step': top_launches, 'ms_per_step_in_kernel': top_ms,
                 'share_of_step': shares,
                 'note': 'population-grouped implicit GEMM on tcgen05 (fp16 operands, fp32 TMEM accumulators, cp.async-gathered '
@@ -292,7 +298,7 @@ def main():
     e2e = None
     if not args.no_e2e:
         import pandas as pd
-        ids = [f'serann-{i}' for i in mine]
+        ids = [f'serann-{rank}-{i}' for i in mine]
         info = pd.DataFrame({'genotype': [data['encodings'][i] for i in mine], 'source_code': [pop[i][0] for i in mine]}, index=ids)
         barrier()
         t0 = time.perf_counter()

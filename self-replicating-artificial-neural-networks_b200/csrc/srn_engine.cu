@@ -100,6 +100,11 @@ struct srn_engine {
     std::vector<ProfRec*> prof;
     srn_config cfg{};
     cudaStream_t stream = 0;
+    cudaStream_t cur = 0;                 // stream the LAUNCH macros use (main stream or one of the side streams)
+    static constexpr int NSIDE = 3;
+    cudaStream_t side[NSIDE] = {};        // independent launch buckets of one depth level overlap their tails on these
+    cudaEvent_t ev_fork = nullptr, ev_join[NSIDE] = {};
+    bool multi_stream = true;
     int num_sms = 148;
     std::vector<Im2colGeo> geos;         // shared im2col buffers of the first layers (one per window geometry)
     __half* im2col = nullptr;
@@ -139,8 +144,8 @@ struct srn_engine {
     do {                                                                                           \
         if (grid_nonzero(grid)) {                                                                          \
             ProfRec* pr_ = h->profiling ? prof_begin(h, (cat)) : nullptr;                          \
-            kern<<<(grid), (block), 0, h->stream>>>(__VA_ARGS__);                                  \
-            if (pr_) cudaEventRecord(pr_->b, h->stream);                                           \
+            kern<<<(grid), (block), 0, h->cur>>>(__VA_ARGS__);                                     \
+            if (pr_) cudaEventRecord(pr_->b, h->cur);                                           \
             g_launches.fetch_add(1, std::memory_order_relaxed);                                    \
         }                                                                                          \
     } while (0)
@@ -153,8 +158,8 @@ static inline bool grid_nonzero(const dim3& g) { return g.x > 0 && g.y > 0 && g.
     do {                                                                                           \
         if (grid_nonzero(grid)) {                                                                  \
             ProfRec* pr_ = h->profiling ? prof_begin(h, (cat)) : nullptr;                          \
-            kern<<<(grid), (block), (smem), h->stream>>>(__VA_ARGS__);                             \
-            if (pr_) cudaEventRecord(pr_->b, h->stream);                                           \
+            kern<<<(grid), (block), (smem), h->cur>>>(__VA_ARGS__);                                \
+            if (pr_) cudaEventRecord(pr_->b, h->cur);                                           \
             g_launches.fetch_add(1, std::memory_order_relaxed);                                    \
         }                                                                                          \
     } while (0)
@@ -164,7 +169,7 @@ static ProfRec* prof_begin(srn_engine* h, int cat) {
     r->cat = cat;
     cudaEventCreate(&r->a);
     cudaEventCreate(&r->b);
-    cudaEventRecord(r->a, h->stream);
+    cudaEventRecord(r->a, h->cur);
     h->prof.push_back(r);
     return r;
 }
@@ -211,6 +216,13 @@ extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
     srn_engine* h = new srn_engine();
     h->cfg = *cfg;
     CK(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
+    for (int i = 0; i < srn_engine::NSIDE; ++i) {
+        CK(cudaStreamCreateWithFlags(&h->side[i], cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&h->ev_join[i], cudaEventDisableTiming));
+    }
+    CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+    h->multi_stream = getenv("SRN_SINGLE_STREAM") == nullptr;
+    h->cur = h->stream;
     h->xe = cfg->image_h * cfg->image_w;
     h->G = cfg->genotype_size;
     h->ncls = cfg->n_classes;
@@ -227,6 +239,8 @@ extern "C" void srn_destroy(srn_engine* h) {
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
     free_population(h);
+    for (int i = 0; i < srn_engine::NSIDE; ++i) { if (h->side[i]) cudaStreamDestroy(h->side[i]); if (h->ev_join[i]) cudaEventDestroy(h->ev_join[i]); }
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     for (int s = 0; s < 2; ++s) { cudaFree(h->x[s]); cudaFree(h->y[s]); cudaFree(h->gb[s]); }
     cudaFree(h->xin); cudaFree(h->gin); cudaFree(h->lab);
     delete h;
@@ -586,16 +600,31 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
             if (g.mode == 1)
                 for (auto& q : g.h) { q.in = h->geos[q.coff].out; q.coff = 0; }
     }
-    // backward runs the groups in reverse: the first writer of each input gradient overwrites, later ones add
+    // backward walks the depth levels from the deepest; inside a level the buckets of first consumers (ordinal 0) run
+    // first, concurrently, then the others one by one (see backward_pass).  In that order the first writer of each
+    // input gradient overwrites and every later one adds.
     {
         std::map<const __half*, bool> written;
-        for (int gi = (int)h->groups.size() - 1; gi >= 0; --gi)
-            for (auto& p : h->groups[gi].h) {
+        auto visit = [&](Group& g) {
+            for (auto& p : g.h) {
                 if (!p.din) continue;
                 bool& w = written[p.din];
                 p.din_acc = w ? 1 : 0;
                 w = true;
             }
+        };
+        int gi = (int)h->groups.size() - 1;
+        while (gi >= 0) {
+            int ge = gi;
+            std::vector<Group*> later;
+            while (ge >= 0 && h->groups[ge].depth == h->groups[gi].depth) {
+                Group& g = h->groups[ge];
+                if (g.mode & 1) { if (g.ordinal == 0) visit(g); else later.push_back(&g); }
+                --ge;
+            }
+            for (Group* g : later) visit(*g);
+            gi = ge;
+        }
     }
     for (auto& g : h->groups) {
         CK(cudaMalloc(&g.d, g.h.size() * sizeof(Prob)));
@@ -800,6 +829,67 @@ static void launch_dgrad_cfg(srn_engine* h, Group& g, Cached* c, int nb) {
            g.d, c->prefix[P_DGRAD], (int)g.h.size(), nb);
 }
 
+// Runs independent launch buckets: bucket 0 on the main stream, the others round-robin on the side streams, fenced
+// by a fork event before and join events after.
+template <class F>
+static int run_level(srn_engine* h, std::vector<Group*>& level, F&& body) {
+    if (level.empty()) return SRN_OK;
+    const bool fan = h->multi_stream && level.size() > 1;
+    if (fan) {
+        cudaEventRecord(h->ev_fork, h->stream);
+        for (int i = 0; i < srn_engine::NSIDE; ++i) cudaStreamWaitEvent(h->side[i], h->ev_fork, 0);
+    }
+    bool used[srn_engine::NSIDE] = {};
+    int rc = SRN_OK;
+    for (size_t k = 0; k < level.size() && !rc; ++k) {
+        const int lane = fan ? (int)(k % (srn_engine::NSIDE + 1)) : 0;
+        h->cur = lane == 0 ? h->stream : h->side[lane - 1];
+        if (lane) used[lane - 1] = true;
+        rc = body(*level[k]);
+    }
+    h->cur = h->stream;
+    for (int i = 0; i < srn_engine::NSIDE; ++i)
+        if (used[i]) { cudaEventRecord(h->ev_join[i], h->side[i]); cudaStreamWaitEvent(h->stream, h->ev_join[i], 0); }
+    return rc;
+}
+
+static int fwd_group(srn_engine* h, Group& g, int nb, const Inputs& I, bool training) {
+    Cached* c;
+    int rc = plan_for(h, g, nb, &c);
+    if (rc) return rc;
+    const int np = (int)g.h.size();
+    switch (g.kind) {
+        case SRN_KIND_DENSE:
+        case SRN_KIND_CONV:
+            if (g.tc) {
+                const int BN = TC_BN[g.cfgF];
+                if (g.tc == 1) LAUNCH_TC(SRN_CAT_GEMM_FWD, TC_FWD, false, P_FWD, BN);
+                else LAUNCH_TC(SRN_CAT_GEMM_FWD, TC_FWD, true, P_FWD, BN);
+                break;
+            }
+            if (g.cfgF == 0) launch_fwd_cfg<0>(h, g, c, nb, I);
+            else if (g.cfgF == 1) launch_fwd_cfg<1>(h, g, c, nb, I);
+            else launch_fwd_cfg<2>(h, g, c, nb, I);
+            break;
+        case SRN_KIND_MAXPOOL:
+            LAUNCH(SRN_CAT_POOL, k_maxpool_fwd, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I);
+            break;
+        case SRN_KIND_BN:
+            if (training) {
+                LAUNCH(SRN_CAT_BN, k_bn_partial, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I, 0);
+                LAUNCH(SRN_CAT_BN, k_bn_finalize_fwd, np, 128, g.d, nb, I);
+            } else {
+                LAUNCH(SRN_CAT_BN, k_bn_prepare_infer, np, 128, g.d);
+            }
+            LAUNCH(SRN_CAT_BN, k_bn_apply, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I);
+            break;
+        case SRN_KIND_CONCAT:
+            LAUNCH(SRN_CAT_CONCAT, k_copy, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I, 0);
+            break;
+    }
+    return SRN_OK;
+}
+
 static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
     const int mode = (I.x_istride == 0 && I.g_istride == 0) ? 1 : 2;
     if (mode == 1) {
@@ -811,82 +901,74 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
             LAUNCH(SRN_CAT_GATHER, k_im2col, (unsigned)((total + 255) / 256), 256, e, nb);
         }
     }
-    for (auto& g : h->groups) {
-        if (!(g.mode & mode)) continue;
-        Cached* c;
-        int rc = plan_for(h, g, nb, &c);
-        if (rc) return rc;
-        const int np = (int)g.h.size();
-        switch (g.kind) {
-            case SRN_KIND_DENSE:
-            case SRN_KIND_CONV:
-                if (g.tc) {
-                    const int BN = TC_BN[g.cfgF];
-                    if (g.tc == 1) LAUNCH_TC(SRN_CAT_GEMM_FWD, TC_FWD, false, P_FWD, BN);
-                    else LAUNCH_TC(SRN_CAT_GEMM_FWD, TC_FWD, true, P_FWD, BN);
-                    break;
-                }
-                if (g.cfgF == 0) launch_fwd_cfg<0>(h, g, c, nb, I);
-                else if (g.cfgF == 1) launch_fwd_cfg<1>(h, g, c, nb, I);
-                else launch_fwd_cfg<2>(h, g, c, nb, I);
-                break;
-            case SRN_KIND_MAXPOOL:
-                LAUNCH(SRN_CAT_POOL, k_maxpool_fwd, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I);
-                break;
-            case SRN_KIND_BN:
-                if (training) {
-                    LAUNCH(SRN_CAT_BN, k_bn_partial, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I, 0);
-                    LAUNCH(SRN_CAT_BN, k_bn_finalize_fwd, np, 128, g.d, nb, I);
-                } else {
-                    LAUNCH(SRN_CAT_BN, k_bn_prepare_infer, np, 128, g.d);
-                }
-                LAUNCH(SRN_CAT_BN, k_bn_apply, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I);
-                break;
-            case SRN_KIND_CONCAT:
-                LAUNCH(SRN_CAT_CONCAT, k_copy, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I, 0);
-                break;
+    // buckets of one depth level are independent: spread them over the side streams so that the tail of one
+    // persistent launch overlaps the ramp-up of the next; levels are separated by events
+    size_t gi = 0;
+    while (gi < h->groups.size()) {
+        size_t ge = gi;
+        std::vector<Group*> level;
+        while (ge < h->groups.size() && h->groups[ge].depth == h->groups[gi].depth) {
+            if (h->groups[ge].mode & mode) level.push_back(&h->groups[ge]);
+            ++ge;
         }
+        int rc = run_level(h, level, [&](Group& g) { return fwd_group(h, g, nb, I, training); });
+        if (rc) return rc;
+        gi = ge;
+    }
+    return SRN_OK;
+}
+
+static int bwd_group(srn_engine* h, Group& g, int nb, const Inputs& I) {
+    Cached* c;
+    int rc = plan_for(h, g, nb, &c);
+    if (rc) return rc;
+    const int np = (int)g.h.size();
+    switch (g.kind) {
+        case SRN_KIND_DENSE:
+        case SRN_KIND_CONV:
+            LAUNCH(SRN_CAT_ACT_BWD, k_act_bwd_bias, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb);
+            if (g.tc) {
+                const int BNf = TC_BN[g.cfgF], BNc = TC_BN[g.cfgC];
+                if (g.tc == 1) LAUNCH_TC(SRN_CAT_GEMM_WGRAD, TC_WGRAD, false, P_WGRAD, BNf);
+                else LAUNCH_TC(SRN_CAT_GEMM_WGRAD, TC_WGRAD, true, P_WGRAD, BNf);
+                LAUNCH_TC(SRN_CAT_GEMM_DGRAD, TC_DGRAD, false, P_DGRAD, BNc);
+                break;
+            }
+            LAUNCH(SRN_CAT_GEMM_WGRAD, k_conv_wgrad, c->total[P_WGRAD], SIMT_THREADS, g.d, c->prefix[P_WGRAD], np, nb, I);
+            if (g.cfgC == 0) launch_dgrad_cfg<0>(h, g, c, nb);
+            else if (g.cfgC == 1) launch_dgrad_cfg<1>(h, g, c, nb);
+            else launch_dgrad_cfg<2>(h, g, c, nb);
+            break;
+        case SRN_KIND_MAXPOOL:
+            LAUNCH(SRN_CAT_POOL, k_maxpool_bwd, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I);
+            break;
+        case SRN_KIND_BN:
+            LAUNCH(SRN_CAT_BN, k_bn_partial, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I, 1);
+            LAUNCH(SRN_CAT_BN, k_bn_finalize_bwd, np, 128, g.d, nb);
+            LAUNCH(SRN_CAT_BN, k_bn_bwd_apply, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I);
+            break;
+        case SRN_KIND_CONCAT:
+            LAUNCH(SRN_CAT_CONCAT, k_copy, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I, 1);
+            break;
     }
     return SRN_OK;
 }
 
 static int backward_pass(srn_engine* h, int nb, const Inputs& I) {
     const int mode = (I.x_istride == 0 && I.g_istride == 0) ? 1 : 2;
-    for (int gi = (int)h->groups.size() - 1; gi >= 0; --gi) {
-        Group& g = h->groups[gi];
-        if (!(g.mode & mode)) continue;
-        Cached* c;
-        int rc = plan_for(h, g, nb, &c);
-        if (rc) return rc;
-        const int np = (int)g.h.size();
-        switch (g.kind) {
-            case SRN_KIND_DENSE:
-            case SRN_KIND_CONV:
-                LAUNCH(SRN_CAT_ACT_BWD, k_act_bwd_bias, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb);
-                if (g.tc) {
-                    const int BNf = TC_BN[g.cfgF], BNc = TC_BN[g.cfgC];
-                    if (g.tc == 1) LAUNCH_TC(SRN_CAT_GEMM_WGRAD, TC_WGRAD, false, P_WGRAD, BNf);
-                    else LAUNCH_TC(SRN_CAT_GEMM_WGRAD, TC_WGRAD, true, P_WGRAD, BNf);
-                    LAUNCH_TC(SRN_CAT_GEMM_DGRAD, TC_DGRAD, false, P_DGRAD, BNc);
-                    break;
-                }
-                LAUNCH(SRN_CAT_GEMM_WGRAD, k_conv_wgrad, c->total[P_WGRAD], SIMT_THREADS, g.d, c->prefix[P_WGRAD], np, nb, I);
-                if (g.cfgC == 0) launch_dgrad_cfg<0>(h, g, c, nb);
-                else if (g.cfgC == 1) launch_dgrad_cfg<1>(h, g, c, nb);
-                else launch_dgrad_cfg<2>(h, g, c, nb);
-                break;
-            case SRN_KIND_MAXPOOL:
-                LAUNCH(SRN_CAT_POOL, k_maxpool_bwd, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I);
-                break;
-            case SRN_KIND_BN:
-                LAUNCH(SRN_CAT_BN, k_bn_partial, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I, 1);
-                LAUNCH(SRN_CAT_BN, k_bn_finalize_bwd, np, 128, g.d, nb);
-                LAUNCH(SRN_CAT_BN, k_bn_bwd_apply, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I);
-                break;
-            case SRN_KIND_CONCAT:
-                LAUNCH(SRN_CAT_CONCAT, k_copy, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I, 1);
-                break;
+    int gi = (int)h->groups.size() - 1;
+    while (gi >= 0) {
+        int ge = gi;
+        std::vector<Group*> first, later;      // consumers that overwrite an input gradient / that add to it afterwards
+        while (ge >= 0 && h->groups[ge].depth == h->groups[gi].depth) {
+            Group& g = h->groups[ge];
+            if (g.mode & mode) (g.ordinal == 0 ? first : later).push_back(&g);
+            --ge;
         }
+        int rc = run_level(h, first, [&](Group& g) { return bwd_group(h, g, nb, I); });
+        if (rc) return rc;
+        for (Group* g : later) { rc = bwd_group(h, *g, nb, I); if (rc) return rc; }    // accumulation order matters
+        gi = ge;
     }
     return SRN_OK;
 }
