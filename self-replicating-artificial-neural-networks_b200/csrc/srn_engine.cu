@@ -101,7 +101,7 @@ struct srn_engine {
     srn_config cfg{};
     cudaStream_t stream = 0;
     cudaStream_t cur = 0;                 // stream the LAUNCH macros use (main stream or one of the side streams)
-    static constexpr int NSIDE = 3;
+    static constexpr int NSIDE = 7;
     cudaStream_t side[NSIDE] = {};        // independent launch buckets of one depth level overlap their tails on these
     cudaEvent_t ev_fork = nullptr, ev_join[NSIDE] = {};
     bool multi_stream = true;
