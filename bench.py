@@ -284,10 +284,15 @@ def main():
     roofline = {'bound': 'tensor', 'kernel': top, 'achieved': achieved, 'peak': tf_sust, 'unit': 'TFLOP/s',
                 'frac': achieved / tf_sust, 'traffic': traffic, 'peak_source': f'{peak_kind} sustained bf16/fp16 dense',
                 'launches_per_step': top_launches, 'ms_per_step_in_kernel': top_ms,
+                'timing': 'CUDA events around every launch of the category, profiled with the launches serialised on one stream',
                 'share_of_step': shares,
                 'note': 'population-grouped implicit GEMM on tcgen05 (fp16 operands, fp32 TMEM accumulators, cp.async-gathered '
                         'operands); achieved = algorithmic FLOPs of this pass over all individuals / its event-timed device time. '
                         'The problems are small-N and gather-bound, far from the dense-GEMM peak: see DESIGN.md section 4'}
+    roofline['step'] = {'algorithmic_TFLOP_per_step': sum(flops.values()) / 1e12,
+                        'achieved_TFLOPs': sum(flops.values()) / (dev_s / args.steps) / 1e12 * (total_ind / len(irs)),
+                        'frac_of_tensor_peak': sum(flops.values()) / (dev_s / args.steps) / 1e12 * (total_ind / len(irs)) / (tf_sust * world),
+                        'note': 'all GEMM passes of one step over the measured step time (launches overlap on several streams)'}
     hb = hbm_bytes_per_step(irs, BATCH)
     roofline['hbm_kernels'] = {k: {'achieved_GBs': hb[k] / (prof[k][0] / 2.0 / 1000.0) / 1e9 if prof[k][1] else None,
                                    'peak_GBs': hbm_peak, 'frac': (hb[k] / (prof[k][0] / 2.0 / 1000.0) / 1e9 / hbm_peak) if prof[k][1] else None}

@@ -1318,6 +1318,8 @@ extern "C" int srn_profile(srn_engine* h, int32_t on) {
     for (ProfRec* r : h->prof) { cudaEventDestroy(r->a); cudaEventDestroy(r->b); delete r; }
     h->prof.clear();
     h->profiling = on != 0;
+    // per-launch event times only mean something when launches do not overlap: profile on one stream
+    h->multi_stream = !h->profiling && getenv("SRN_SINGLE_STREAM") == nullptr;
     return SRN_OK;
 }
 
