@@ -511,7 +511,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             int p = 0;
             for (int j = 0; j < my_tiles; ++j) {
                 const int acc = j & 1;
-                if (j >= 2) mbar_wait_relaxed(sTEmpty + acc * 8, (uint32_t)((j / 2 - 1) & 1));   // epilogue drained this accumulator
+                if (j >= 2) mbar_wait(sTEmpty + acc * 8, (uint32_t)((j / 2 - 1) & 1));   // epilogue drained this accumulator
                 const uint32_t tacc = tmem + (uint32_t)(acc * acc_cols);
                 int nk = 1; uint32_t idesc = 0;
                 for (int kb = 0; kb < nk; ++kb, ++p) {
@@ -543,6 +543,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             const uint32_t trow = tacc + ((uint32_t)(ewarp * 32) << 16);
             if (MODE == TC_FWD) {
                 const int HoWo = p.Ho * p.Wo;
+                const __half* bias = p.bias; const int act = p.act;
                 __half* orow = nullptr;
                 if (mrow < T.Mrows) {
                     const int b = fdiv(mrow, T.fd_rows), rem = mrow - b * HoWo;
@@ -556,11 +557,12 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                     for (int h8 = 0; h8 < 2; ++h8) {
                         const int n = n0 + cb + h8 * 8;
                         if (n >= Ncols) break;
+                        const Half8 bv = ld8(bias + n);      // bias arrays are padded to 8 elements in the arena
                         Half8 o;
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
                             float z = 0.f;
-                            if (n + j < Ncols) z = act_forward(rh(rh(v[h8 * 8 + j]) + __half2float(p.bias[n + j])), p.act);
+                            if (n + j < Ncols) z = act_forward(rh(rh(v[h8 * 8 + j]) + __half2float(bv.v[j])), act);
                             o.v[j] = __float2half_rn(z);
                         }
                         st8(orow + n, o);
@@ -604,12 +606,18 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                     float v[16];
                     tmem_ld16(trow + cb, v);
                     if (!grow) continue;
+                    if (single && n0 + cb + 16 <= p.ldw) {   // whole chunk inside the padded row: pad columns get exact zeros
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const int f = n0 + cb + j;
-                        if (f < Ncols) {
-                            if (single) grow[f] = v[j];
-                            else if (v[j] != 0.f) atomicAdd(&grow[f], v[j]);
+                        for (int j = 0; j < 16; j += 4)
+                            *reinterpret_cast<float4*>(grow + n0 + cb + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const int f = n0 + cb + j;
+                            if (f < Ncols) {
+                                if (single) grow[f] = v[j];
+                                else if (v[j] != 0.f) atomicAdd(&grow[f], v[j]);
+                            }
                         }
                     }
                 }
@@ -617,7 +625,9 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
         };
         for (int j = 0; j < my_tiles; ++j) {
             const int acc = j & 1;
-            mbar_wait_relaxed(sTFull + acc * 8, (uint32_t)((j / 2) & 1));
+            // long tiles: back off while waiting so that the spin does not take issue slots from the loaders
+            if (ring[j % TC_RING].nk > 32) mbar_wait_relaxed(sTFull + acc * 8, (uint32_t)((j / 2) & 1));
+            else mbar_wait(sTFull + acc * 8, (uint32_t)((j / 2) & 1));
             tc_fence_after();
             epilogue(ring[j % TC_RING], tmem + (uint32_t)(acc * acc_cols), ewarp);
             tc_fence_before();
