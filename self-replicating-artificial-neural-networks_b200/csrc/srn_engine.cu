@@ -93,10 +93,11 @@ struct Group {
 
 using namespace srn;
 
-struct ProfRec { int cat; cudaEvent_t a, b; };
+struct ProfRec { int cat; int group; cudaEvent_t a, b; };
 
 struct srn_engine {
     bool profiling = false;
+    int cur_group = -1;                   // launch bucket being issued (profiling detail)
     std::vector<ProfRec*> prof;
     srn_config cfg{};
     cudaStream_t stream = 0;
@@ -167,6 +168,7 @@ static inline bool grid_nonzero(const dim3& g) { return g.x > 0 && g.y > 0 && g.
 static ProfRec* prof_begin(srn_engine* h, int cat) {
     ProfRec* r = new ProfRec();
     r->cat = cat;
+    r->group = h->cur_group;
     cudaEventCreate(&r->a);
     cudaEventCreate(&r->b);
     cudaEventRecord(r->a, h->cur);
@@ -855,6 +857,7 @@ static int run_level(srn_engine* h, std::vector<Group*>& level, F&& body) {
 
 static int fwd_group(srn_engine* h, Group& g, int nb, const Inputs& I, bool training) {
     Cached* c;
+    h->cur_group = (int)(&g - h->groups.data());
     int rc = plan_for(h, g, nb, &c);
     if (rc) return rc;
     const int np = (int)g.h.size();
@@ -920,6 +923,7 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
 
 static int bwd_group(srn_engine* h, Group& g, int nb, const Inputs& I) {
     Cached* c;
+    h->cur_group = (int)(&g - h->groups.data());
     int rc = plan_for(h, g, nb, &c);
     if (rc) return rc;
     const int np = (int)g.h.size();
@@ -1319,7 +1323,7 @@ extern "C" int srn_profile(srn_engine* h, int32_t on) {
     h->prof.clear();
     h->profiling = on != 0;
     // per-launch event times only mean something when launches do not overlap: profile on one stream
-    h->multi_stream = !h->profiling && getenv("SRN_SINGLE_STREAM") == nullptr;
+    h->multi_stream = (!h->profiling || on == 2) && getenv("SRN_SINGLE_STREAM") == nullptr;      // on == 2: timeline of the overlapped schedule
     return SRN_OK;
 }
 
@@ -1335,4 +1339,54 @@ extern "C" int srn_profile_read(srn_engine* h, float* ms, int32_t* launches) {
         launches[r->cat] += 1;
     }
     return SRN_OK;
+}
+
+// Per-launch detail of the last profiled region (debug hook): ms[i] = event time of launch i, info[8 i ..] =
+// {category, bucket, kind, tc, BN forward, BN dgrad, problems, depth}, start[i] = offset of its start from the first
+// launch (meaningful across streams: srn_profile(h, 2) keeps the side streams on), work[3 i ..] = {FLOPs of one GEMM pass over the
+// bucket's real (unpadded) shapes, activation bytes read, activation bytes written} at batch nb.
+extern "C" int srn_debug_profile_detail(srn_engine* h, int32_t nb, int32_t cap, float* ms, float* start, int32_t* info, double* work) {
+    if (!h || !ms || !start || !info || !work) return -1;
+    if (cudaSetDevice(h->cfg.device) != cudaSuccess || cudaStreamSynchronize(h->stream) != cudaSuccess) return -1;
+    int n = 0;
+    for (ProfRec* r : h->prof) {
+        if (n >= cap) break;
+        float t = 0.f;
+        cudaEventElapsedTime(&t, r->a, r->b);
+        ms[n] = t;
+        start[n] = 0.f;
+        cudaEventElapsedTime(&start[n], h->prof.front()->a, r->a);      // offset from the first launch of the region
+        int32_t* o = info + 8 * (size_t)n;
+        double* w = work + 3 * (size_t)n;
+        o[0] = r->cat; o[1] = r->group;
+        for (int k = 2; k < 8; ++k) o[k] = -1;
+        w[0] = w[1] = w[2] = 0.0;
+        if (r->group >= 0 && r->group < (int)h->groups.size()) {
+            const Group& g = h->groups[r->group];
+            o[2] = g.kind; o[3] = g.tc; o[4] = g.cfgF; o[5] = g.cfgC; o[6] = (int)g.h.size(); o[7] = g.depth;
+            for (const Prob& p : g.h) {
+                const double in_rows = (double)nb * p.H * p.W, out_rows = (double)nb * p.Ho * p.Wo;
+                if (g.kind == SRN_KIND_DENSE || g.kind == SRN_KIND_CONV)
+                    w[0] += 2.0 * out_rows * p.kh * p.kw * p.C * p.F;
+                w[1] += in_rows * p.Cs * 2.0;
+                w[2] += out_rows * (g.kind == SRN_KIND_DENSE || g.kind == SRN_KIND_CONV ? p.Fs : p.Cs) * 2.0;
+            }
+        }
+        ++n;
+    }
+    return n;
+}
+
+// Shapes of the problems of one launch bucket (debug hook): 16 ints per problem
+// {H, W, C, Cs, Ho, Wo, F, Fs, kh, kw, sh, sw, act, din_acc, individual, has din}.
+extern "C" int srn_debug_group_probs(srn_engine* h, int32_t group, int32_t cap, int32_t* out) {
+    if (!h || !out || group < 0 || group >= (int)h->groups.size()) return -1;
+    int n = 0;
+    for (const Prob& p : h->groups[group].h) {
+        if (n >= cap) break;
+        int32_t* o = out + 16 * (size_t)n++;
+        o[0] = p.H; o[1] = p.W; o[2] = p.C; o[3] = p.Cs; o[4] = p.Ho; o[5] = p.Wo; o[6] = p.F; o[7] = p.Fs;
+        o[8] = p.kh; o[9] = p.kw; o[10] = p.sh; o[11] = p.sw; o[12] = p.act; o[13] = p.din_acc; o[14] = p.indiv; o[15] = p.din != nullptr;
+    }
+    return n;
 }

@@ -43,11 +43,12 @@ enum { TC_FWD = 0, TC_DGRAD = 1, TC_WGRAD = 2 };
 
 constexpr int TC_RING = 32;           // tile descriptors in shared memory: epilogue <= 10 tiles behind the loader, 4 ahead
 constexpr int TC_DESC_AHEAD = 4;
+constexpr int TC_LUT = 512;            // 16-byte k chunks per lookup table: reductions up to 4096 elements, longer ones compute on the fly
 // Pipeline depth per N tile: BN <= 64 keeps two CTAs per SM (4 stages each), wider tiles take the SM alone with as
 // many stages as fit.  Loaders never wait for their own copies: completion is signalled to the stage's "full"
 // barrier by the copy engine itself (cp.async.mbarrier.arrive.noinc), so up to `stages` k-blocks are in flight.
 __host__ __device__ inline int tc_stages(int BN) { return BN <= 64 ? 4 : (BN <= 128 ? 3 : 4); }
-__host__ __device__ inline int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + BN * TC_BK * 2) + 256 + TC_RING * 256; }
+__host__ __device__ inline int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + BN * TC_BK * 2) + 256 + TC_RING * 256 + 2 * TC_LUT * 8; }
 __host__ __device__ inline int tc_acc_cols(int BN) { return BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256)); }
 __host__ __device__ inline int tc_tmem_cols(int BN) { return 2 * tc_acc_cols(BN); }     // two accumulators
 __host__ __device__ inline int round_up8(int v) { return (v + 7) & ~7; }
@@ -70,24 +71,13 @@ __host__ __device__ inline int tc_tiles_wgrad(const Prob& p, int nb, int BN) {
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // 16-byte asynchronous copy; when !valid the destination is zero-filled (src-size 0) and src is not read, but it
-// must still be a mapped address: callers pass clamped, always-valid pointers instead of selecting a dummy
+// must still be a mapped address: callers pass offset 0 of the tensor then.  ptxas folds the size select into the
+// zero-fill predicate operand of one LDGSTS.
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %2, 0;\n"
-        "@p cp.async.cg.shared.global [%0], [%1], 16;\n"
-        "@!p cp.async.cg.shared.global [%0], [%1], 16, 0;\n"
-        "}\n" ::"r"(dst), "l"(src), "r"((int)valid) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(src), "r"(valid ? 16u : 0u) : "memory");
 }
 __device__ __forceinline__ void cp_async16_ca(uint32_t dst, const void* src, bool valid) {   // keeps the line in L1 (im2col reuse)
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %2, 0;\n"
-        "@p cp.async.ca.shared.global [%0], [%1], 16;\n"
-        "@!p cp.async.ca.shared.global [%0], [%1], 16, 0;\n"
-        "}\n" ::"r"(dst), "l"(src), "r"((int)valid) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(src), "r"(valid ? 16u : 0u) : "memory");
 }
 // arrive on an mbarrier once all cp.async issued so far by this thread have landed (no wait in the thread)
 __device__ __forceinline__ void cp_async_arrive_noinc(uint32_t bar) {
@@ -106,16 +96,18 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void loaders_sync() { asm volatile("bar.sync 1, 256;\n" ::: "memory"); }   // the loader warps only
+// try_wait suspends the thread until the phase completes or the time hint (ns) runs out, so a long hint means few
+// polls: every poll is a shared-memory access that competes with the copies and the operand reads
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n"
         ".reg .pred P1;\n"
         "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, %2;\n"
         "@P1 bra WAIT_DONE;\n"
         "bra WAIT_LOOP;\n"
         "WAIT_DONE:\n"
-        "}\n" ::"r"(bar), "r"(parity) : "memory");
+        "}\n" ::"r"(bar), "r"(parity), "r"(20000u) : "memory");
 }
 // same, for waits that last a whole tile (epilogue, accumulator hand-back): back off so that the spinning warps
 // do not take issue slots from the loaders
@@ -248,6 +240,24 @@ inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool
     t.fd_kw = make_fastdiv(p.kw);
 }
 
+// What the k index of a 16-byte chunk means for a problem: (window position, channel) of the padded reduction space.
+struct KGeo { int cs, kw, ww, C, klim, bias; FastDiv fdc, fdkw; bool dense; };
+// Table entry of chunk `chunk` (k = 8 * chunk .. + 7).  y: bit 31 = inside the reduction; x = byte offset to add to the
+// row's base.  FWD: x = ((ki * W + kj) * Cs + c) * 2, y bits 0-19 = weight row ij * C + c, bits 20-23 = real channels in
+// the chunk.  DGRAD: x = (f - (ki * Wo + kj) * Fs + bias) * 2, y bits 0-7 = ki, 8-15 = kj, 16-30 = f / 8.
+template <int MODE>
+__device__ __forceinline__ int2 tc_k_entry(const KGeo& g, int chunk) {
+    const int k = chunk * 8;
+    if (k >= g.klim) return make_int2(0, 0);
+    int ij = 0, cp = k, ki = 0, kj = 0;
+    if (!g.dense) { ij = fdiv(k, g.fdc); cp = k - ij * g.cs; ki = fdiv(ij, g.fdkw); kj = ij - ki * g.kw; }
+    if (MODE == TC_DGRAD)
+        return make_int2(2 * (cp - (ki * g.ww + kj) * g.cs + g.bias),
+                         (int)(0x80000000u | (uint32_t)ki | ((uint32_t)kj << 8) | ((uint32_t)(cp >> 3) << 16)));
+    const int nvalid = min(8, max(0, g.C - cp));
+    return make_int2(2 * ((ki * g.ww + kj) * g.cs + cp), (int)(0x80000000u | (uint32_t)(ij * g.C + cp) | ((uint32_t)nvalid << 20)));
+}
+
 template <int MODE, bool SCALAR_A>
 static __global__ void __launch_bounds__(TC_THREADS)
 k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I) {
@@ -266,8 +276,10 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
     const uint32_t sTFull = sEmpty + TC_MAX_STAGES * 8;
     const uint32_t sTEmpty = sTFull + 2 * 8;
     const uint32_t sSlot = sTEmpty + 2 * 8;
+    const uint32_t sLut = sFull + 256;                    // two k-chunk tables of TC_LUT entries (this tile, next tile)
     TcTile* ring = reinterpret_cast<TcTile*>(sgen + (sRing - sbase));
     volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(sgen + (sSlot - sbase));
+    int2* lut = reinterpret_cast<int2*>(sgen + (sLut - sbase));
     const int acc_cols = tc_acc_cols(BN), tmem_cols = tc_tmem_cols(BN);
 
     const int G = gridDim.x, cta = blockIdx.x;
@@ -301,34 +313,59 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
         // =================================================================== loaders (8 warps)
         // A tile: 128 (m or kk) x 64 k in 16-byte chunks = 1024 chunks, 4 per thread; B tile: BN x 64, BN/32 per
         // thread.  A warp covers 8 rows x 4 consecutive chunks per item (64 contiguous bytes per row).
-        // Per-tile loader state lives in registers: everything the k loop needs is copied out of the descriptor
-        // once per tile, and gather pointers are clamped to mapped addresses so that an out-of-range chunk only
-        // changes the copy's predicate (zero fill), never its address computation.
-        const __half* l_in = nullptr; int l_in_bs = 0;
-        const __half* a_row[2] = {nullptr, nullptr}; bool a_ok[2] = {false, false};   // FWD: this thread's two im2col rows
-        int a_b[2], a_h[2], a_w[2];      // DGRAD: input position of this thread's two rows (a_b < 0: out of range)
+        // Per-tile loader state lives in registers; what depends only on k (window offset, weight row, validity of a
+        // 16-byte k chunk) comes from a per-tile lookup table in shared memory that the loaders fill one tile ahead,
+        // so the k loop is address adds, predicates and copies.  All gather offsets are 32-bit byte offsets inside
+        // one tensor; an out-of-range chunk gets offset 0 and a zero-filling copy.
+        const char* l_in = nullptr; int l_in_bs = 0;
+        const char* t_w = nullptr; const char* t_gout = nullptr;
+        uint32_t a_off[2] = {0, 0}; bool a_ok[2] = {false, false};   // FWD: this thread's two im2col rows
+        int a_h[2] = {0, 0}, a_w[2] = {0, 0}, a_base[2] = {0, 0};    // DGRAD: input position of its two rows, biased offset
         int w_koff[4]; bool w_kok[4];    // WGRAD (vector): offsets of this thread's four kk chunks inside the window
-        const __half* t_w = nullptr; const __half* t_gout = nullptr;
-        int t_ldw = 0, t_C = 0, t_Cs = 1, t_Fs = 1, t_kw = 1, t_W = 1, t_Wo = 1, t_Ho = 1, t_sh = 1, t_sw = 1;
-        int t_Kf = 0, t_Kd = 0, t_n0 = 0, t_out_bs = 0, t_HoWo = 1, t_r0 = 0, t_r1 = 0, t_m0 = 0;
-        bool t_dense = true;
-        FastDiv t_fdc{}, t_fdkw{}, t_fdrows{}, t_fdw{};
+        int t_ldw = 0, t_Cs = 1, t_Fs = 1, t_kw = 1, t_W = 1, t_Wo = 1, t_Ho = 1, t_sh = 1, t_sw = 1;
+        int t_Kf = 0, t_n0 = 0, t_out_bs = 0, t_HoWo = 1, t_r0 = 0, t_r1 = 0, t_m0 = 0, t_C = 0, t_Cldw = 0, t_C8 = 0;
+        bool t_lut = false, t_s1 = true;
+        KGeo geo{};
+        FastDiv t_fdrows{}, t_fdw{};
         int lj = 0, lnk = 0;
+        auto geo_of = [&](const TcTile& T) {
+            const Prob& p = T.p;
+            KGeo g;
+            const int KK = p.kh * p.kw;
+            g.dense = KK == 1; g.kw = p.kw; g.C = p.C; g.fdc = T.fd_c; g.fdkw = T.fd_kw;
+            if (MODE == TC_DGRAD) { g.cs = p.Fs; g.ww = p.Wo; g.klim = KK * p.Fs; g.bias = ((p.kh - 1) * p.Wo + (p.kw - 1)) * p.Fs; }
+            else { g.cs = p.Cs; g.ww = p.W; g.klim = SCALAR_A ? KK : KK * p.Cs; g.bias = 0; }
+            return g;
+        };
+        auto fill_lut = [&](int j) {       // table of tile j -> buffer j & 1 (FWD and DGRAD only)
+            if (MODE == TC_WGRAD || SCALAR_A || j >= my_tiles) return;
+            const TcTile& T = ring[j % TC_RING];
+            const int chunks = T.nk * 8;
+            if (chunks > TC_LUT) return;
+            const KGeo g = geo_of(T);
+            int2* L = lut + (j & 1) * TC_LUT;
+            for (int c = tid; c < chunks; c += TC_LOADERS) L[c] = tc_k_entry<MODE>(g, c);
+        };
         auto loader_enter_tile = [&]() {
-            loaders_sync();                 // descriptor lj was stored before the previous loaders_sync
+            loaders_sync();                 // descriptor lj and table lj were stored before the previous loaders_sync
             const TcTile& T = ring[lj % TC_RING];
             desc_store(lj + TC_DESC_AHEAD);
             desc_load(lj + TC_DESC_AHEAD + 1);
+            fill_lut(lj + 1);
             const Prob& p = T.p;
-            l_in = resolve_in(p, I, l_in_bs);
+            { const __half* in = resolve_in(p, I, l_in_bs); l_in = reinterpret_cast<const char*>(in); }
             lnk = T.nk;
-            t_w = p.w; t_gout = p.gout; t_ldw = p.ldw; t_C = p.C; t_Cs = p.Cs; t_Fs = p.Fs; t_kw = p.kw; t_W = p.W;
+            t_w = reinterpret_cast<const char*>(p.w); t_gout = reinterpret_cast<const char*>(p.gout);
+            t_ldw = p.ldw; t_C = p.C; t_Cs = p.Cs; t_Fs = p.Fs; t_kw = p.kw; t_W = p.W;
             t_Wo = p.Wo; t_Ho = p.Ho; t_sh = p.sh; t_sw = p.sw; t_n0 = T.n0; t_out_bs = p.out_bs; t_HoWo = p.Ho * p.Wo;
             t_r0 = T.r0; t_r1 = T.r1; t_m0 = T.m0;
+            t_Cldw = p.C * p.ldw; t_C8 = p.C - T.n0;
             const int KK = p.kh * p.kw;
-            t_dense = KK == 1;
-            t_Kf = SCALAR_A ? KK : KK * p.Cs; t_Kd = KK * p.Fs;
-            t_fdc = T.fd_c; t_fdkw = T.fd_kw; t_fdrows = T.fd_rows; t_fdw = T.fd_w;
+            t_Kf = SCALAR_A ? KK : KK * p.Cs;
+            t_lut = T.nk * 8 <= TC_LUT;
+            t_s1 = p.sh == 1 && p.sw == 1;
+            geo = geo_of(T);
+            t_fdrows = T.fd_rows; t_fdw = T.fd_w;
             const int HW = p.H * p.W;
             if (MODE == TC_FWD) {
 #pragma unroll
@@ -338,17 +375,21 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                     const int mc = a_ok[j] ? m : 0;
                     const int b = fdiv(mc, t_fdrows), rem = mc - b * t_HoWo;
                     const int ho = fdiv(rem, t_fdw), wo = rem - ho * t_Wo;
-                    a_row[j] = l_in + (long long)b * l_in_bs + ((long long)(ho * t_sh) * t_W + wo * t_sw) * t_Cs;
+                    a_off[j] = 2u * ((uint32_t)b * (uint32_t)l_in_bs + (uint32_t)(((ho * t_sh) * t_W + wo * t_sw) * t_Cs));
                 }
             } else if (MODE == TC_DGRAD) {
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
                     const int m = T.m0 + (warp * 2 + j) * 8 + l8;
-                    a_b[j] = -1; a_h[j] = 0; a_w[j] = 0;
+                    a_h[j] = -0x40000000; a_w[j] = 0; a_base[j] = 0;        // out of range: every window test fails
                     if (m < T.Mrows) {
-                        a_b[j] = fdiv(m, t_fdrows);
-                        const int rem = m - a_b[j] * HW;
+                        const int b = fdiv(m, t_fdrows);
+                        const int rem = m - b * HW;
                         a_h[j] = fdiv(rem, t_fdw); a_w[j] = rem - a_h[j] * t_W;
+                        // stride 1: source element = b * out_bs + ((h - ki) * Wo + (w - kj)) * Fs + kf; the table holds
+                        // kf - (ki * Wo + kj) * Fs + bias >= 0
+                        a_base[j] = 2 * (b * t_out_bs + (a_h[j] * t_Wo + a_w[j]) * t_Fs - geo.bias);
+                        if (!t_s1) a_base[j] = b * t_out_bs;
                     }
                 }
             } else if (!SCALAR_A) {
@@ -357,11 +398,15 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                     const int kk = T.m0 + (q * 4 + lq) * 8;
                     w_kok[q] = kk < T.Mrows;
                     const int kc = w_kok[q] ? kk : 0;
-                    const int ij = fdiv(kc, t_fdc), cp = kc - ij * t_Cs;
-                    const int i = fdiv(ij, t_fdkw), j = ij - i * t_kw;
+                    const int ij = fdiv(kc, geo.fdc), cp = kc - ij * t_Cs;
+                    const int i = fdiv(ij, geo.fdkw), j = ij - i * t_kw;
                     w_koff[q] = (i * t_W + j) * t_Cs + cp;
                 }
             }
+        };
+        auto k_entry = [&](int chunk) -> int2 {
+            if (t_lut) return lut[(lj & 1) * TC_LUT + chunk];
+            return tc_k_entry<MODE>(geo, chunk);
         };
         auto load_stage = [&](int stage, int kb) {
             const uint32_t aS = sA + stage * TC_A_BYTES, bS = sB + stage * B_BYTES;
@@ -369,36 +414,30 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             if (MODE == TC_FWD) {
                 // A, K-major.  Items (row block 2*warp + j, k chunk h*4 + lq): two rows x two chunks.
                 if (!SCALAR_A) {
-                    int koff[2]; bool kok[2];
+                    int2 e[2];
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const int k = kb * TC_BK + (h * 4 + lq) * 8;
-                        kok[h] = k < t_Kf;
-                        const int kc = kok[h] ? k : 0;
-                        koff[h] = kc;
-                        if (!t_dense) {
-                            const int ij = fdiv(kc, t_fdc), cp = kc - ij * t_Cs;
-                            const int ki = fdiv(ij, t_fdkw), kj = ij - ki * t_kw;
-                            koff[h] = (ki * t_W + kj) * t_Cs + cp;
-                        }
-                    }
+                    for (int h = 0; h < 2; ++h) e[h] = k_entry(kb * 8 + h * 4 + lq);
 #pragma unroll
                     for (int j = 0; j < 2; ++j)
 #pragma unroll
-                        for (int h = 0; h < 2; ++h)
-                            cp_async16_ca(aS + core_off(warp * 2 + j, h * 4 + lq, l8), a_row[j] + koff[h], a_ok[j] && kok[h]);
+                        for (int h = 0; h < 2; ++h) {
+                            const bool ok = a_ok[j] && e[h].y < 0;
+                            cp_async16_ca(aS + core_off(warp * 2 + j, h * 4 + lq, l8), l_in + (ok ? a_off[j] + (uint32_t)e[h].x : 0u), ok);
+                        }
                 } else {
                     // first layer on a one-channel model input with per-individual inputs: element-wise gather
+                    const __half* in_h = reinterpret_cast<const __half*>(l_in);
 #pragma unroll
                     for (int j = 0; j < 2; ++j)
 #pragma unroll
                         for (int h = 0; h < 2; ++h) {
                             const int k = kb * TC_BK + (h * 4 + lq) * 8;
+                            const __half* row = in_h + (a_off[j] >> 1);
                             Half8 v;
-                            int ki = fdiv(k, t_fdkw), kj = k - ki * t_kw;
+                            int ki = fdiv(k, geo.fdkw), kj = k - ki * t_kw;
 #pragma unroll
                             for (int e = 0; e < 8; ++e) {
-                                v.v[e] = (a_ok[j] && k + e < t_Kf) ? a_row[j][ki * t_W + kj] : __float2half_rn(0.f);
+                                v.v[e] = (a_ok[j] && k + e < t_Kf) ? row[ki * t_W + kj] : __float2half_rn(0.f);
                                 if (++kj == t_kw) { kj = 0; ++ki; }
                             }
                             *reinterpret_cast<Half8*>(sgen + (aS - sbase) + core_off(warp * 2 + j, h * 4 + lq, l8)) = v;
@@ -407,54 +446,52 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                 // B, MN-major: this warp owns k rows kb*64 + warp*8 .. +7 (one per l8), Q quads of n chunks.
                 // W rows are [(ij, c)][ldw]; pad channels have no row.
                 {
-                    const int k = kb * TC_BK + warp * 8 + l8;
-                    bool kok = k < t_Kf;
-                    const int kc = kok ? k : 0;
-                    int wrow = kc;
-                    if (SCALAR_A) {}
-                    else if (t_dense) kok = kok && kc < t_C;
-                    else { const int ij = fdiv(kc, t_fdc), cp = kc - ij * t_Cs; kok = kok && cp < t_C; wrow = ij * t_C + cp; }
-                    if (!kok) wrow = 0;
-                    const __half* wr = t_w + (long long)wrow * t_ldw;
+                    int wrow; bool kok;
+                    if (SCALAR_A) { wrow = kb * TC_BK + warp * 8 + l8; kok = wrow < t_Kf; }
+                    else { const int2 eb = k_entry(kb * 8 + warp); wrow = (eb.y & 0xFFFFF) + l8; kok = l8 < ((eb.y >> 20) & 15); }
+                    const uint32_t wr = kok ? 2u * (uint32_t)(wrow * t_ldw + t_n0) : 0u;
+                    const int nleft = kok ? t_ldw - t_n0 : 0;            // columns of this row from n0 on
 #pragma unroll 4
                     for (int i = 0; i < Q; ++i) {
-                        const int nch = i * 4 + lq, n = t_n0 + nch * 8;
-                        const bool ok = kok && n < t_ldw;
-                        cp_async16(bS + core_off(nch, warp, l8), wr + (ok ? n : 0), ok);
+                        const int nch = i * 4 + lq;
+                        const bool ok = nch * 8 < nleft;
+                        cp_async16(bS + core_off(nch, warp, l8), t_w + (ok ? wr + (uint32_t)(nch * 16) : 0u), ok);
                     }
                 }
             } else if (MODE == TC_DGRAD) {
-                // k = (ij, f) over the padded filters: two chunks per thread and k-block, decomposed once
-                int kki[2], kkj[2], kf[2]; long long wbase[2]; bool kok[2];
+                // k = (ij, f) over the padded filters: two chunks per thread and k-block
+                int2 e[2];
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int k = kb * TC_BK + (h * 4 + lq) * 8;
-                    kok[h] = k < t_Kd;
-                    const int kc = kok[h] ? k : 0;
-                    int ij = 0; kf[h] = kc; kki[h] = 0; kkj[h] = 0;
-                    if (!t_dense) { ij = fdiv(kc, t_fdc); kf[h] = kc - ij * t_Fs; kki[h] = fdiv(ij, t_fdkw); kkj[h] = ij - kki[h] * t_kw; }
-                    wbase[h] = (long long)ij * t_C * t_ldw + kf[h];
-                }
+                for (int h = 0; h < 2; ++h) e[h] = k_entry(kb * 8 + h * 4 + lq);
 #pragma unroll
                 for (int j = 0; j < 2; ++j)
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
-                        bool ok = a_b[j] >= 0 && kok[h];
-                        const int hh = a_h[j] - kki[h], ww = a_w[j] - kkj[h];
-                        // strides are 1 or 2 in practice: shifts for those, a real division otherwise
-                        const int ho = t_sh == 1 ? hh : (t_sh == 2 ? hh >> 1 : hh / t_sh);
-                        const int wo = t_sw == 1 ? ww : (t_sw == 2 ? ww >> 1 : ww / t_sw);
-                        ok = ok && hh >= 0 && ww >= 0 && ho * t_sh == hh && wo * t_sw == ww && ho < t_Ho && wo < t_Wo;
-                        const long long off = ok ? (long long)a_b[j] * t_out_bs + (ho * t_Wo + wo) * t_Fs + kf[h] : 0;
-                        cp_async16_ca(aS + core_off(warp * 2 + j, h * 4 + lq, l8), t_gout + off, ok);
+                        const int hh = a_h[j] - (e[h].y & 255), ww = a_w[j] - ((e[h].y >> 8) & 255);
+                        bool ok; uint32_t off;
+                        if (t_s1) {
+                            ok = e[h].y < 0 && (unsigned)hh < (unsigned)t_Ho && (unsigned)ww < (unsigned)t_Wo;
+                            off = (uint32_t)(a_base[j] + e[h].x);
+                        } else {
+                            // strides are 1 or 2 in practice: shifts for those, a real division otherwise
+                            const int ho = t_sh == 1 ? hh : (t_sh == 2 ? hh >> 1 : hh / t_sh);
+                            const int wo = t_sw == 1 ? ww : (t_sw == 2 ? ww >> 1 : ww / t_sw);
+                            ok = e[h].y < 0 && hh >= 0 && ww >= 0 && ho * t_sh == hh && wo * t_sw == ww && ho < t_Ho && wo < t_Wo;
+                            off = 2u * (uint32_t)(a_base[j] + (ho * t_Wo + wo) * t_Fs + ((e[h].y >> 16) & 0x7FFF) * 8);
+                        }
+                        cp_async16_ca(aS + core_off(warp * 2 + j, h * 4 + lq, l8), t_gout + (ok ? off : 0u), ok);
                     }
                 // B, K-major: rows n = input channel c, k = (ij, f) contiguous in f; items q = warp*Q + i -> (row block q/2, chunk half q%2)
+                uint32_t wb[2];
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+                    wb[h] = 2u * (uint32_t)(((e[h].y & 255) * t_kw + ((e[h].y >> 8) & 255)) * t_Cldw + ((e[h].y >> 16) & 0x7FFF) * 8 + t_n0 * t_ldw);
 #pragma unroll 4
                 for (int i = 0; i < Q; ++i) {
                     const int q = warp * Q + i, blk = q >> 1, h = q & 1;
-                    const int c = t_n0 + blk * 8 + l8;
-                    const bool ok = c < t_C && kok[h];
-                    cp_async16(bS + core_off(blk, h * 4 + lq, l8), t_w + (ok ? wbase[h] + (long long)c * t_ldw : 0), ok);
+                    const int c = blk * 8 + l8;
+                    const bool ok = c < t_C8 && e[h].y < 0;
+                    cp_async16(bS + core_off(blk, h * 4 + lq, l8), t_w + (ok ? wb[h] + 2u * (uint32_t)(c * t_ldw) : 0u), ok);
                 }
             } else {
                 // this warp owns reduction rows r0 + kb*64 + warp*8 .. +7 (one per l8)
@@ -463,8 +500,8 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                 const int rc = rok ? r : t_r0;
                 const int b = fdiv(rc, t_fdrows), rem = rc - b * t_HoWo;
                 const int ho = fdiv(rem, t_fdw), wo = rem - ho * t_Wo;
-                const __half* in_row = l_in + (long long)b * l_in_bs + ((long long)(ho * t_sh) * t_W + wo * t_sw) * t_Cs;
-                const __half* go_row = t_gout + (long long)b * t_out_bs + (long long)rem * t_Fs;
+                const __half* in_row = reinterpret_cast<const __half*>(l_in) + (long long)b * l_in_bs + ((long long)(ho * t_sh) * t_W + wo * t_sw) * t_Cs;
+                const __half* go_row = reinterpret_cast<const __half*>(t_gout) + (long long)b * t_out_bs + (long long)rem * t_Fs;
                 // A, MN-major: 4 quads of kk chunks
 #pragma unroll
                 for (int qd = 0; qd < 4; ++qd) {
@@ -472,7 +509,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                     if (SCALAR_A) {
                         Half8 v;
                         const int kk = t_m0 + cc * 8;
-                        int ki = fdiv(kk, t_fdkw), kj = kk - ki * t_kw;
+                        int ki = fdiv(kk, geo.fdkw), kj = kk - ki * t_kw;
 #pragma unroll
                         for (int e = 0; e < 8; ++e) {
                             v.v[e] = (rok && kk + e < t_Kf) ? in_row[ki * t_W + kj] : __float2half_rn(0.f);
@@ -493,30 +530,31 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             }
         };
 
-        int p = 0;                       // stream position: k-blocks issued so far
+        fill_lut(0);
+        int sb = 0; uint32_t ph = 1;     // ring stage and the parity a fresh "empty" barrier passes immediately
         for (lj = 0; lj < my_tiles; ++lj) {
             loader_enter_tile();
-            for (int kb = 0; kb < lnk; ++kb, ++p) {
-                const int sb = p % STAGES;
-                if (p >= STAGES) mbar_wait(sEmpty + sb * 8, (uint32_t)((p / STAGES - 1) & 1));
+            for (int kb = 0; kb < lnk; ++kb) {
+                mbar_wait(sEmpty + sb * 8, ph);
                 load_stage(sb, kb);
                 if (SCALAR_A) fence_proxy_async();       // the element-wise gather used ordinary shared-memory stores
                 cp_async_arrive_noinc(sFull + sb * 8);   // fires when this thread's copies for the stage have landed
+                if (++sb == STAGES) { sb = 0; ph ^= 1u; }
             }
         }
         cp_async_wait_all();
     } else if (warp == TC_LW) {
         // =================================================================== MMA issuer
         if (lane == 0) {
-            int p = 0;
+            int st = 0; uint32_t fph = 0;     // ring stage and the parity of its "full" barrier
+            const uint64_t dA0 = umma_desc(sA), dB0 = umma_desc(sB);
             for (int j = 0; j < my_tiles; ++j) {
                 const int acc = j & 1;
-                if (j >= 2) mbar_wait(sTEmpty + acc * 8, (uint32_t)((j / 2 - 1) & 1));   // epilogue drained this accumulator
+                if (j >= 2) mbar_wait(sTEmpty + acc * 8, (uint32_t)(((j >> 1) - 1) & 1));   // epilogue drained this accumulator
                 const uint32_t tacc = tmem + (uint32_t)(acc * acc_cols);
                 int nk = 1; uint32_t idesc = 0;
-                for (int kb = 0; kb < nk; ++kb, ++p) {
-                    const int st = p % STAGES;
-                    mbar_wait(sFull + st * 8, (uint32_t)((p / STAGES) & 1));
+                for (int kb = 0; kb < nk; ++kb) {
+                    mbar_wait(sFull + st * 8, fph);
                     fence_proxy_async();     // the stage was written through the generic proxy (cp.async), UMMA reads it through the async proxy
                     tc_fence_after();
                     if (kb == 0) {       // the descriptor was fetched by the loaders long before this stage was published
@@ -524,11 +562,12 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                         nk = T.nk;
                         idesc = umma_idesc(MODE == TC_WGRAD ? 1 : 0, MODE == TC_DGRAD ? 0 : 1, T.n_umma);
                     }
-                    const uint32_t aS = sA + st * TC_A_BYTES, bS = sB + st * B_BYTES;
+                    const uint64_t dA = dA0 + (uint64_t)((uint32_t)(st * TC_A_BYTES) >> 4), dB = dB0 + (uint64_t)(((uint32_t)st * B_BYTES) >> 4);
 #pragma unroll
                     for (int ks = 0; ks < TC_BK / 16; ++ks)
-                        umma_f16(tacc, umma_desc(aS + ks * 256), umma_desc(bS + ks * 256), idesc, (kb | ks) ? 1u : 0u);
+                        umma_f16(tacc, dA + (uint64_t)(ks * 16), dB + (uint64_t)(ks * 16), idesc, (kb | ks) ? 1u : 0u);
                     umma_commit(sEmpty + st * 8);
+                    if (++st == STAGES) { st = 0; fph ^= 1u; }
                 }
                 umma_commit(sTFull + acc * 8);
             }

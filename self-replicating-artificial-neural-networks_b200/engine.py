@@ -89,6 +89,8 @@ def load_library(rebuild: bool = False) -> C.CDLL:
     lib.srn_debug_get_tensor.argtypes = [vp, i32, i32, i32, i32, vp]
     lib.srn_debug_get_grad.argtypes = [vp, i32, i32, i32, vp, i64]
     lib.srn_debug_launch_groups.argtypes = [vp]
+    lib.srn_debug_group_probs.argtypes = [vp, i32, i32, vp]
+    lib.srn_debug_profile_detail.argtypes = [vp, i32, i32, vp, vp, vp, vp]
     _lib = lib
     return lib
 
@@ -315,6 +317,25 @@ class Engine:
 
     def launch_groups(self) -> int:
         return int(self._lib.srn_debug_launch_groups(self._h))
+
+    def group_probs(self, group: int, cap: int = 4096):
+        """Problem shapes of one launch bucket, [n, 16] (see srn_debug_group_probs in srn_engine.cu)."""
+        out = np.zeros((cap, 16), np.int32)
+        n = int(self._lib.srn_debug_group_probs(self._h, group, cap, _ptr(out)))
+        if n < 0:
+            raise RuntimeError('srn_debug_group_probs failed')
+        return out[:n]
+
+    def profile_detail(self, nb: int, cap: int = 1 << 16):
+        """Per-launch records of the last profiled region: (ms[n], info[n, 8], work[n, 3]), see srn_engine.cu."""
+        ms = np.zeros(cap, np.float32)
+        self.profile_start_ms = start = np.zeros(cap, np.float32)
+        info = np.zeros((cap, 8), np.int32)
+        work = np.zeros((cap, 3), np.float64)
+        n = int(self._lib.srn_debug_profile_detail(self._h, nb, cap, _ptr(ms), _ptr(start), _ptr(info), _ptr(work)))
+        if n < 0:
+            raise RuntimeError('srn_debug_profile_detail failed')
+        return ms[:n], info[:n], work[:n]
 
 
 def levenshtein(a: str, b: str) -> int:

@@ -20,6 +20,18 @@ X_layer = MaxPool2D(pool_size=2)(X_layer)
 con = concatenate([Reshape((1, -1))(X_layer), Reshape((1, -1))(g_layer)])
 con = Dense(units=64, activation='relu')(con)
 loss_balance = 0.5""",
+    'wide': """X_layer = Conv2D(filters=128, kernel_size=3, strides=1)(X_layer)
+X_layer = Conv2D(filters=64, kernel_size=3, strides=1)(X_layer)
+X_layer = MaxPool2D(pool_size=4)(X_layer)
+con = concatenate([Reshape((1, -1))(X_layer), Reshape((1, -1))(g_layer)])
+con = Dense(units=64, activation='relu')(con)
+loss_balance = 0.5""",
+    'mid': """X_layer = Conv2D(filters=32, kernel_size=3, strides=1)(X_layer)
+X_layer = Conv2D(filters=24, kernel_size=3, strides=1)(X_layer)
+X_layer = MaxPool2D(pool_size=4)(X_layer)
+con = concatenate([Reshape((1, -1))(X_layer), Reshape((1, -1))(g_layer)])
+con = Dense(units=64, activation='relu')(con)
+loss_balance = 0.5""",
 }
 
 if __name__ == '__main__':
@@ -41,3 +53,10 @@ if __name__ == '__main__':
     for k, (ms, c) in prof.items():
         if c:
             print(f'  {k:12s} {ms / steps:8.3f} ms/step  {c // steps:3d} launches')
+    eng.profile(True)
+    eng.fit(1, 750, 0, shuffle_seed=2, max_steps=1)
+    ms, info, work = eng.profile_detail(750)
+    eng.profile(False)
+    for t, i, w in zip(ms, info, work):
+        if 1 <= i[0] <= 3:
+            print(f'    {Engine.CATEGORIES[i[0]]:11s} bucket {i[1]:2d} tc {i[3]} BNf {i[4]} BNc {i[5]} probs {i[6]}: {t:.4f} ms {w[0] / 1e9 / t:7.1f} TFLOP/s')
