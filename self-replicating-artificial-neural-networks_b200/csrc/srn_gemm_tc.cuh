@@ -48,7 +48,9 @@ constexpr int TC_LUT = 512;            // 16-byte k chunks per lookup table: red
 // many stages as fit.  Loaders never wait for their own copies: completion is signalled to the stage's "full"
 // barrier by the copy engine itself (cp.async.mbarrier.arrive.noinc), so up to `stages` k-blocks are in flight.
 __host__ __device__ inline int tc_stages(int BN) { return BN <= 64 ? 4 : (BN <= 128 ? 3 : 4); }
-__host__ __device__ inline int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + BN * TC_BK * 2) + 256 + TC_RING * 256 + 2 * TC_LUT * 8; }
+// B tiles are stored with 128-byte rows (swizzle-128B atoms), so a 32-wide MN-major tile takes the room of a 64-wide one
+__host__ __device__ inline int tc_b_bytes(int BN) { return (BN < 64 ? 64 : BN) * TC_BK * 2; }
+__host__ __device__ inline int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + tc_b_bytes(BN)) + 256 + TC_RING * 256 + 2 * TC_LUT * 8; }
 __host__ __device__ inline int tc_acc_cols(int BN) { return BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256)); }
 __host__ __device__ inline int tc_tmem_cols(int BN) { return 2 * tc_acc_cols(BN); }     // two accumulators
 __host__ __device__ inline int round_up8(int v) { return (v + 7) & ~7; }
@@ -135,9 +137,13 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(taddr), "r"(cols) : "memory");
 }
 
-// shared-memory matrix descriptor, no swizzle: start >> 4 | LBO >> 4 << 16 | SBO >> 4 << 32 | version 1 << 46
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
-    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(128u >> 4) << 16) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46);
+// shared-memory matrix descriptor, swizzle-128B (layout type 2 at bits 61-63): start >> 4 | LBO >> 4 << 16 |
+// SBO >> 4 << 32 | version 1 << 46.  Canonical layouts in 16-byte units (cute/atom/mma_traits_sm100.hpp):
+//   K-major   ((8, n), 2)      : ((8, SBO), 1)           rows of 128 B = 64 k, 8 rows per 1024-byte atom, LBO unused
+//   MN-major  ((8, n), (8, k)) : ((1, LBO), (8, SBO))    rows of 128 B = 64 m/n of one k, 8 k per atom
+// with the 16-byte chunk index XOR-ed with the row index inside the atom (address bits 4-6 ^= bits 7-9).
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
 // instruction descriptor, kind::f16: D = f32 (bits 4-5 = 1), A = B = f16 (0), major bits 15/16, N >> 3 at 17, M >> 4 at 24
 __device__ __forceinline__ uint32_t umma_idesc(int a_mn_major, int b_mn_major, int n) {
@@ -168,9 +174,12 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
-// byte offset of the 16-byte unit (mn_group, k_group, row-in-core) inside a tile
-__device__ __forceinline__ uint32_t core_off(int mn_group, int k_group, int r8) {
-    return (uint32_t)((mn_group * 8 + k_group) * 128 + r8 * 16);
+// byte offset of a 16-byte chunk inside an operand tile (tile bases are 1024-byte aligned)
+__device__ __forceinline__ uint32_t sw_k_off(int row, int chunk) {    // K-major: row = m/n index, chunk = k chunk 0..7
+    return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
+}
+__device__ __forceinline__ uint32_t sw_mn_off(int u, int kk) {        // MN-major: u = m/n chunk, kk = k row 0..63; 64 m/n per 8192-byte group
+    return (uint32_t)((u >> 3) * 8192 + (kk >> 3) * 1024 + (kk & 7) * 128 + (((u & 7) ^ (kk & 7)) << 4));
 }
 
 // ------------------------------------------------------------------ the kernel
@@ -201,7 +210,8 @@ struct __align__(16) TcTile {
     FastDiv fd_w;      // Wo (fwd, wgrad) or W (dgrad)
     FastDiv fd_c;      // channel stride of the k index: Cs (fwd, wgrad) or Fs (dgrad)
     FastDiv fd_kw;
-    unsigned char pad[256 - sizeof(Prob) - 8 * sizeof(int) - 4 * sizeof(FastDiv)];
+    int klast;         // K = 16 steps of the last k-block (1..4): the tail of the reduction is neither loaded nor multiplied
+    unsigned char pad[256 - sizeof(Prob) - 9 * sizeof(int) - 4 * sizeof(FastDiv)];
 };
 static_assert(sizeof(TcTile) == 256, "TcTile is one 256-byte table entry / ring slot");
 
@@ -233,6 +243,10 @@ inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool
         t.r0 = split * TC_WGRAD_ROWS; t.r1 = min(nb * HoWo, t.r0 + TC_WGRAD_ROWS);
         t.nk = (t.r1 - t.r0 + TC_BK - 1) / TC_BK;
     }
+    {
+        const int Ktot = MODE == TC_FWD ? Kf : (MODE == TC_DGRAD ? KK * p.Fs : t.r1 - t.r0);
+        t.klast = (Ktot - (t.nk - 1) * TC_BK + 15) / 16;
+    }
     t.n_umma = min(BN, ((t.Ncols - t.n0 + 15) / 16) * 16);
     t.fd_rows = make_fastdiv(MODE == TC_DGRAD ? p.H * p.W : HoWo);
     t.fd_w = make_fastdiv(MODE == TC_DGRAD ? p.W : p.Wo);
@@ -259,15 +273,16 @@ __device__ __forceinline__ int2 tc_k_entry(const KGeo& g, int chunk) {
 }
 
 template <int MODE, bool SCALAR_A>
-static __global__ void __launch_bounds__(TC_THREADS)
+static __global__ void __launch_bounds__(TC_THREADS, 2)
 k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int l8 = lane & 7, lq = lane >> 3;              // row inside a core matrix, chunk inside a quad
     const uint32_t sraw = smem_u32(smem_raw);
-    const uint32_t sbase = (sraw + 127u) & ~127u;
+    const uint32_t sbase = sraw;
+    if (sraw & 1023u) __trap();                           // swizzle-128B atoms need 1024-byte alignment (the dynamic window starts on one)
     unsigned char* sgen = smem_raw + (sbase - sraw);      // generic pointer to the same place as sbase
-    const uint32_t B_BYTES = (uint32_t)BN * TC_BK * 2;
+    const uint32_t B_BYTES = (uint32_t)tc_b_bytes(BN);
     const int STAGES = tc_stages(BN);
     const uint32_t sA = sbase, sB = sbase + STAGES * TC_A_BYTES;
     const uint32_t sRing = sB + STAGES * B_BYTES;         // TC_RING tile descriptors of 256 bytes
@@ -311,19 +326,28 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
 
     if (warp < TC_LW) {
         // =================================================================== loaders (8 warps)
-        // A tile: 128 (m or kk) x 64 k in 16-byte chunks = 1024 chunks, 4 per thread; B tile: BN x 64, BN/32 per
-        // thread.  A warp covers 8 rows x 4 consecutive chunks per item (64 contiguous bytes per row).
-        // Per-tile loader state lives in registers; what depends only on k (window offset, weight row, validity of a
-        // 16-byte k chunk) comes from a per-tile lookup table in shared memory that the loaders fill one tile ahead,
-        // so the k loop is address adds, predicates and copies.  All gather offsets are 32-bit byte offsets inside
-        // one tensor; an out-of-range chunk gets offset 0 and a zero-filling copy.
+        // Operand tiles are stored in the swizzle-128B canonical layouts.  One warp-wide copy instruction moves
+        // 4 rows x 8 chunks: the 8 lanes of a quarter warp read 128 contiguous bytes of one row (one L1 line when
+        // the row is contiguous in memory - a cached 16-byte LDGSTS costs one L1 wavefront per line a quarter warp
+        // touches, tools/micro/ldgsts_wavefronts.cu) and write the 8 chunk slots of one 128-byte shared-memory
+        // row (all 32 banks).  A thread therefore owns one chunk column (lane & 7) and rows 4 * warp + lane / 8
+        // + 32 i, so what depends only on k (window offset, weight row, validity of a 16-byte k chunk) is read once
+        // per k-block from a per-tile lookup table in shared memory that the loaders fill one tile ahead.  All
+        // gather offsets are 32-bit byte offsets inside one tensor; an out-of-range chunk gets offset 0 and a
+        // zero-filling copy.
+        const int ch = lane & 7, sub = lane >> 3, rlo = warp * 4 + sub;          // chunk column, row inside a block of 32
+        const uint32_t k_dst = sw_k_off(rlo, ch);                                 // K-major tile: rows rlo + 32 i at + 4096 i
         const char* l_in = nullptr; int l_in_bs = 0;
         const char* t_w = nullptr; const char* t_gout = nullptr;
-        uint32_t a_off[2] = {0, 0}; bool a_ok[2] = {false, false};   // FWD: this thread's two im2col rows
-        int a_h[2] = {0, 0}, a_w[2] = {0, 0}, a_base[2] = {0, 0};    // DGRAD: input position of its two rows, biased offset
-        int w_koff[4]; bool w_kok[4];    // WGRAD (vector): offsets of this thread's four kk chunks inside the window
+        uint32_t a_off[4] = {0, 0, 0, 0}; bool a_ok[4] = {false, false, false, false};   // FWD: this thread's (up to) four im2col rows
+        uint32_t a_dst[2] = {0, 0};
+        // Short reductions (first layers: K = 16 or 32) use 2 or 4 chunks per row, so a copy instruction covers 16 or 8
+        // rows and no lane copies zeros: t_cs = log2(chunks per row), t_items = rows per thread, t_ch = this thread's chunk
+        int t_cs = 3, t_items = 4, t_ch = ch, t_ga = 2;
+        int a_h[4] = {0, 0, 0, 0}, a_w[4] = {0, 0, 0, 0}, a_base[4] = {0, 0, 0, 0};       // DGRAD: input position of its rows, biased offset
+        int w_koff[2] = {0, 0}; bool w_kok[2] = {false, false};    // WGRAD (vector): offsets of this thread's two kk chunks inside the window
         int t_ldw = 0, t_Cs = 1, t_Fs = 1, t_kw = 1, t_W = 1, t_Wo = 1, t_Ho = 1, t_sh = 1, t_sw = 1;
-        int t_Kf = 0, t_n0 = 0, t_out_bs = 0, t_HoWo = 1, t_r0 = 0, t_r1 = 0, t_m0 = 0, t_C = 0, t_Cldw = 0, t_C8 = 0;
+        int t_Kf = 0, t_n0 = 0, t_out_bs = 0, t_HoWo = 1, t_r0 = 0, t_r1 = 0, t_m0 = 0, t_Cldw = 0, t_C8 = 0;
         bool t_lut = false, t_s1 = true;
         KGeo geo{};
         FastDiv t_fdrows{}, t_fdw{};
@@ -356,7 +380,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             { const __half* in = resolve_in(p, I, l_in_bs); l_in = reinterpret_cast<const char*>(in); }
             lnk = T.nk;
             t_w = reinterpret_cast<const char*>(p.w); t_gout = reinterpret_cast<const char*>(p.gout);
-            t_ldw = p.ldw; t_C = p.C; t_Cs = p.Cs; t_Fs = p.Fs; t_kw = p.kw; t_W = p.W;
+            t_ldw = p.ldw; t_Cs = p.Cs; t_Fs = p.Fs; t_kw = p.kw; t_W = p.W;
             t_Wo = p.Wo; t_Ho = p.Ho; t_sh = p.sh; t_sw = p.sw; t_n0 = T.n0; t_out_bs = p.out_bs; t_HoWo = p.Ho * p.Wo;
             t_r0 = T.r0; t_r1 = T.r1; t_m0 = T.m0;
             t_Cldw = p.C * p.ldw; t_C8 = p.C - T.n0;
@@ -368,39 +392,52 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             t_fdrows = T.fd_rows; t_fdw = T.fd_w;
             const int HW = p.H * p.W;
             if (MODE == TC_FWD) {
+                t_cs = (T.nk == 1 && t_Kf <= 32) ? (t_Kf <= 16 ? 1 : 2) : 3;
+                t_items = 1 << (t_cs - 1);
+                const int rpw = 32 >> t_cs, subr = lane >> t_cs;
+                t_ch = lane & ((1 << t_cs) - 1);
 #pragma unroll
-                for (int j = 0; j < 2; ++j) {
-                    const int m = T.m0 + (warp * 2 + j) * 8 + l8;
-                    a_ok[j] = m < T.Mrows;
-                    const int mc = a_ok[j] ? m : 0;
+                for (int i = 0; i < 4; ++i) {
+                    const int r = i * rpw * 8 + warp * rpw + subr;       // < 128 for i < t_items
+                    const int m = T.m0 + r;
+                    a_ok[i] = i < t_items && m < T.Mrows;
+                    const int mc = a_ok[i] ? m : 0;
                     const int b = fdiv(mc, t_fdrows), rem = mc - b * t_HoWo;
                     const int ho = fdiv(rem, t_fdw), wo = rem - ho * t_Wo;
-                    a_off[j] = 2u * ((uint32_t)b * (uint32_t)l_in_bs + (uint32_t)(((ho * t_sh) * t_W + wo * t_sw) * t_Cs));
+                    a_off[i] = 2u * ((uint32_t)b * (uint32_t)l_in_bs + (uint32_t)(((ho * t_sh) * t_W + wo * t_sw) * t_Cs));
+                    if (i < 2) a_dst[i] = sw_k_off(r & 127, t_ch);
                 }
             } else if (MODE == TC_DGRAD) {
 #pragma unroll
-                for (int j = 0; j < 2; ++j) {
-                    const int m = T.m0 + (warp * 2 + j) * 8 + l8;
-                    a_h[j] = -0x40000000; a_w[j] = 0; a_base[j] = 0;        // out of range: every window test fails
+                for (int i = 0; i < 4; ++i) {
+                    const int m = T.m0 + i * 32 + rlo;
+                    a_h[i] = -0x40000000; a_w[i] = 0; a_base[i] = 0;        // out of range: every window test fails
                     if (m < T.Mrows) {
                         const int b = fdiv(m, t_fdrows);
                         const int rem = m - b * HW;
-                        a_h[j] = fdiv(rem, t_fdw); a_w[j] = rem - a_h[j] * t_W;
+                        a_h[i] = fdiv(rem, t_fdw); a_w[i] = rem - a_h[i] * t_W;
                         // stride 1: source element = b * out_bs + ((h - ki) * Wo + (w - kj)) * Fs + kf; the table holds
                         // kf - (ki * Wo + kj) * Fs + bias >= 0
-                        a_base[j] = 2 * (b * t_out_bs + (a_h[j] * t_Wo + a_w[j]) * t_Fs - geo.bias);
-                        if (!t_s1) a_base[j] = b * t_out_bs;
+                        a_base[i] = 2 * (b * t_out_bs + (a_h[i] * t_Wo + a_w[i]) * t_Fs - geo.bias);
+                        if (!t_s1) a_base[i] = b * t_out_bs;
                     }
                 }
-            } else if (!SCALAR_A) {
+            } else {
+                // valid kk chunks of this tile: 2 or 4 (first layers) use the narrow lane mappings, up to 8 one group, else two
+                const int mu = min(16, (T.Mrows - T.m0 + 7) >> 3);
+                t_cs = mu <= 2 ? 1 : (mu <= 4 ? 2 : 3);
+                t_ga = mu > 8 ? 2 : 1;
+                t_ch = lane & ((1 << t_cs) - 1);
+                if (!SCALAR_A) {
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int kk = T.m0 + (q * 4 + lq) * 8;
-                    w_kok[q] = kk < T.Mrows;
-                    const int kc = w_kok[q] ? kk : 0;
-                    const int ij = fdiv(kc, geo.fdc), cp = kc - ij * t_Cs;
-                    const int i = fdiv(ij, geo.fdkw), j = ij - i * t_kw;
-                    w_koff[q] = (i * t_W + j) * t_Cs + cp;
+                    for (int g = 0; g < 2; ++g) {
+                        const int kk = T.m0 + (g * 8 + t_ch) * 8;
+                        w_kok[g] = kk < T.Mrows;
+                        const int kc = w_kok[g] ? kk : 0;
+                        const int ij = fdiv(kc, geo.fdc), cp = kc - ij * t_Cs;
+                        const int i = fdiv(ij, geo.fdkw), j = ij - i * t_kw;
+                        w_koff[g] = (i * t_W + j) * t_Cs + cp;
+                    }
                 }
             }
         };
@@ -408,124 +445,180 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             if (t_lut) return lut[(lj & 1) * TC_LUT + chunk];
             return tc_k_entry<MODE>(geo, chunk);
         };
+        // MN-major B tile (k rows x n chunks): BN = 32 has four chunks per row, so a quarter warp takes rows r and
+        // r + 4 (their swizzled slots never share a bank); wider tiles take whole 128-byte row segments
+        auto load_b_mn = [&](uint32_t bS, int krows, auto&& row_src) {   // rows >= krows are not read by the MMAs of this k-block
+            if (BN == 32) {
+                const int q = lane >> 2, kl = warp * 8 + ((q & 1) * 4 + (q >> 1)), u = lane & 3;
+                if (kl < krows) {
+                    int left; const char* src = row_src(kl, left);
+                    const bool ok = u * 16 < left;
+                    cp_async16(bS + sw_mn_off(u, kl), src + (ok ? u * 16 : 0), ok);
+                }
+            } else {
+                const int G = BN >> 6;
+                const uint32_t d0 = bS + sw_mn_off(ch, rlo);           // row rlo + 32 h at + 4096 h, group g at + 8192 g
+                if (krows >= 64) {
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        int left; const char* src = row_src(h * 32 + rlo, left);
+#pragma unroll 4
+                        for (int g = 0; g < G; ++g) {
+                            const int ub = g * 128 + ch * 16;
+                            const bool ok = ub < left;
+                            cp_async16(d0 + h * 4096 + g * 8192, src + (ok ? ub : 0), ok);
+                        }
+                    }
+                } else if (rlo < krows) {                                 // short reductions: krows is 16, 32 or 48
+                    int left; const char* src = row_src(rlo, left);
+                    for (int g = 0; g < G; ++g) {
+                        const int ub = g * 128 + ch * 16;
+                        const bool ok = ub < left;
+                        cp_async16(d0 + g * 8192, src + (ok ? ub : 0), ok);
+                    }
+                    if (krows > 32 && rlo + 32 < krows) {
+                        src = row_src(rlo + 32, left);
+                        for (int g = 0; g < G; ++g) {
+                            const int ub = g * 128 + ch * 16;
+                            const bool ok = ub < left;
+                            cp_async16(d0 + 4096 + g * 8192, src + (ok ? ub : 0), ok);
+                        }
+                    }
+                }
+            }
+        };
         auto load_stage = [&](int stage, int kb) {
             const uint32_t aS = sA + stage * TC_A_BYTES, bS = sB + stage * B_BYTES;
-            const int Q = BN >> 5;                           // B items per thread = quads of 4 chunks along the major axis
             if (MODE == TC_FWD) {
-                // A, K-major.  Items (row block 2*warp + j, k chunk h*4 + lq): two rows x two chunks.
+                // A, K-major: four rows, one k chunk
                 if (!SCALAR_A) {
-                    int2 e[2];
+                    const int2 e = k_entry(kb * 8 + t_ch);
+                    if (t_cs == 3) {
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) e[h] = k_entry(kb * 8 + h * 4 + lq);
-#pragma unroll
-                    for (int j = 0; j < 2; ++j)
-#pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            const bool ok = a_ok[j] && e[h].y < 0;
-                            cp_async16_ca(aS + core_off(warp * 2 + j, h * 4 + lq, l8), l_in + (ok ? a_off[j] + (uint32_t)e[h].x : 0u), ok);
+                        for (int i = 0; i < 4; ++i) {
+                            const bool ok = a_ok[i] && e.y < 0;
+                            cp_async16_ca(aS + k_dst + i * 4096, l_in + (ok ? a_off[i] + (uint32_t)e.x : 0u), ok);
                         }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 2; ++i) {
+                            if (i < t_items) {
+                                const bool ok = a_ok[i] && e.y < 0;
+                                cp_async16_ca(aS + a_dst[i], l_in + (ok ? a_off[i] + (uint32_t)e.x : 0u), ok);
+                            }
+                        }
+                    }
                 } else {
                     // first layer on a one-channel model input with per-individual inputs: element-wise gather
                     const __half* in_h = reinterpret_cast<const __half*>(l_in);
+                    const int k = kb * TC_BK + t_ch * 8;
 #pragma unroll
-                    for (int j = 0; j < 2; ++j)
-#pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            const int k = kb * TC_BK + (h * 4 + lq) * 8;
-                            const __half* row = in_h + (a_off[j] >> 1);
+                    for (int i = 0; i < 4; ++i) {
+                        if (i < t_items) {
+                            const __half* row = in_h + (a_off[i] >> 1);
                             Half8 v;
                             int ki = fdiv(k, geo.fdkw), kj = k - ki * t_kw;
 #pragma unroll
                             for (int e = 0; e < 8; ++e) {
-                                v.v[e] = (a_ok[j] && k + e < t_Kf) ? row[ki * t_W + kj] : __float2half_rn(0.f);
+                                v.v[e] = (a_ok[i] && k + e < t_Kf) ? row[ki * t_W + kj] : __float2half_rn(0.f);
                                 if (++kj == t_kw) { kj = 0; ++ki; }
                             }
-                            *reinterpret_cast<Half8*>(sgen + (aS - sbase) + core_off(warp * 2 + j, h * 4 + lq, l8)) = v;
+                            *reinterpret_cast<Half8*>(sgen + (aS - sbase) + (t_cs == 3 ? k_dst + i * 4096 : a_dst[i & 1])) = v;
                         }
+                    }
                 }
-                // B, MN-major: this warp owns k rows kb*64 + warp*8 .. +7 (one per l8), Q quads of n chunks.
-                // W rows are [(ij, c)][ldw]; pad channels have no row.
-                {
+                // B, MN-major: k rows kb*64 .. +63, n chunks from n0.  W rows are [(ij, c)][ldw]; pad channels have no row.
+                load_b_mn(bS, min(64, (t_Kf - kb * TC_BK + 15) & ~15), [&](int kl, int& left) -> const char* {
                     int wrow; bool kok;
-                    if (SCALAR_A) { wrow = kb * TC_BK + warp * 8 + l8; kok = wrow < t_Kf; }
-                    else { const int2 eb = k_entry(kb * 8 + warp); wrow = (eb.y & 0xFFFFF) + l8; kok = l8 < ((eb.y >> 20) & 15); }
-                    const uint32_t wr = kok ? 2u * (uint32_t)(wrow * t_ldw + t_n0) : 0u;
-                    const int nleft = kok ? t_ldw - t_n0 : 0;            // columns of this row from n0 on
-#pragma unroll 4
-                    for (int i = 0; i < Q; ++i) {
-                        const int nch = i * 4 + lq;
-                        const bool ok = nch * 8 < nleft;
-                        cp_async16(bS + core_off(nch, warp, l8), t_w + (ok ? wr + (uint32_t)(nch * 16) : 0u), ok);
-                    }
-                }
+                    if (SCALAR_A) { wrow = kb * TC_BK + kl; kok = wrow < t_Kf; }
+                    else { const int2 eb = k_entry(kb * 8 + (kl >> 3)); wrow = (eb.y & 0xFFFFF) + (kl & 7); kok = (kl & 7) < ((eb.y >> 20) & 15); }
+                    left = kok ? 2 * (t_ldw - t_n0) : 0;
+                    return t_w + (kok ? 2u * (uint32_t)(wrow * t_ldw + t_n0) : 0u);
+                });
             } else if (MODE == TC_DGRAD) {
-                // k = (ij, f) over the padded filters: two chunks per thread and k-block
-                int2 e[2];
+                // k = (ij, f) over the padded filters: one chunk per thread and k-block, four rows
+                const int2 e = k_entry(kb * 8 + ch);
+                const int ki = e.y & 255, kj = (e.y >> 8) & 255, kf = ((e.y >> 16) & 0x7FFF) * 8;
 #pragma unroll
-                for (int h = 0; h < 2; ++h) e[h] = k_entry(kb * 8 + h * 4 + lq);
-#pragma unroll
-                for (int j = 0; j < 2; ++j)
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const int hh = a_h[j] - (e[h].y & 255), ww = a_w[j] - ((e[h].y >> 8) & 255);
-                        bool ok; uint32_t off;
-                        if (t_s1) {
-                            ok = e[h].y < 0 && (unsigned)hh < (unsigned)t_Ho && (unsigned)ww < (unsigned)t_Wo;
-                            off = (uint32_t)(a_base[j] + e[h].x);
-                        } else {
-                            // strides are 1 or 2 in practice: shifts for those, a real division otherwise
-                            const int ho = t_sh == 1 ? hh : (t_sh == 2 ? hh >> 1 : hh / t_sh);
-                            const int wo = t_sw == 1 ? ww : (t_sw == 2 ? ww >> 1 : ww / t_sw);
-                            ok = e[h].y < 0 && hh >= 0 && ww >= 0 && ho * t_sh == hh && wo * t_sw == ww && ho < t_Ho && wo < t_Wo;
-                            off = 2u * (uint32_t)(a_base[j] + (ho * t_Wo + wo) * t_Fs + ((e[h].y >> 16) & 0x7FFF) * 8);
-                        }
-                        cp_async16_ca(aS + core_off(warp * 2 + j, h * 4 + lq, l8), t_gout + (ok ? off : 0u), ok);
+                for (int i = 0; i < 4; ++i) {
+                    const int hh = a_h[i] - ki, ww = a_w[i] - kj;
+                    bool ok; uint32_t off;
+                    if (t_s1) {
+                        ok = e.y < 0 && (unsigned)hh < (unsigned)t_Ho && (unsigned)ww < (unsigned)t_Wo;
+                        off = (uint32_t)(a_base[i] + e.x);
+                    } else {
+                        // strides are 1 or 2 in practice: shifts for those, a real division otherwise
+                        const int ho = t_sh == 1 ? hh : (t_sh == 2 ? hh >> 1 : hh / t_sh);
+                        const int wo = t_sw == 1 ? ww : (t_sw == 2 ? ww >> 1 : ww / t_sw);
+                        ok = e.y < 0 && hh >= 0 && ww >= 0 && ho * t_sh == hh && wo * t_sw == ww && ho < t_Ho && wo < t_Wo;
+                        off = 2u * (uint32_t)(a_base[i] + (ho * t_Wo + wo) * t_Fs + kf);
                     }
-                // B, K-major: rows n = input channel c, k = (ij, f) contiguous in f; items q = warp*Q + i -> (row block q/2, chunk half q%2)
-                uint32_t wb[2];
-#pragma unroll
-                for (int h = 0; h < 2; ++h)
-                    wb[h] = 2u * (uint32_t)(((e[h].y & 255) * t_kw + ((e[h].y >> 8) & 255)) * t_Cldw + ((e[h].y >> 16) & 0x7FFF) * 8 + t_n0 * t_ldw);
+                    cp_async16_ca(aS + k_dst + i * 4096, t_gout + (ok ? off : 0u), ok);
+                }
+                // B, K-major: rows n = input channel c, k = (ij, f) contiguous in f
+                const uint32_t wb = 2u * (uint32_t)((ki * t_kw + kj) * t_Cldw + kf + t_n0 * t_ldw);
 #pragma unroll 4
-                for (int i = 0; i < Q; ++i) {
-                    const int q = warp * Q + i, blk = q >> 1, h = q & 1;
-                    const int c = blk * 8 + l8;
-                    const bool ok = c < t_C8 && e[h].y < 0;
-                    cp_async16(bS + core_off(blk, h * 4 + lq, l8), t_w + (ok ? wb[h] + 2u * (uint32_t)(c * t_ldw) : 0u), ok);
+                for (int i = 0; i < (BN >> 5); ++i) {
+                    const int c = i * 32 + rlo;
+                    const bool ok = c < t_C8 && e.y < 0;
+                    cp_async16(bS + k_dst + i * 4096, t_w + (ok ? wb + 2u * (uint32_t)(c * t_ldw) : 0u), ok);
                 }
             } else {
-                // this warp owns reduction rows r0 + kb*64 + warp*8 .. +7 (one per l8)
-                const int r = t_r0 + kb * TC_BK + warp * 8 + l8;
-                const bool rok = r < t_r1;
-                const int rc = rok ? r : t_r0;
-                const int b = fdiv(rc, t_fdrows), rem = rc - b * t_HoWo;
-                const int ho = fdiv(rem, t_fdw), wo = rem - ho * t_Wo;
-                const __half* in_row = reinterpret_cast<const __half*>(l_in) + (long long)b * l_in_bs + ((long long)(ho * t_sh) * t_W + wo * t_sw) * t_Cs;
-                const __half* go_row = reinterpret_cast<const __half*>(t_gout) + (long long)b * t_out_bs + (long long)rem * t_Fs;
-                // A, MN-major: 4 quads of kk chunks
-#pragma unroll
-                for (int qd = 0; qd < 4; ++qd) {
-                    const int cc = qd * 4 + lq;
+                // reduction rows r0 + kb*64 .. +63; A, MN-major (rows x kk chunks); B, MN-major: dOut rows, f chunks from n0
+                auto in_row_of = [&](int kl, bool& rok, int& b, int& rem) -> const __half* {
+                    const int r = t_r0 + kb * TC_BK + kl;
+                    rok = r < t_r1;
+                    const int rc = rok ? r : t_r0;
+                    b = fdiv(rc, t_fdrows); rem = rc - b * t_HoWo;
+                    const int ho = fdiv(rem, t_fdw), wo = rem - ho * t_Wo;
+                    return reinterpret_cast<const __half*>(l_in) + (long long)b * l_in_bs + ((long long)(ho * t_sh) * t_W + wo * t_sw) * t_Cs;
+                };
+                auto copy_a = [&](const __half* in_row, bool rok, int kl, int g) {
+                    const int u = g * 8 + t_ch;
                     if (SCALAR_A) {
                         Half8 v;
-                        const int kk = t_m0 + cc * 8;
+                        const int kk = t_m0 + u * 8;
                         int ki = fdiv(kk, geo.fdkw), kj = kk - ki * t_kw;
 #pragma unroll
                         for (int e = 0; e < 8; ++e) {
                             v.v[e] = (rok && kk + e < t_Kf) ? in_row[ki * t_W + kj] : __float2half_rn(0.f);
                             if (++kj == t_kw) { kj = 0; ++ki; }
                         }
-                        *reinterpret_cast<Half8*>(sgen + (aS - sbase) + core_off(cc, warp, l8)) = v;
+                        *reinterpret_cast<Half8*>(sgen + (aS - sbase) + sw_mn_off(u, kl)) = v;
                     } else {
-                        cp_async16_ca(aS + core_off(cc, warp, l8), in_row + w_koff[qd], rok && w_kok[qd]);
+                        cp_async16_ca(aS + sw_mn_off(u, kl), in_row + w_koff[g], rok && w_kok[g]);
                     }
-                }
-                // B, MN-major: Q quads of f chunks
-#pragma unroll 4
-                for (int i = 0; i < Q; ++i) {
-                    const int nch = i * 4 + lq, f = t_n0 + nch * 8;
-                    const bool ok = rok && f < t_Fs;
-                    cp_async16(bS + core_off(nch, warp, l8), go_row + (ok ? f : 0), ok);
+                };
+                auto go_of = [&](int kl, int& left) -> const char* {
+                    const int r = t_r0 + kb * TC_BK + kl;
+                    const bool rok = r < t_r1;
+                    const int rc = rok ? r : t_r0;
+                    const int b = fdiv(rc, t_fdrows), rem = rc - b * t_HoWo;
+                    left = rok ? 2 * (t_Fs - t_n0) : 0;
+                    return t_gout + 2 * ((long long)b * t_out_bs + (long long)rem * t_Fs + t_n0);
+                };
+                if (t_cs == 3) {
+                    const char* go_row[2]; int go_left[2];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int kl = h * 32 + rlo;
+                        bool rok; int b, rem;
+                        const __half* in_row = in_row_of(kl, rok, b, rem);
+                        go_row[h] = t_gout + 2 * ((long long)b * t_out_bs + (long long)rem * t_Fs + t_n0);
+                        go_left[h] = rok ? 2 * (t_Fs - t_n0) : 0;
+                        copy_a(in_row, rok, kl, 0);
+                        if (t_ga == 2) copy_a(in_row, rok, kl, 1);
+                    }
+                    if (BN == 32) load_b_mn(bS, 64, go_of);
+                    else load_b_mn(bS, 64, [&](int kl, int& left) -> const char* { left = go_left[kl >> 5]; return go_row[kl >> 5]; });
+                } else {
+                    const int rpw = 32 >> t_cs, kl = warp * rpw + (lane >> t_cs);      // 16 or 8 rows per warp
+                    if (kl < 64) {
+                        bool rok; int b, rem;
+                        const __half* in_row = in_row_of(kl, rok, b, rem);
+                        copy_a(in_row, rok, kl, 0);
+                    }
+                    load_b_mn(bS, 64, go_of);
                 }
             }
         };
@@ -547,25 +640,29 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
         // =================================================================== MMA issuer
         if (lane == 0) {
             int st = 0; uint32_t fph = 0;     // ring stage and the parity of its "full" barrier
-            const uint64_t dA0 = umma_desc(sA), dB0 = umma_desc(sB);
+            // K-major operands advance 32 bytes per K = 16 step inside the 128-byte rows, MN-major ones two 8-k atoms
+            const uint64_t dA0 = MODE == TC_WGRAD ? umma_desc_sw128(sA, 8192, 1024) : umma_desc_sw128(sA, 16, 1024);
+            const uint64_t dB0 = MODE == TC_DGRAD ? umma_desc_sw128(sB, 16, 1024) : umma_desc_sw128(sB, 8192, 1024);
+            const uint64_t a_step = MODE == TC_WGRAD ? (2048 >> 4) : (32 >> 4), b_step = MODE == TC_DGRAD ? (32 >> 4) : (2048 >> 4);
             for (int j = 0; j < my_tiles; ++j) {
                 const int acc = j & 1;
                 if (j >= 2) mbar_wait(sTEmpty + acc * 8, (uint32_t)(((j >> 1) - 1) & 1));   // epilogue drained this accumulator
                 const uint32_t tacc = tmem + (uint32_t)(acc * acc_cols);
-                int nk = 1; uint32_t idesc = 0;
+                int nk = 1, klast = 4; uint32_t idesc = 0;
                 for (int kb = 0; kb < nk; ++kb) {
                     mbar_wait(sFull + st * 8, fph);
                     fence_proxy_async();     // the stage was written through the generic proxy (cp.async), UMMA reads it through the async proxy
                     tc_fence_after();
                     if (kb == 0) {       // the descriptor was fetched by the loaders long before this stage was published
                         const TcTile& T = ring[j % TC_RING];
-                        nk = T.nk;
+                        nk = T.nk; klast = T.klast;
                         idesc = umma_idesc(MODE == TC_WGRAD ? 1 : 0, MODE == TC_DGRAD ? 0 : 1, T.n_umma);
                     }
                     const uint64_t dA = dA0 + (uint64_t)((uint32_t)(st * TC_A_BYTES) >> 4), dB = dB0 + (uint64_t)(((uint32_t)st * B_BYTES) >> 4);
+                    const int nks = kb == nk - 1 ? klast : TC_BK / 16;
 #pragma unroll
                     for (int ks = 0; ks < TC_BK / 16; ++ks)
-                        umma_f16(tacc, dA + (uint64_t)(ks * 16), dB + (uint64_t)(ks * 16), idesc, (kb | ks) ? 1u : 0u);
+                        if (ks < nks) umma_f16(tacc, dA + a_step * ks, dB + b_step * ks, idesc, (kb | ks) ? 1u : 0u);
                     umma_commit(sEmpty + st * 8);
                     if (++st == STAGES) { st = 0; fph ^= 1u; }
                 }
