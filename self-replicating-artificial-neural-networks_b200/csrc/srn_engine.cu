@@ -798,7 +798,7 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
                     tt[t].p = g.h[i];
                     tc_describe_tile(tt[t], t - pre[i], nb, BN, mode, g.tc == 2);
                 }
-            std::stable_sort(tt.begin(), tt.end(), [](const TcTile& a, const TcTile& b) { return a.nk > b.nk; });
+            std::stable_sort(tt.begin(), tt.end(), [](const TcTile& a, const TcTile& b) { return a.nk * a.nsub > b.nk * b.nsub; });
             TcTile* dt = nullptr;
             CK(cudaMalloc(&dt, tt.size() * sizeof(TcTile)));
             CK(cudaMemcpy(dt, tt.data(), tt.size() * sizeof(TcTile), cudaMemcpyHostToDevice));

@@ -59,8 +59,16 @@ __host__ __device__ inline int round_up8(int v) { return (v + 7) & ~7; }
 __host__ __device__ inline int tc_k_fwd(const Prob& p) { return p.kh * p.kw * p.Cs; }
 __host__ __device__ inline int tc_k_dgrad(const Prob& p) { return p.kh * p.kw * p.Fs; }
 
+// Forward problems whose reduction fits one k-block and that have many row tiles (first layers, per-pixel Dense) are cut
+// into tiles of TC_SUB consecutive 128-row sub-tiles: one descriptor, one loader/issuer/epilogue set-up for all of them.
+constexpr int TC_SUB = 8;
+__host__ __device__ inline int tc_fwd_sub(const Prob& p, int nb) {
+    const int mt = (nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM;
+    return (tc_k_fwd(p) <= TC_BK && mt >= 8 * TC_SUB) ? TC_SUB : 1;
+}
 __host__ __device__ inline int tc_tiles_fwd(const Prob& p, int nb, int BN) {
-    return ((nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM) * ((p.F + BN - 1) / BN);
+    const int mt = (nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM, sub = tc_fwd_sub(p, nb);
+    return ((mt + sub - 1) / sub) * ((p.F + BN - 1) / BN);
 }
 __host__ __device__ inline int tc_tiles_dgrad(const Prob& p, int nb, int BN) {
     return ((nb * p.H * p.W + TC_BM - 1) / TC_BM) * ((p.C + BN - 1) / BN);
@@ -174,6 +182,24 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// 32 consecutive fp32 columns of this thread's TMEM lane (one wait for the whole batch)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+}
+// two fp32 accumulators -> packed fp16 (round to nearest even), low half = first
+__device__ __forceinline__ __half2 pack_h2(uint32_t lo, uint32_t hi) {
+    return __floats2half2_rn(__uint_as_float(lo), __uint_as_float(hi));
+}
+
 // byte offset of a 16-byte chunk inside an operand tile (tile bases are 1024-byte aligned)
 __device__ __forceinline__ uint32_t sw_k_off(int row, int chunk) {    // K-major: row = m/n index, chunk = k chunk 0..7
     return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
@@ -211,7 +237,8 @@ struct __align__(16) TcTile {
     FastDiv fd_c;      // channel stride of the k index: Cs (fwd, wgrad) or Fs (dgrad)
     FastDiv fd_kw;
     int klast;         // K = 16 steps of the last k-block (1..4): the tail of the reduction is neither loaded nor multiplied
-    unsigned char pad[256 - sizeof(Prob) - 9 * sizeof(int) - 4 * sizeof(FastDiv)];
+    int nsub;          // 128-row sub-tiles m0, m0 + 128, .. covered by this descriptor (forward only, else 1)
+    unsigned char pad[256 - sizeof(Prob) - 10 * sizeof(int) - 4 * sizeof(FastDiv)];
 };
 static_assert(sizeof(TcTile) == 256, "TcTile is one 256-byte table entry / ring slot");
 
@@ -223,11 +250,12 @@ inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool
     const int HoWo = p.Ho * p.Wo;
     const int KK = p.kh * p.kw;
     const int Kf = SCALAR_A ? KK : KK * p.Cs;
-    t.r0 = 0; t.r1 = 0;
+    t.r0 = 0; t.r1 = 0; t.nsub = 1;
     if (MODE == TC_FWD) {
         t.Mrows = nb * HoWo; t.Ncols = p.F;
-        const int tn = (t.Ncols + BN - 1) / BN;
-        t.m0 = (tile / tn) * TC_BM; t.n0 = (tile % tn) * BN;
+        const int tn = (t.Ncols + BN - 1) / BN, sub = tc_fwd_sub(p, nb), mt = (t.Mrows + TC_BM - 1) / TC_BM;
+        t.m0 = (tile / tn) * sub * TC_BM; t.n0 = (tile % tn) * BN;
+        t.nsub = min(sub, mt - (tile / tn) * sub);
         t.nk = (Kf + TC_BK - 1) / TC_BK;
     } else if (MODE == TC_DGRAD) {
         t.Mrows = nb * p.H * p.W; t.Ncols = p.C;
@@ -351,7 +379,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
         bool t_lut = false, t_s1 = true;
         KGeo geo{};
         FastDiv t_fdrows{}, t_fdw{};
-        int lj = 0, lnk = 0;
+        int lj = 0, lnk = 0, lsub = 1, t_Mrows = 0;
         auto geo_of = [&](const TcTile& T) {
             const Prob& p = T.p;
             KGeo g;
@@ -378,7 +406,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             fill_lut(lj + 1);
             const Prob& p = T.p;
             { const __half* in = resolve_in(p, I, l_in_bs); l_in = reinterpret_cast<const char*>(in); }
-            lnk = T.nk;
+            lnk = T.nk; lsub = T.nsub; t_Mrows = T.Mrows;
             t_w = reinterpret_cast<const char*>(p.w); t_gout = reinterpret_cast<const char*>(p.gout);
             t_ldw = p.ldw; t_Cs = p.Cs; t_Fs = p.Fs; t_kw = p.kw; t_W = p.W;
             t_Wo = p.Wo; t_Ho = p.Ho; t_sh = p.sh; t_sw = p.sw; t_n0 = T.n0; t_out_bs = p.out_bs; t_HoWo = p.Ho * p.Wo;
@@ -394,19 +422,10 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             if (MODE == TC_FWD) {
                 t_cs = (T.nk == 1 && t_Kf <= 32) ? (t_Kf <= 16 ? 1 : 2) : 3;
                 t_items = 1 << (t_cs - 1);
-                const int rpw = 32 >> t_cs, subr = lane >> t_cs;
                 t_ch = lane & ((1 << t_cs) - 1);
+                const int rpw = 32 >> t_cs, subr = lane >> t_cs;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int r = i * rpw * 8 + warp * rpw + subr;       // < 128 for i < t_items
-                    const int m = T.m0 + r;
-                    a_ok[i] = i < t_items && m < T.Mrows;
-                    const int mc = a_ok[i] ? m : 0;
-                    const int b = fdiv(mc, t_fdrows), rem = mc - b * t_HoWo;
-                    const int ho = fdiv(rem, t_fdw), wo = rem - ho * t_Wo;
-                    a_off[i] = 2u * ((uint32_t)b * (uint32_t)l_in_bs + (uint32_t)(((ho * t_sh) * t_W + wo * t_sw) * t_Cs));
-                    if (i < 2) a_dst[i] = sw_k_off(r & 127, t_ch);
-                }
+                for (int i = 0; i < 2; ++i) a_dst[i] = sw_k_off((i * rpw * 8 + warp * rpw + subr) & 127, t_ch);
             } else if (MODE == TC_DGRAD) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
@@ -439,6 +458,18 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                         w_koff[g] = (i * t_W + j) * t_Cs + cp;
                     }
                 }
+            }
+        };
+        auto fwd_rows = [&](int m0) {        // FWD: this thread's rows of the sub-tile starting at row m0
+            const int rpw = 32 >> t_cs, subr = lane >> t_cs;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int m = m0 + i * rpw * 8 + warp * rpw + subr;
+                a_ok[i] = i < t_items && m < t_Mrows;
+                const int mc = a_ok[i] ? m : 0;
+                const int b = fdiv(mc, t_fdrows), rem = mc - b * t_HoWo;
+                const int ho = fdiv(rem, t_fdw), wo = rem - ho * t_Wo;
+                a_off[i] = 2u * ((uint32_t)b * (uint32_t)l_in_bs + (uint32_t)(((ho * t_sh) * t_W + wo * t_sw) * t_Cs));
             }
         };
         auto k_entry = [&](int chunk) -> int2 {
@@ -627,12 +658,15 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
         int sb = 0; uint32_t ph = 1;     // ring stage and the parity a fresh "empty" barrier passes immediately
         for (lj = 0; lj < my_tiles; ++lj) {
             loader_enter_tile();
-            for (int kb = 0; kb < lnk; ++kb) {
-                mbar_wait(sEmpty + sb * 8, ph);
-                load_stage(sb, kb);
-                if (SCALAR_A) fence_proxy_async();       // the element-wise gather used ordinary shared-memory stores
-                cp_async_arrive_noinc(sFull + sb * 8);   // fires when this thread's copies for the stage have landed
-                if (++sb == STAGES) { sb = 0; ph ^= 1u; }
+            for (int s = 0; s < lsub; ++s) {
+                if (MODE == TC_FWD) fwd_rows(t_m0 + s * TC_BM);
+                for (int kb = 0; kb < lnk; ++kb) {
+                    mbar_wait(sEmpty + sb * 8, ph);
+                    load_stage(sb, kb);
+                    if (SCALAR_A) fence_proxy_async();       // the element-wise gather used ordinary shared-memory stores
+                    cp_async_arrive_noinc(sFull + sb * 8);   // fires when this thread's copies for the stage have landed
+                    if (++sb == STAGES) { sb = 0; ph ^= 1u; }
+                }
             }
         }
         cp_async_wait_all();
@@ -644,38 +678,41 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             const uint64_t dA0 = MODE == TC_WGRAD ? umma_desc_sw128(sA, 8192, 1024) : umma_desc_sw128(sA, 16, 1024);
             const uint64_t dB0 = MODE == TC_DGRAD ? umma_desc_sw128(sB, 16, 1024) : umma_desc_sw128(sB, 8192, 1024);
             const uint64_t a_step = MODE == TC_WGRAD ? (2048 >> 4) : (32 >> 4), b_step = MODE == TC_DGRAD ? (32 >> 4) : (2048 >> 4);
+            int jj = 0;                       // accumulator hand-overs so far (one per sub-tile)
             for (int j = 0; j < my_tiles; ++j) {
-                const int acc = j & 1;
-                if (j >= 2) mbar_wait(sTEmpty + acc * 8, (uint32_t)(((j >> 1) - 1) & 1));   // epilogue drained this accumulator
-                const uint32_t tacc = tmem + (uint32_t)(acc * acc_cols);
-                int nk = 1, klast = 4; uint32_t idesc = 0;
-                for (int kb = 0; kb < nk; ++kb) {
-                    mbar_wait(sFull + st * 8, fph);
-                    fence_proxy_async();     // the stage was written through the generic proxy (cp.async), UMMA reads it through the async proxy
-                    tc_fence_after();
-                    if (kb == 0) {       // the descriptor was fetched by the loaders long before this stage was published
-                        const TcTile& T = ring[j % TC_RING];
-                        nk = T.nk; klast = T.klast;
-                        idesc = umma_idesc(MODE == TC_WGRAD ? 1 : 0, MODE == TC_DGRAD ? 0 : 1, T.n_umma);
-                    }
-                    const uint64_t dA = dA0 + (uint64_t)((uint32_t)(st * TC_A_BYTES) >> 4), dB = dB0 + (uint64_t)(((uint32_t)st * B_BYTES) >> 4);
-                    const int nks = kb == nk - 1 ? klast : TC_BK / 16;
+                int nk = 1, klast = 4, nsub = 1; uint32_t idesc = 0;
+                for (int s = 0; s < nsub; ++s, ++jj) {
+                    const int acc = jj & 1;
+                    if (jj >= 2) mbar_wait(sTEmpty + acc * 8, (uint32_t)(((jj >> 1) - 1) & 1));   // epilogue drained this accumulator
+                    const uint32_t tacc = tmem + (uint32_t)(acc * acc_cols);
+                    for (int kb = 0; kb < nk; ++kb) {
+                        mbar_wait(sFull + st * 8, fph);
+                        fence_proxy_async();     // the stage was written through the generic proxy (cp.async), UMMA reads it through the async proxy
+                        tc_fence_after();
+                        if ((s | kb) == 0) {     // the descriptor was fetched by the loaders long before this stage was published
+                            const TcTile& T = ring[j % TC_RING];
+                            nk = T.nk; klast = T.klast; nsub = T.nsub;
+                            idesc = umma_idesc(MODE == TC_WGRAD ? 1 : 0, MODE == TC_DGRAD ? 0 : 1, T.n_umma);
+                        }
+                        const uint64_t dA = dA0 + (uint64_t)((uint32_t)(st * TC_A_BYTES) >> 4), dB = dB0 + (uint64_t)(((uint32_t)st * B_BYTES) >> 4);
+                        const int nks = kb == nk - 1 ? klast : TC_BK / 16;
 #pragma unroll
-                    for (int ks = 0; ks < TC_BK / 16; ++ks)
-                        if (ks < nks) umma_f16(tacc, dA + a_step * ks, dB + b_step * ks, idesc, (kb | ks) ? 1u : 0u);
-                    umma_commit(sEmpty + st * 8);
-                    if (++st == STAGES) { st = 0; fph ^= 1u; }
+                        for (int ks = 0; ks < TC_BK / 16; ++ks)
+                            if (ks < nks) umma_f16(tacc, dA + a_step * ks, dB + b_step * ks, idesc, (kb | ks) ? 1u : 0u);
+                        umma_commit(sEmpty + st * 8);
+                        if (++st == STAGES) { st = 0; fph ^= 1u; }
+                    }
+                    umma_commit(sTFull + acc * 8);
                 }
-                umma_commit(sTFull + acc * 8);
             }
         }
     } else {
         // =================================================================== epilogue (4 warps)
         const int ewarp = warp & 3;      // TMEM lanes 32 * ewarp .. + 31
-        auto epilogue = [&](const TcTile& T, uint32_t tacc, int ewarp) {
+        auto epilogue = [&](const TcTile& T, int sub, uint32_t tacc, int ewarp) {
             const Prob& p = T.p;
             const int Cs = p.Cs, Fs = p.Fs;
-            const int mrow = T.m0 + ewarp * 32 + lane, n0 = T.n0, Ncols = T.Ncols;
+            const int mrow = T.m0 + sub * TC_BM + ewarp * 32 + lane, n0 = T.n0, Ncols = T.Ncols;
             const uint32_t trow = tacc + ((uint32_t)(ewarp * 32) << 16);
             if (MODE == TC_FWD) {
                 const int HoWo = p.Ho * p.Wo;
@@ -685,21 +722,35 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                     const int b = fdiv(mrow, T.fd_rows), rem = mrow - b * HoWo;
                     orow = p.out + (long long)b * p.out_bs + (long long)rem * Fs;
                 }
-                for (int cb = 0; cb < T.n_umma; cb += 16) {
-                    float v[16];
-                    tmem_ld16(trow + cb, v);
+                // 32 accumulator columns per TMEM read.  Linear and ReLU layers round, add the bias and clamp as packed
+                // halves (one rounding per TensorFlow op, as the float path does); sigmoid goes through fp32.
+                for (int cb = 0; cb < T.n_umma; cb += 32) {
+                    uint32_t r[32];
+                    tmem_ld32(trow + cb, r);
                     if (!orow) continue;
 #pragma unroll
-                    for (int h8 = 0; h8 < 2; ++h8) {
+                    for (int h8 = 0; h8 < 4; ++h8) {
                         const int n = n0 + cb + h8 * 8;
                         if (n >= Ncols) break;
                         const Half8 bv = ld8(bias + n);      // bias arrays are padded to 8 elements in the arena
                         Half8 o;
+                        if (act != 2 && n + 8 <= Ncols) {
+                            const __half2* b2 = reinterpret_cast<const __half2*>(&bv);
+                            __half2* o2 = reinterpret_cast<__half2*>(&o);
+                            const __half2 zero = __float2half2_rn(0.f);
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            float z = 0.f;
-                            if (n + j < Ncols) z = act_forward(rh(rh(v[h8 * 8 + j]) + __half2float(bv.v[j])), act);
-                            o.v[j] = __float2half_rn(z);
+                            for (int j = 0; j < 4; ++j) {
+                                __half2 z = __hadd2(pack_h2(r[h8 * 8 + 2 * j], r[h8 * 8 + 2 * j + 1]), b2[j]);
+                                if (act == 1) z = __hmax2_nan(z, zero);
+                                o2[j] = z;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                float z = 0.f;
+                                if (n + j < Ncols) z = act_forward(rh(rh(__uint_as_float(r[h8 * 8 + j])) + __half2float(bv.v[j])), act);
+                                o.v[j] = __float2half_rn(z);
+                            }
                         }
                         st8(orow + n, o);
                     }
@@ -711,21 +762,32 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                     const int b = fdiv(mrow, T.fd_rows), rem = mrow - b * HW;
                     drow = p.din + (long long)b * p.in_bs + (long long)rem * Cs;
                 }
-                for (int cb = 0; cb < T.n_umma; cb += 16) {
-                    float v[16];
-                    tmem_ld16(trow + cb, v);
+                const bool accum = p.din_acc != 0;
+                for (int cb = 0; cb < T.n_umma; cb += 32) {
+                    uint32_t r[32];
+                    tmem_ld32(trow + cb, r);
                     if (!drow) continue;
+                    Half8 prev[4];
+                    if (accum) {
 #pragma unroll
-                    for (int h8 = 0; h8 < 2; ++h8) {
+                        for (int h8 = 0; h8 < 4; ++h8)
+                            if (n0 + cb + h8 * 8 < Ncols) prev[h8] = ld8(drow + n0 + cb + h8 * 8);
+                    }
+#pragma unroll
+                    for (int h8 = 0; h8 < 4; ++h8) {
                         const int c = n0 + cb + h8 * 8;
                         if (c >= Ncols) break;
                         Half8 o;
-                        if (p.din_acc) o = ld8(drow + c);
+                        __half2* o2 = reinterpret_cast<__half2*>(&o);
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            float x = (c + j < Ncols) ? v[h8 * 8 + j] : 0.f;
-                            if (p.din_acc) x = rh(x) + __half2float(o.v[j]);
-                            o.v[j] = __float2half_rn(x);
+                        for (int j = 0; j < 4; ++j) {
+                            __half2 z = pack_h2(r[h8 * 8 + 2 * j], r[h8 * 8 + 2 * j + 1]);
+                            if (accum) z = __hadd2(z, reinterpret_cast<const __half2*>(&prev[h8])[j]);
+                            o2[j] = z;
+                        }
+                        if (c + 8 > Ncols) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) if (c + j >= Ncols) o.v[j] = __float2half_rn(0.f);
                         }
                         st8(drow + c, o);
                     }
@@ -759,15 +821,20 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                 }
             }
         };
+        int jj = 0;
         for (int j = 0; j < my_tiles; ++j) {
-            const int acc = j & 1;
-            // long tiles: back off while waiting so that the spin does not take issue slots from the loaders
-            if (ring[j % TC_RING].nk > 32) mbar_wait_relaxed(sTFull + acc * 8, (uint32_t)((j / 2) & 1));
-            else mbar_wait(sTFull + acc * 8, (uint32_t)((j / 2) & 1));
-            tc_fence_after();
-            epilogue(ring[j % TC_RING], tmem + (uint32_t)(acc * acc_cols), ewarp);
-            tc_fence_before();
-            mbar_arrive(sTEmpty + acc * 8);
+            const TcTile& T = ring[j % TC_RING];
+            const int nsub = T.nsub;
+            for (int s = 0; s < nsub; ++s, ++jj) {
+                const int acc = jj & 1;
+                // long tiles: back off while waiting so that the spin does not take issue slots from the loaders
+                if (T.nk > 32) mbar_wait_relaxed(sTFull + acc * 8, (uint32_t)((jj >> 1) & 1));
+                else mbar_wait(sTFull + acc * 8, (uint32_t)((jj >> 1) & 1));
+                tc_fence_after();
+                epilogue(T, s, tmem + (uint32_t)(acc * acc_cols), ewarp);
+                tc_fence_before();
+                mbar_arrive(sTEmpty + acc * 8);
+            }
         }
     }
     tc_fence_before();
