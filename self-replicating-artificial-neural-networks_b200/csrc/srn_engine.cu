@@ -758,7 +758,7 @@ static int pass_items(const Group& g, const Prob& p, int pass, int nb) {
             if (pass == P_BWD_EW) return p.din ? ew_blocks(in_rows, p.Cs) : 0;
             return 0;
         case SRN_KIND_CONCAT:
-            if (pass == P_FWD) return copy_blocks(p, nb);
+            if (pass == P_FWD) return copy_blocks_fwd(p, nb);
             if (pass == P_BWD_EW) return p.din ? copy_blocks(p, nb) : 0;
             return 0;
     }
@@ -1377,16 +1377,17 @@ extern "C" int srn_debug_profile_detail(srn_engine* h, int32_t nb, int32_t cap, 
     return n;
 }
 
-// Shapes of the problems of one launch bucket (debug hook): 16 ints per problem
-// {H, W, C, Cs, Ho, Wo, F, Fs, kh, kw, sh, sw, act, din_acc, individual, has din}.
+// Shapes of the problems of one launch bucket (debug hook): 20 ints per problem
+// {H, W, C, Cs, Ho, Wo, F, Fs, kh, kw, sh, sw, act, din_acc, individual, has din, coff, n_el, Cj, in_sel}.
 extern "C" int srn_debug_group_probs(srn_engine* h, int32_t group, int32_t cap, int32_t* out) {
     if (!h || !out || group < 0 || group >= (int)h->groups.size()) return -1;
     int n = 0;
     for (const Prob& p : h->groups[group].h) {
         if (n >= cap) break;
-        int32_t* o = out + 16 * (size_t)n++;
+        int32_t* o = out + 20 * (size_t)n++;
         o[0] = p.H; o[1] = p.W; o[2] = p.C; o[3] = p.Cs; o[4] = p.Ho; o[5] = p.Wo; o[6] = p.F; o[7] = p.Fs;
         o[8] = p.kh; o[9] = p.kw; o[10] = p.sh; o[11] = p.sw; o[12] = p.act; o[13] = p.din_acc; o[14] = p.indiv; o[15] = p.din != nullptr;
+        o[16] = p.coff; o[17] = p.n_el; o[18] = p.Cj; o[19] = p.in_sel;
     }
     return n;
 }

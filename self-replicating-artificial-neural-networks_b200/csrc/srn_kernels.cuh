@@ -538,6 +538,15 @@ __host__ __device__ inline int copy_blocks(const Prob& p, int nb) {
     const long long per = copy_mode(p) ? (long long)(p.n_el / p.C) * (p.Cs / 8) : p.n_el;
     return (int)(((long long)nb * per + EW_PER_CTA - 1) / EW_PER_CTA);
 }
+// Forward compaction into one destination row (flatten + concatenate of a tensor whose channel count is not a multiple
+// of 8, or at an unaligned offset): the work unit is an aligned 16-byte chunk of the DESTINATION, gathered element by
+// element from the padded source, so that the stores are full chunks instead of eight 2-byte stores per source chunk.
+__host__ __device__ inline bool copy_dst_major(const Prob& p) { return copy_mode(p) == 1 && p.Cj == p.n_el; }
+__host__ __device__ inline int copy_blocks_fwd(const Prob& p, int nb) {
+    if (!copy_dst_major(p)) return copy_blocks(p, nb);
+    const long long per = (p.coff + p.n_el + 7) / 8 - p.coff / 8;
+    return (int)(((long long)nb * per + EW_PER_CTA - 1) / EW_PER_CTA);
+}
 
 static __global__ void __launch_bounds__(EW_THREADS)
 k_copy(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, Inputs I, int bwd) {
@@ -546,22 +555,53 @@ k_copy(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob
     if (bwd && p.din == nullptr) return;
     const int blk = blockIdx.x - prefix[pi];
     const int mode = copy_mode(p);
-    const int nq = mode ? p.Cs / 8 : 1;
-    const int per = mode ? (p.n_el / p.C) * nq : p.n_el;      // units per sample
-    const long long total = (long long)nb * per;
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
-    long long u = (long long)blk * EW_PER_CTA + threadIdx.x;
+    if (!bwd && copy_dst_major(p)) {
+        const int q0 = p.coff >> 3, nqd = ((p.coff + p.n_el + 7) >> 3) - q0;
+        const unsigned total = (unsigned)nb * (unsigned)nqd;
+        unsigned u = (unsigned)blk * EW_PER_CTA + threadIdx.x;
+#pragma unroll 1
+        for (int i = 0; i < EW_PER_THREAD; ++i, u += EW_THREADS) {
+            if (u >= total) break;
+            const unsigned b = u / (unsigned)nqd; const int q = q0 + (int)(u - b * (unsigned)nqd);
+            const int e0 = q * 8 - p.coff;                       // flat source element of the chunk's first slot (may be < 0)
+            const int ec = max(e0, 0);
+            int sr = (int)((unsigned)ec / (unsigned)p.C), sc = ec - sr * p.C;
+            const __half* src = in + (long long)b * in_bs;
+            __half* dst = p.out + (long long)b * p.out_bs + q * 8;
+            Half8 v;
+            bool full = e0 >= 0 && e0 + 8 <= p.n_el;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int e = e0 + j;
+                if (e >= 0 && e < p.n_el) {
+                    v.v[j] = src[(long long)sr * p.Cs + sc];
+                    if (++sc == p.C) { sc = 0; ++sr; }
+                    if (!full) dst[j] = v.v[j];
+                }
+            }
+            if (full) st8(dst, v);
+        }
+        return;
+    }
+    const int nq = mode ? p.Cs / 8 : 1;
+    const int per = mode ? (p.n_el / p.C) * nq : p.n_el;      // units per sample
+    const unsigned total = (unsigned)nb * (unsigned)per;      // units of the whole batch fit 32 bits (srn_build checks tensor sizes)
+    unsigned u = (unsigned)blk * EW_PER_CTA + threadIdx.x;
 #pragma unroll 1
     for (int i = 0; i < EW_PER_THREAD; ++i, u += EW_THREADS) {
         if (u >= total) break;
-        const long long b = u / per; const int uu = (int)(u - b * per);
+        const unsigned bb = u / (unsigned)per; const int uu = (int)(u - bb * (unsigned)per);
+        const long long b = bb;
         int sr, sc;
-        if (mode) { sr = uu / nq; sc = (uu - sr * nq) * 8; } else { sr = uu / p.C; sc = uu - sr * p.C; }
+        if (mode) { sr = (int)((unsigned)uu / (unsigned)nq); sc = (uu - sr * nq) * 8; }
+        else if (p.C == 1) { sr = uu; sc = 0; }
+        else { sr = (int)((unsigned)uu / (unsigned)p.C); sc = uu - sr * p.C; }
         if (sc >= p.C) continue;                                // a chunk that is pad only
         const long long so = b * in_bs + (long long)sr * p.Cs + sc;
         const int ee = sr * p.C + sc;                           // flat index of the first element of the unit
-        int dr = ee / p.Cj, dc = ee - dr * p.Cj;
+        int dr = (int)((unsigned)ee / (unsigned)p.Cj), dc = ee - dr * p.Cj;
         if (mode == 2) {
             const long long dd = b * p.out_bs + (long long)dr * p.Fs + p.coff + dc;
             if (!bwd) st8(p.out + dd, ld8(in + so));

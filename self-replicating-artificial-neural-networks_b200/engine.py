@@ -319,8 +319,8 @@ class Engine:
         return int(self._lib.srn_debug_launch_groups(self._h))
 
     def group_probs(self, group: int, cap: int = 4096):
-        """Problem shapes of one launch bucket, [n, 16] (see srn_debug_group_probs in srn_engine.cu)."""
-        out = np.zeros((cap, 16), np.int32)
+        """Problem shapes of one launch bucket, [n, 20] (see srn_debug_group_probs in srn_engine.cu)."""
+        out = np.zeros((cap, 20), np.int32)
         n = int(self._lib.srn_debug_group_probs(self._h, group, cap, _ptr(out)))
         if n < 0:
             raise RuntimeError('srn_debug_group_probs failed')

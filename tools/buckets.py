@@ -44,7 +44,8 @@ if __name__ == '__main__':
     print(f'total serialised kernel time {total:.3f} ms/step over {len(rows)} (category, bucket) rows')
     print('\n'.join(lines[:70]))
     for g in sys.argv[3:]:
-        print('bucket', g, '{H, W, C, Cs, Ho, Wo, F, Fs, kh, kw, sh, sw, act, din_acc, individual, has din}')
+        print('bucket', g, '{H, W, C, Cs, Ho, Wo, F, Fs, kh, kw, sh, sw, act, din_acc, individual, has din, coff, n_el, Cj, in_sel}')
+        np.set_printoptions(linewidth=200, threshold=100000)
         print(eng.group_probs(int(g)))
     if out:
         pathlib.Path(out).write_text('\n'.join(lines) + '\n')
