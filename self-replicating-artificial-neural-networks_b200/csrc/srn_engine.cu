@@ -798,6 +798,25 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
                     tt[t].p = g.h[i];
                     tc_describe_tile(tt[t], t - pre[i], nb, BN, mode, g.tc == 2);
                 }
+            if (pass == P_FWD && g.tc == 1) {
+                // split-K scratch: zeroed once, every launch leaves it zeroed (srn_gemm_tc.cuh)
+                for (int i = 0; i < np; ++i) {
+                    if (tc_fwd_split(g.h[i], nb, BN) <= 1) continue;
+                    const Prob& p = g.h[i];
+                    const size_t rows = (size_t)nb * p.Ho * p.Wo;
+                    const size_t acc_bytes = rows * p.Fs * sizeof(float);
+                    const size_t cnt_ints = 4 * ((rows + TC_BM - 1) / TC_BM) * ((p.F + BN - 1) / BN);
+                    char* buf = nullptr;
+                    CK(cudaMalloc(&buf, acc_bytes + cnt_ints * sizeof(int)));
+                    CK(cudaMemset(buf, 0, acc_bytes + cnt_ints * sizeof(int)));
+                    h->scratch_prefix.push_back(reinterpret_cast<int*>(buf));
+                    h->device_bytes += (long long)(acc_bytes + cnt_ints * sizeof(int));
+                    for (int t = pre[i]; t < pre[i + 1]; ++t) {
+                        tt[t].sk_acc = reinterpret_cast<float*>(buf);
+                        tt[t].sk_cnt = reinterpret_cast<int*>(buf + acc_bytes);
+                    }
+                }
+            }
             std::stable_sort(tt.begin(), tt.end(), [](const TcTile& a, const TcTile& b) { return a.nk * a.nsub > b.nk * b.nsub; });
             TcTile* dt = nullptr;
             CK(cudaMalloc(&dt, tt.size() * sizeof(TcTile)));

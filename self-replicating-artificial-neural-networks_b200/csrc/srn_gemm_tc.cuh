@@ -41,7 +41,8 @@ constexpr int TC_WGRAD_ROWS = 4096;   // reduction rows per wgrad CTA (64 k-bloc
 
 enum { TC_FWD = 0, TC_DGRAD = 1, TC_WGRAD = 2 };
 
-constexpr int TC_RING = 32;           // tile descriptors in shared memory: epilogue <= 10 tiles behind the loader, 4 ahead
+constexpr int TC_RING = 24;           // tile descriptors in shared memory: epilogue <= 10 tiles behind the loader, 4 ahead
+constexpr int TC_TILE_BYTES = 320;    // one tile descriptor (table entry / ring slot)
 constexpr int TC_DESC_AHEAD = 4;
 constexpr int TC_LUT = 512;            // 16-byte k chunks per lookup table: reductions up to 4096 elements, longer ones compute on the fly
 // Pipeline depth per N tile: BN <= 64 keeps two CTAs per SM (4 stages each), wider tiles take the SM alone with as
@@ -50,7 +51,7 @@ constexpr int TC_LUT = 512;            // 16-byte k chunks per lookup table: red
 __host__ __device__ inline int tc_stages(int BN) { return BN <= 64 ? 4 : (BN <= 128 ? 3 : 4); }
 // B tiles are stored with 128-byte rows (swizzle-128B atoms), so a 32-wide MN-major tile takes the room of a 64-wide one
 __host__ __device__ inline int tc_b_bytes(int BN) { return (BN < 64 ? 64 : BN) * TC_BK * 2; }
-__host__ __device__ inline int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + tc_b_bytes(BN)) + 256 + TC_RING * 256 + 2 * TC_LUT * 8; }
+__host__ __device__ inline int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + tc_b_bytes(BN)) + 256 + TC_RING * TC_TILE_BYTES + 2 * TC_LUT * 8; }
 __host__ __device__ inline int tc_acc_cols(int BN) { return BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256)); }
 __host__ __device__ inline int tc_tmem_cols(int BN) { return 2 * tc_acc_cols(BN); }     // two accumulators
 __host__ __device__ inline int round_up8(int v) { return (v + 7) & ~7; }
@@ -66,9 +67,16 @@ __host__ __device__ inline int tc_fwd_sub(const Prob& p, int nb) {
     const int mt = (nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM;
     return (tc_k_fwd(p) <= TC_BK && mt >= 8 * TC_SUB) ? TC_SUB : 1;
 }
+// Forward problems with few output tiles and a long reduction (Dense on a flattened feature map: 750 rows, K up to
+// 25 000) are split along k so that the reduction runs on many SMs; the partial sums meet in an fp32 scratch tile.
+__host__ __device__ inline int tc_fwd_split(const Prob& p, int nb, int BN) {
+    const int mt = (nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM, tn = (p.F + BN - 1) / BN, nk = (tc_k_fwd(p) + TC_BK - 1) / TC_BK;
+    if (mt * tn > 48 || nk < 16) return 1;
+    return nk / 8 < 32 ? nk / 8 : 32;
+}
 __host__ __device__ inline int tc_tiles_fwd(const Prob& p, int nb, int BN) {
     const int mt = (nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM, sub = tc_fwd_sub(p, nb);
-    return ((mt + sub - 1) / sub) * ((p.F + BN - 1) / BN);
+    return ((mt + sub - 1) / sub) * ((p.F + BN - 1) / BN) * tc_fwd_split(p, nb, BN);
 }
 __host__ __device__ inline int tc_tiles_dgrad(const Prob& p, int nb, int BN) {
     return ((nb * p.H * p.W + TC_BM - 1) / TC_BM) * ((p.C + BN - 1) / BN);
@@ -238,9 +246,14 @@ struct __align__(16) TcTile {
     FastDiv fd_kw;
     int klast;         // K = 16 steps of the last k-block (1..4): the tail of the reduction is neither loaded nor multiplied
     int nsub;          // 128-row sub-tiles m0, m0 + 128, .. covered by this descriptor (forward only, else 1)
-    unsigned char pad[256 - sizeof(Prob) - 10 * sizeof(int) - 4 * sizeof(FastDiv)];
+    // split-K (forward, few output tiles and a long reduction): this tile covers k-blocks kb0 .. kb0 + nk - 1 of nsplit
+    // splits; partial sums meet in the fp32 scratch sk_acc [Mrows][Fs], sk_cnt[4 * sk_tile + warp] counts arrivals
+    int kb0, nsplit, sk_tile, sk_pad;
+    float* sk_acc;
+    int* sk_cnt;
+    unsigned char pad[TC_TILE_BYTES - sizeof(Prob) - 14 * sizeof(int) - 4 * sizeof(FastDiv) - 2 * sizeof(void*)];
 };
-static_assert(sizeof(TcTile) == 256, "TcTile is one 256-byte table entry / ring slot");
+static_assert(sizeof(TcTile) == TC_TILE_BYTES, "TcTile is one table entry / ring slot");
 
 // index in the table of the j-th tile of CTA c (G CTAs): rounds alternate direction so that costs even out
 __host__ __device__ inline int tc_tile_index(int c, int j, int G) { return j * G + ((j & 1) ? G - 1 - c : c); }
@@ -250,13 +263,24 @@ inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool
     const int HoWo = p.Ho * p.Wo;
     const int KK = p.kh * p.kw;
     const int Kf = SCALAR_A ? KK : KK * p.Cs;
-    t.r0 = 0; t.r1 = 0; t.nsub = 1;
+    t.r0 = 0; t.r1 = 0; t.nsub = 1; t.kb0 = 0; t.nsplit = 1; t.sk_tile = 0; t.sk_pad = 0; t.sk_acc = nullptr; t.sk_cnt = nullptr;
+    int Kend = 0;                                           // end of this tile's part of the reduction (elements)
     if (MODE == TC_FWD) {
         t.Mrows = nb * HoWo; t.Ncols = p.F;
         const int tn = (t.Ncols + BN - 1) / BN, sub = tc_fwd_sub(p, nb), mt = (t.Mrows + TC_BM - 1) / TC_BM;
+        const int per_split = ((mt + sub - 1) / sub) * tn, split = tile / per_split;
+        tile -= split * per_split;
         t.m0 = (tile / tn) * sub * TC_BM; t.n0 = (tile % tn) * BN;
         t.nsub = min(sub, mt - (tile / tn) * sub);
         t.nk = (Kf + TC_BK - 1) / TC_BK;
+        t.nsplit = SCALAR_A ? 1 : tc_fwd_split(p, nb, BN);
+        if (t.nsplit > 1) {
+            const int base = t.nk / t.nsplit, rem = t.nk % t.nsplit;
+            t.kb0 = split * base + min(split, rem);
+            t.nk = base + (split < rem ? 1 : 0);
+            t.sk_tile = tile;
+        }
+        Kend = min(Kf, (t.kb0 + t.nk) * TC_BK);
     } else if (MODE == TC_DGRAD) {
         t.Mrows = nb * p.H * p.W; t.Ncols = p.C;
         const int tn = (t.Ncols + BN - 1) / BN;
@@ -272,7 +296,7 @@ inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool
         t.nk = (t.r1 - t.r0 + TC_BK - 1) / TC_BK;
     }
     {
-        const int Ktot = MODE == TC_FWD ? Kf : (MODE == TC_DGRAD ? KK * p.Fs : t.r1 - t.r0);
+        const int Ktot = MODE == TC_FWD ? Kend - t.kb0 * TC_BK : (MODE == TC_DGRAD ? KK * p.Fs : t.r1 - t.r0);
         t.klast = (Ktot - (t.nk - 1) * TC_BK + 15) / 16;
     }
     t.n_umma = min(BN, ((t.Ncols - t.n0 + 15) / 16) * 16);
@@ -313,8 +337,8 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
     const uint32_t B_BYTES = (uint32_t)tc_b_bytes(BN);
     const int STAGES = tc_stages(BN);
     const uint32_t sA = sbase, sB = sbase + STAGES * TC_A_BYTES;
-    const uint32_t sRing = sB + STAGES * B_BYTES;         // TC_RING tile descriptors of 256 bytes
-    const uint32_t sFull = sRing + TC_RING * 256;         // barriers: full[S], empty[S], tmem_full[2], tmem_empty[2]
+    const uint32_t sRing = sB + STAGES * B_BYTES;         // TC_RING tile descriptors
+    const uint32_t sFull = sRing + TC_RING * TC_TILE_BYTES;         // barriers: full[S], empty[S], tmem_full[2], tmem_empty[2]
     const uint32_t sEmpty = sFull + TC_MAX_STAGES * 8;
     const uint32_t sTFull = sEmpty + TC_MAX_STAGES * 8;
     const uint32_t sTEmpty = sTFull + 2 * 8;
@@ -332,11 +356,11 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
     // of the first half-warp; the load of the next one is in flight while the current tile is being gathered
     uint4 dreg = make_uint4(0, 0, 0, 0);
     auto desc_load = [&](int j) {
-        if (j < my_tiles && tid < 16)
+        if (j < my_tiles && tid < TC_TILE_BYTES / 16)
             dreg = __ldg(reinterpret_cast<const uint4*>(table + tc_tile_index(cta, j, G)) + tid);
     };
     auto desc_store = [&](int j) {
-        if (j < my_tiles && tid < 16) reinterpret_cast<uint4*>(ring + (j % TC_RING))[tid] = dreg;
+        if (j < my_tiles && tid < TC_TILE_BYTES / 16) reinterpret_cast<uint4*>(ring + (j % TC_RING))[tid] = dreg;
     };
 
     if (tid == 0) {
@@ -379,7 +403,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
         bool t_lut = false, t_s1 = true;
         KGeo geo{};
         FastDiv t_fdrows{}, t_fdw{};
-        int lj = 0, lnk = 0, lsub = 1, t_Mrows = 0;
+        int lj = 0, lnk = 0, lsub = 1, t_Mrows = 0, lkb0 = 0;
         auto geo_of = [&](const TcTile& T) {
             const Prob& p = T.p;
             KGeo g;
@@ -392,8 +416,8 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
         auto fill_lut = [&](int j) {       // table of tile j -> buffer j & 1 (FWD and DGRAD only)
             if (MODE == TC_WGRAD || SCALAR_A || j >= my_tiles) return;
             const TcTile& T = ring[j % TC_RING];
-            const int chunks = T.nk * 8;
-            if (chunks > TC_LUT) return;
+            const int chunks = (T.kb0 + T.nk) * 8;
+            if (chunks > TC_LUT || T.p.kh * T.p.kw == 1) return;      // Dense entries are cheaper to compute than to look up
             const KGeo g = geo_of(T);
             int2* L = lut + (j & 1) * TC_LUT;
             for (int c = tid; c < chunks; c += TC_LOADERS) L[c] = tc_k_entry<MODE>(g, c);
@@ -406,7 +430,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             fill_lut(lj + 1);
             const Prob& p = T.p;
             { const __half* in = resolve_in(p, I, l_in_bs); l_in = reinterpret_cast<const char*>(in); }
-            lnk = T.nk; lsub = T.nsub; t_Mrows = T.Mrows;
+            lnk = T.nk; lsub = T.nsub; t_Mrows = T.Mrows; lkb0 = T.kb0;
             t_w = reinterpret_cast<const char*>(p.w); t_gout = reinterpret_cast<const char*>(p.gout);
             t_ldw = p.ldw; t_Cs = p.Cs; t_Fs = p.Fs; t_kw = p.kw; t_W = p.W;
             t_Wo = p.Wo; t_Ho = p.Ho; t_sh = p.sh; t_sw = p.sw; t_n0 = T.n0; t_out_bs = p.out_bs; t_HoWo = p.Ho * p.Wo;
@@ -414,7 +438,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             t_Cldw = p.C * p.ldw; t_C8 = p.C - T.n0;
             const int KK = p.kh * p.kw;
             t_Kf = SCALAR_A ? KK : KK * p.Cs;
-            t_lut = T.nk * 8 <= TC_LUT;
+            t_lut = (T.kb0 + T.nk) * 8 <= TC_LUT && KK != 1;
             t_s1 = p.sh == 1 && p.sw == 1;
             geo = geo_of(T);
             t_fdrows = T.fd_rows; t_fdw = T.fd_w;
@@ -660,7 +684,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
             loader_enter_tile();
             for (int s = 0; s < lsub; ++s) {
                 if (MODE == TC_FWD) fwd_rows(t_m0 + s * TC_BM);
-                for (int kb = 0; kb < lnk; ++kb) {
+                for (int kb = lkb0; kb < lkb0 + lnk; ++kb) {
                     mbar_wait(sEmpty + sb * 8, ph);
                     load_stage(sb, kb);
                     if (SCALAR_A) fence_proxy_async();       // the element-wise gather used ordinary shared-memory stores
@@ -721,6 +745,50 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
                 if (mrow < T.Mrows) {
                     const int b = fdiv(mrow, T.fd_rows), rem = mrow - b * HoWo;
                     orow = p.out + (long long)b * p.out_bs + (long long)rem * Fs;
+                }
+                if (T.nsplit > 1) {
+                    // split-K: add this part of the reduction into the fp32 scratch row; the warp that arrives last for
+                    // its 32 rows reads the sums back, applies bias and activation, stores fp16 and leaves zeros behind
+                    float* arow = mrow < T.Mrows ? T.sk_acc + (long long)mrow * Fs : nullptr;
+                    for (int cb = 0; cb < T.n_umma; cb += 32) {
+                        uint32_t r[32];
+                        tmem_ld32(trow + cb, r);
+                        if (!arow) continue;
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const int n = n0 + cb + q * 4;
+                            if (n < Ncols && cb + q * 4 < T.n_umma)
+                                atomicAdd(reinterpret_cast<float4*>(arow + n), make_float4(__uint_as_float(r[q * 4]), __uint_as_float(r[q * 4 + 1]),
+                                                                                           __uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3])));
+                        }
+                    }
+                    __threadfence();
+                    __syncwarp();
+                    int* cnt = T.sk_cnt + T.sk_tile * 4 + ewarp;
+                    int old = 0;
+                    if (lane == 0) old = atomicAdd(cnt, 1);
+                    old = __shfl_sync(0xffffffffu, old, 0);
+                    if (old != T.nsplit - 1) return;
+                    __threadfence();
+                    if (orow) {
+                        for (int n = n0; n < Ncols && n < n0 + T.n_umma; n += 8) {
+                            const float4 a = __ldcg(reinterpret_cast<const float4*>(arow + n)), b = __ldcg(reinterpret_cast<const float4*>(arow + n + 4));
+                            const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+                            const Half8 bv = ld8(bias + n);
+                            Half8 o;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                float z = 0.f;
+                                if (n + j < Ncols) z = act_forward(rh(rh(v[j]) + __half2float(bv.v[j])), act);
+                                o.v[j] = __float2half_rn(z);
+                            }
+                            st8(orow + n, o);
+                            __stcg(reinterpret_cast<float4*>(arow + n), make_float4(0.f, 0.f, 0.f, 0.f));
+                            __stcg(reinterpret_cast<float4*>(arow + n + 4), make_float4(0.f, 0.f, 0.f, 0.f));
+                        }
+                    }
+                    if (lane == 0) *cnt = 0;
+                    return;
                 }
                 // 32 accumulator columns per TMEM read.  Linear and ReLU layers round, add the bias and clamp as packed
                 // halves (one rounding per TensorFlow op, as the float path does); sigmoid goes through fp32.
