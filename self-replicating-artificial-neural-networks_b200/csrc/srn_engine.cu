@@ -209,11 +209,11 @@ extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
     CK(cudaSetDevice(cfg->device));
     {
         const int max_smem = tc_smem_bytes(256);
-        CK(cudaFuncSetAttribute(k_gemm_tc<TC_FWD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CK(cudaFuncSetAttribute(k_gemm_tc<TC_FWD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CK(cudaFuncSetAttribute(k_gemm_tc<TC_DGRAD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CK(cudaFuncSetAttribute(k_gemm_tc<TC_WGRAD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CK(cudaFuncSetAttribute(k_gemm_tc<TC_WGRAD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+#define TC_ATTR(MODE, SCALAR, BN_) CK(cudaFuncSetAttribute(k_gemm_tc<MODE, SCALAR, BN_>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(BN_)))
+#define TC_ATTR4(MODE, SCALAR) TC_ATTR(MODE, SCALAR, 32); TC_ATTR(MODE, SCALAR, 64); TC_ATTR(MODE, SCALAR, 128); TC_ATTR(MODE, SCALAR, 256)
+        TC_ATTR4(TC_FWD, false); TC_ATTR4(TC_FWD, true); TC_ATTR4(TC_DGRAD, false); TC_ATTR4(TC_WGRAD, false); TC_ATTR4(TC_WGRAD, true);
+#undef TC_ATTR4
+#undef TC_ATTR
     }
     srn_engine* h = new srn_engine();
     h->cfg = *cfg;
@@ -835,9 +835,18 @@ static int tc_grid(srn_engine* h, int total, int BN) {
     const int per_sm = std::max(1, std::min(4, (227 * 1024) / (tc_smem_bytes(BN) + 1024)));
     return std::min(total, h->num_sms * per_sm);
 }
+#define LAUNCH_TC1(cat, MODE, SCALAR, pass, BN_)                                                   \
+    LAUNCH_SMEM(cat, (k_gemm_tc<MODE, SCALAR, BN_>), tc_grid(h, c->total[pass], BN_), TC_THREADS, tc_smem_bytes(BN_), \
+                c->tiles[pass], c->total[pass], nb, I)
 #define LAUNCH_TC(cat, MODE, SCALAR, pass, BN_)                                                    \
-    LAUNCH_SMEM(cat, (k_gemm_tc<MODE, SCALAR>), tc_grid(h, c->total[pass], BN_), TC_THREADS, tc_smem_bytes(BN_), \
-                c->tiles[pass], c->total[pass], nb, BN_, I)
+    do {                                                                                           \
+        switch (BN_) {                                                                             \
+            case 32: LAUNCH_TC1(cat, MODE, SCALAR, pass, 32); break;                               \
+            case 64: LAUNCH_TC1(cat, MODE, SCALAR, pass, 64); break;                               \
+            case 128: LAUNCH_TC1(cat, MODE, SCALAR, pass, 128); break;                             \
+            default: LAUNCH_TC1(cat, MODE, SCALAR, pass, 256); break;                              \
+        }                                                                                          \
+    } while (0)
 
 template <int CFG>
 static void launch_fwd_cfg(srn_engine* h, Group& g, Cached* c, int nb, const Inputs& I) {

@@ -48,12 +48,12 @@ constexpr int TC_LUT = 512;            // 16-byte k chunks per lookup table: red
 // Pipeline depth per N tile: BN <= 64 keeps two CTAs per SM (4 stages each), wider tiles take the SM alone with as
 // many stages as fit.  Loaders never wait for their own copies: completion is signalled to the stage's "full"
 // barrier by the copy engine itself (cp.async.mbarrier.arrive.noinc), so up to `stages` k-blocks are in flight.
-__host__ __device__ inline int tc_stages(int BN) { return BN <= 64 ? 4 : (BN <= 128 ? 3 : 4); }
+__host__ __device__ constexpr int tc_stages(int BN) { return BN <= 64 ? 4 : (BN <= 128 ? 3 : 4); }
 // B tiles are stored with 128-byte rows (swizzle-128B atoms), so a 32-wide MN-major tile takes the room of a 64-wide one
-__host__ __device__ inline int tc_b_bytes(int BN) { return (BN < 64 ? 64 : BN) * TC_BK * 2; }
-__host__ __device__ inline int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + tc_b_bytes(BN)) + 256 + TC_RING * TC_TILE_BYTES + 2 * TC_LUT * 8; }
-__host__ __device__ inline int tc_acc_cols(int BN) { return BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256)); }
-__host__ __device__ inline int tc_tmem_cols(int BN) { return 2 * tc_acc_cols(BN); }     // two accumulators
+__host__ __device__ constexpr int tc_b_bytes(int BN) { return (BN < 64 ? 64 : BN) * TC_BK * 2; }
+__host__ __device__ constexpr int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + tc_b_bytes(BN)) + 256 + TC_RING * TC_TILE_BYTES + 2 * TC_LUT * 8; }
+__host__ __device__ constexpr int tc_acc_cols(int BN) { return BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256)); }
+__host__ __device__ constexpr int tc_tmem_cols(int BN) { return 2 * tc_acc_cols(BN); }     // two accumulators
 __host__ __device__ inline int round_up8(int v) { return (v + 7) & ~7; }
 
 // reduction length of each pass as the kernel sees it: over padded channels
@@ -324,9 +324,9 @@ __device__ __forceinline__ int2 tc_k_entry(const KGeo& g, int chunk) {
     return make_int2(2 * ((ki * g.ww + kj) * g.cs + cp), (int)(0x80000000u | (uint32_t)(ij * g.C + cp) | ((uint32_t)nvalid << 20)));
 }
 
-template <int MODE, bool SCALAR_A>
-static __global__ void __launch_bounds__(TC_THREADS, 2)
-k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I) {
+template <int MODE, bool SCALAR_A, int BN>
+static __global__ void __launch_bounds__(TC_THREADS, (BN <= 128 ? 2 : 1))
+k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int l8 = lane & 7, lq = lane >> 3;              // row inside a core matrix, chunk inside a quad
@@ -334,8 +334,8 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
     const uint32_t sbase = sraw;
     if (sraw & 1023u) __trap();                           // swizzle-128B atoms need 1024-byte alignment (the dynamic window starts on one)
     unsigned char* sgen = smem_raw + (sbase - sraw);      // generic pointer to the same place as sbase
-    const uint32_t B_BYTES = (uint32_t)tc_b_bytes(BN);
-    const int STAGES = tc_stages(BN);
+    constexpr uint32_t B_BYTES = (uint32_t)tc_b_bytes(BN);
+    constexpr int STAGES = tc_stages(BN);
     const uint32_t sA = sbase, sB = sbase + STAGES * TC_A_BYTES;
     const uint32_t sRing = sB + STAGES * B_BYTES;         // TC_RING tile descriptors
     const uint32_t sFull = sRing + TC_RING * TC_TILE_BYTES;         // barriers: full[S], empty[S], tmem_full[2], tmem_empty[2]
@@ -347,7 +347,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, int BN, Inputs I
     TcTile* ring = reinterpret_cast<TcTile*>(sgen + (sRing - sbase));
     volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(sgen + (sSlot - sbase));
     int2* lut = reinterpret_cast<int2*>(sgen + (sLut - sbase));
-    const int acc_cols = tc_acc_cols(BN), tmem_cols = tc_tmem_cols(BN);
+    constexpr int acc_cols = tc_acc_cols(BN), tmem_cols = tc_tmem_cols(BN);
 
     const int G = gridDim.x, cta = blockIdx.x;
     int my_tiles = ntiles / G;                                      // full rounds, plus maybe one of the last round
