@@ -1,23 +1,24 @@
 // Population-grouped implicit GEMM on the 5th-generation tensor cores (tcgen05 + TMEM), sm_100a.
 //
-// One CTA (128 threads) owns a 128 x BN output tile of one (individual, layer) problem.  Operands are
-// gathered from the NHWC fp16 activations / padded weight rows with 16-byte cp.async into shared memory in
-// the *canonical no-swizzle* UMMA layout: 8x8-element core matrices of 128 contiguous bytes, core (mn_group,
-// k_group) at ((mn_group * 8 + k_group) * 128) bytes.  Both K-major operands (8 rows x 16 B of k) and MN-major
-// operands (8 k-rows x 16 B of m/n) use that arrangement, so every descriptor has LBO = 128 B (next k group)
-// and SBO = 1024 B (next m/n group), and only the major bits of the instruction descriptor differ:
+// One CTA (416 threads) owns 128 x BN output tiles of (individual, layer) problems.  Operands are gathered from the
+// NHWC fp16 activations / padded weight rows with 16-byte cp.async into shared memory in the swizzle-128B canonical
+// UMMA layouts (rows of 128 bytes in 1024-byte atoms of 8 rows, 16-byte chunk index XOR row index):
 //   forward  Out = A(K-major, im2col rows) x W(MN-major, [k][n] rows)
 //   dgrad    dIn = dOut'(K-major)         x W(K-major, rows (ij, c), contiguous f)
 //   wgrad    dW  = A(MN-major, [row][kk]) x dOut(MN-major, [row][f])      (reduction over rows)
-// The kernel is persistent and warp-specialised.  A CTA walks its share of a host-built table of 256-byte tile
-// descriptors (sorted by cost, dealt out in snake order, prefetched four tiles ahead) and treats the k-blocks
-// of its tiles as one stream:
-//   warps 0-7  loaders: gather k-block p into ring stage p % S with cp.async; each thread's copies arrive on the
-//              stage's "full" barrier by themselves when they land (cp.async.mbarrier.arrive.noinc);
-//   warp 8     one thread waits "full", issues four K=16 tcgen05.mma into one of two TMEM accumulators and
+// K-major tiles hold 64 k per row, MN-major tiles 64 m/n of one k per row (LBO = 8192 B between groups of 64 m/n,
+// SBO = 1024 B between groups of 8 rows / 8 k); only the major bits of the instruction descriptor and the per-step
+// advance of the matrix descriptors differ between the passes.
+// The kernel is persistent and warp-specialised.  A CTA walks its share of a host-built table of tile descriptors
+// (sorted by cost, dealt out in snake order, prefetched four tiles ahead) and treats the k-blocks of its tiles as
+// one stream:
+//   warps 0-7  loaders: gather k-block p into ring stage p % S with cp.async, 4 rows x 8 chunks per warp-wide copy
+//              (a quarter warp reads 128 contiguous bytes of one row: one L1 wavefront per line); each thread's
+//              copies arrive on the stage's "full" barrier by themselves when they land (cp.async.mbarrier.arrive.noinc);
+//   warp 8     one thread waits "full", issues up to four K=16 tcgen05.mma into one of two TMEM accumulators and
 //              commits to the stage's "empty" barrier (and to "tmem_full" after a tile's last k-block);
 //   warps 9-12 epilogue: wait "tmem_full", read the accumulator with tcgen05.ld (warp w owns TMEM lanes
-//              32 (w % 4) ..), apply the same epilogues as the SIMT kernels, arrive on "tmem_empty".
+//              32 (w % 4) ..), apply bias / activation / gradient stores, arrive on "tmem_empty".
 // Loads, MMAs and epilogues of neighbouring tiles therefore overlap; nothing in the loop is a CTA-wide barrier.
 //
 // Every activation tensor has its channel stride padded to 8 with zero pad (srn_common.cuh), so a 16-byte
