@@ -28,16 +28,17 @@ __host__ __device__ inline int col_chunks(long long rows, int Cs) {
 
 // offset of row r (over all samples) of an input tensor; model inputs may be strided or broadcast per sample
 __device__ __forceinline__ long long in_row_off(long long r, int rps, int bs, int Cs) {
-    long long b = r / rps;
-    return b * bs + (r - b * rps) * (long long)Cs;
+    if (bs == rps * Cs) return r * Cs;                       // samples back to back: no division
+    const unsigned b = (unsigned)r / (unsigned)rps;          // rows of a batch fit 32 bits
+    return (long long)b * bs + (long long)((unsigned)r - b * (unsigned)rps) * Cs;
 }
 
 // offset of row r (over all samples) of an output / output-gradient tensor.  Normally samples are contiguous
 // (bs == rps * Fs); a tensor written in place into a concatenation buffer has the buffer's batch stride instead
 __device__ __forceinline__ long long out_row_off(long long r, int rps, int bs, int Fs) {
     if (bs == rps * Fs) return r * Fs;
-    const long long b = r / rps;
-    return b * bs + (r - b * rps) * (long long)Fs;
+    const unsigned b = (unsigned)r / (unsigned)rps;
+    return (long long)b * bs + (long long)((unsigned)r - b * (unsigned)rps) * Fs;
 }
 
 // sums over the row lanes of a CTA: sm holds one value per (thread, j); thread `ch` (< nq * cw) gets channel ch
@@ -192,6 +193,22 @@ __device__ __forceinline__ void bn_scale_shift(float mean16, float var16, float 
     shift = rh(beta - rh(mean16 * inv));
 }
 
+// Sum of the per-chunk partials of channel c in chunk order (double accumulators); eight chunks are loaded at a time
+// so that the L2 latencies overlap.
+__device__ __forceinline__ void bn_chunk_sums(const float* part, int chunks, int Cs, int c, double& s1, double& s2) {
+    s1 = 0.0; s2 = 0.0;
+    const float2* pp = reinterpret_cast<const float2*>(part) + c;
+    int k = 0;
+    for (; k + 8 <= chunks; k += 8) {
+        float2 v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __ldcg(pp + (long long)(k + j) * Cs);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s1 += v[j].x; s2 += v[j].y; }
+    }
+    for (; k < chunks; ++k) { const float2 v = __ldcg(pp + (long long)k * Cs); s1 += v.x; s2 += v.y; }
+}
+
 // one CTA per problem: combine partials, derive scale/shift, update the moving statistics (fp16 op by op)
 static __global__ void __launch_bounds__(128)
 k_bn_finalize_fwd(const Prob* __restrict__ probs, int nb, Inputs I) {
@@ -207,8 +224,8 @@ k_bn_finalize_fwd(const Prob* __restrict__ probs, int nb, Inputs I) {
             p.save[c] = 0.f; p.save[Cs + c] = 0.f; p.save[2 * Cs + c] = 0.f; p.save[3 * Cs + c] = 0.f;
             continue;
         }
-        double s1 = 0.0, s2 = 0.0;
-        for (int k = 0; k < chunks; ++k) { s1 += part[((long long)k * Cs + c) * 2]; s2 += part[((long long)k * Cs + c) * 2 + 1]; }
+        double s1, s2;
+        bn_chunk_sums(part, chunks, Cs, c, s1, s2);
         const double n = (double)rows;
         const double dm = s1 / n;
         const float mean32 = (float)((double)__half2float(in[c]) + dm);
@@ -269,7 +286,7 @@ k_bn_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, int n
 #pragma unroll
     for (int i = 0; i < EW_PER_THREAD; ++i, q += EW_THREADS) {
         if (q >= total) break;
-        const long long r = q / nq; const int c0 = (int)(q - r * nq) * cw;
+        const unsigned ru = (unsigned)q / (unsigned)nq; const long long r = ru; const int c0 = (int)((unsigned)q - ru * (unsigned)nq) * cw;
         const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = out_row_off(r, rps, p.out_bs, p.Fs) + c0;
         if (cw == 8) {
             const Half8 x = ld8(in + io);
@@ -294,8 +311,8 @@ k_bn_finalize_bwd(const Prob* __restrict__ probs, int nb) {
     float* part = p.save + 4 * Cs;
     for (int c = threadIdx.x; c < Cs; c += blockDim.x) {
         if (c >= C) { part[c * 2] = 0.f; part[c * 2 + 1] = 0.f; continue; }
-        double s1 = 0.0, s2 = 0.0;
-        for (int k = 0; k < chunks; ++k) { s1 += part[((long long)k * Cs + c) * 2]; s2 += part[((long long)k * Cs + c) * 2 + 1]; }
+        double s1, s2;
+        bn_chunk_sums(part, chunks, Cs, c, s1, s2);
         const float inv_raw = p.save[Cs + c];
         const float gamma = __half2float(p.w[c]);
         atomicAdd(&p.gb[c], (float)s1);                       // dbeta
@@ -324,7 +341,7 @@ k_bn_bwd_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
 #pragma unroll
     for (int i = 0; i < EW_PER_THREAD; ++i, q += EW_THREADS) {
         if (q >= total) break;
-        const long long r = q / nq; const int c0 = (int)(q - r * nq) * cw;
+        const unsigned ru = (unsigned)q / (unsigned)nq; const long long r = ru; const int c0 = (int)((unsigned)q - ru * (unsigned)nq) * cw;
         const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = out_row_off(r, rps, p.out_bs, p.Fs) + c0;
         if (cw == 8) {
             const Half8 x = ld8(in + io), dy = ld8(p.gout + oo);
@@ -364,8 +381,8 @@ k_maxpool_fwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
 #pragma unroll 1
     for (int it = 0; it < EW_PER_THREAD; ++it, q += EW_THREADS) {
         if (q >= total) break;
-        const long long pix = q / nq; const int c0 = (int)(q - pix * nq) * cw;
-        const long long b = pix / HoWo; const int rem = (int)(pix - b * HoWo);
+        const unsigned pix = (unsigned)q / (unsigned)nq; const int c0 = (int)((unsigned)q - pix * (unsigned)nq) * cw;
+        const unsigned bu = pix / (unsigned)HoWo; const long long b = bu; const int rem = (int)(pix - bu * (unsigned)HoWo);
         const int ho = rem / p.Wo, wo = rem - ho * p.Wo;
         const __half* base = in + b * in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * Cs + c0;
         float best[8];
@@ -416,8 +433,8 @@ k_maxpool_bwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
 #pragma unroll 1
         for (int it = 0; it < EW_PER_THREAD; ++it, q += EW_THREADS) {
             if (q >= wtotal) break;
-            const long long pix = q / nq; const int c0 = (int)(q - pix * nq) * cw;
-            const long long b = pix / HoWo; const int rem = (int)(pix - b * HoWo);
+            const unsigned pix = (unsigned)q / (unsigned)nq; const int c0 = (int)((unsigned)q - pix * (unsigned)nq) * cw;
+            const unsigned bu = pix / (unsigned)HoWo; const long long b = bu; const int rem = (int)(pix - bu * (unsigned)HoWo);
             const int ho = rem / p.Wo, wo = rem - ho * p.Wo;
             const long long oo = out_row_off(pix, HoWo, p.out_bs, p.Fs) + c0;
             float mx[8], go[8]; int arg[8];
@@ -463,8 +480,8 @@ k_maxpool_bwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
 #pragma unroll 1
     for (int it = 0; it < EW_PER_THREAD; ++it, q += EW_THREADS) {
         if (q >= total) break;
-        const long long pix = q / nq; const int c0 = (int)(q - pix * nq) * cw;
-        const long long b = pix / HW; const int rem = (int)(pix - b * HW);
+        const unsigned pix = (unsigned)q / (unsigned)nq; const int c0 = (int)((unsigned)q - pix * (unsigned)nq) * cw;
+        const unsigned bu = pix / (unsigned)HW; const long long b = bu; const int rem = (int)(pix - bu * (unsigned)HW);
         const int h = rem / p.W, w = rem - h * p.W;
         const __half* ib = in + b * in_bs + c0;
         float xv[8], g[8];
@@ -657,8 +674,8 @@ k_im2col(Im2colGeo g, int nb) {
     const long long total = (long long)nb * HoWo * nq;
     long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= total) return;
-    const long long pos = q / nq; const int k0 = (int)(q - pos * nq) * 8;
-    const long long b = pos / HoWo; const int rem = (int)(pos - b * HoWo);
+    const unsigned pos = (unsigned)q / (unsigned)nq; const int k0 = (int)((unsigned)q - pos * (unsigned)nq) * 8;
+    const unsigned bu = pos / (unsigned)HoWo; const long long b = bu; const int rem = (int)(pos - bu * (unsigned)HoWo);
     const int ho = rem / g.Wo, wo = rem - ho * g.Wo;
     const __half* src = g.in + b * g.in_bs + (long long)(ho * g.sh) * g.W + wo * g.sw;
     Half8 v;

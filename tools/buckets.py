@@ -44,6 +44,8 @@ if __name__ == '__main__':
     print(f'total serialised kernel time {total:.3f} ms/step over {len(rows)} (category, bucket) rows')
     print('\n'.join(lines[:70]))
     for g in sys.argv[3:]:
+        sel = [(float(t) / steps, PROFILE_CATEGORIES[i[0]]) for t, i in zip(ms, info) if int(i[1]) == int(g)]
+        print('bucket', g, 'launches in issue order (ms, summed over', steps, 'steps / steps):', [f'{c}:{t:.4f}' for t, c in sel])
         print('bucket', g, '{H, W, C, Cs, Ho, Wo, F, Fs, kh, kw, sh, sw, act, din_acc, individual, has din, coff, n_el, Cj, in_sel}')
         np.set_printoptions(linewidth=200, threshold=100000)
         print(eng.group_probs(int(g)))
