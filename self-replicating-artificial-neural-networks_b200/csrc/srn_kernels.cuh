@@ -143,7 +143,35 @@ k_bn_partial(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
         if (active) {
             float pivot[8];
             for (int j = 0; j < g.cw; ++j) pivot[j] = bwd ? p.save[cq * g.cw + j] : __half2float(in[cq * g.cw + j]);
-            for (long long r = r0 + rl; r < r1; r += g.RL) {
+            long long r = r0 + rl;
+            if (g.cw == 8) {
+                // four rows per trip: the loads of a trip are independent, so four (eight backward) are in flight per thread
+                for (; r + 3LL * g.RL < r1; r += 4LL * g.RL) {
+                    Half8 x[4], dy[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const long long rr = r + (long long)u * g.RL;
+                        x[u] = ld8(in + in_row_off(rr, rps, in_bs, Cs) + (long long)cq * 8);
+                        if (bwd) dy[u] = ld8(p.gout + out_row_off(rr, rps, p.out_bs, p.Fs) + (long long)cq * 8);
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            if (bwd) {
+                                const float d = __half2float(dy[u].v[j]);
+                                s1[j] += d;
+                                s2[j] += d * (__half2float(x[u].v[j]) - pivot[j]);
+                            } else {
+                                const float xv = __half2float(x[u].v[j]) - pivot[j];
+                                s1[j] += xv;
+                                s2[j] += xv * xv;
+                            }
+                        }
+                    }
+                }
+            }
+            for (; r < r1; r += g.RL) {
                 const long long io = in_row_off(r, rps, in_bs, Cs) + (long long)cq * g.cw;
                 if (g.cw == 8) {
                     const Half8 x = ld8(in + io);
