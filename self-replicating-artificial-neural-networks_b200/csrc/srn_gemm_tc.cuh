@@ -79,8 +79,26 @@ __host__ __device__ inline int tc_tiles_fwd(const Prob& p, int nb, int BN) {
     const int mt = (nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM, sub = tc_fwd_sub(p, nb);
     return ((mt + sub - 1) / sub) * ((p.F + BN - 1) / BN) * tc_fwd_split(p, nb, BN);
 }
+// The input gradient of a strided convolution is computed per residue class (ph, pw) of the input position: a pixel
+// h = ph + sh h' only receives the taps ki = ph + sh ki', so each class is a stride-1 problem over Hc x Wc pixels with
+// khp x kwp taps (a class with no tap still gets tiles: its pixels receive zeros).  Stride 1 is the single class (0, 0).
+struct DgClass { int ph, pw, Hc, Wc, khp, kwp; };
+__host__ __device__ inline DgClass tc_dgrad_class(const Prob& p, int cls) {
+    DgClass d;
+    d.ph = cls / p.sw; d.pw = cls - d.ph * p.sw;
+    d.Hc = p.H > d.ph ? (p.H - d.ph + p.sh - 1) / p.sh : 0;
+    d.Wc = p.W > d.pw ? (p.W - d.pw + p.sw - 1) / p.sw : 0;
+    d.khp = p.kh > d.ph ? (p.kh - d.ph + p.sh - 1) / p.sh : 0;
+    d.kwp = p.kw > d.pw ? (p.kw - d.pw + p.sw - 1) / p.sw : 0;
+    return d;
+}
+__host__ __device__ inline int tc_tiles_dgrad_class(const Prob& p, const DgClass& d, int nb, int BN) {
+    return ((nb * d.Hc * d.Wc + TC_BM - 1) / TC_BM) * ((p.C + BN - 1) / BN);
+}
 __host__ __device__ inline int tc_tiles_dgrad(const Prob& p, int nb, int BN) {
-    return ((nb * p.H * p.W + TC_BM - 1) / TC_BM) * ((p.C + BN - 1) / BN);
+    int n = 0;
+    for (int cls = 0; cls < p.sh * p.sw; ++cls) n += tc_tiles_dgrad_class(p, tc_dgrad_class(p, cls), nb, BN);
+    return n;
 }
 __host__ __device__ inline int tc_tiles_wgrad(const Prob& p, int nb, int BN) {
     return ((tc_k_fwd(p) + TC_BM - 1) / TC_BM) * ((p.F + BN - 1) / BN) * ((nb * p.Ho * p.Wo + TC_WGRAD_ROWS - 1) / TC_WGRAD_ROWS);
@@ -252,7 +270,8 @@ struct __align__(16) TcTile {
     int kb0, nsplit, sk_tile, sk_pad;
     float* sk_acc;
     int* sk_cnt;
-    unsigned char pad[TC_TILE_BYTES - sizeof(Prob) - 14 * sizeof(int) - 4 * sizeof(FastDiv) - 2 * sizeof(void*)];
+    int ph, pw, Hc, Wc, khp, kwp;     // dgrad: residue class of this tile (tc_dgrad_class)
+    unsigned char pad[TC_TILE_BYTES - sizeof(Prob) - 20 * sizeof(int) - 4 * sizeof(FastDiv) - 2 * sizeof(void*)];
 };
 static_assert(sizeof(TcTile) == TC_TILE_BYTES, "TcTile is one table entry / ring slot");
 
@@ -283,10 +302,18 @@ inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool
         }
         Kend = min(Kf, (t.kb0 + t.nk) * TC_BK);
     } else if (MODE == TC_DGRAD) {
-        t.Mrows = nb * p.H * p.W; t.Ncols = p.C;
+        DgClass d = tc_dgrad_class(p, 0);
+        for (int cls = 0; cls < p.sh * p.sw; ++cls) {
+            d = tc_dgrad_class(p, cls);
+            const int n = tc_tiles_dgrad_class(p, d, nb, BN);
+            if (tile < n) break;
+            tile -= n;
+        }
+        t.ph = d.ph; t.pw = d.pw; t.Hc = d.Hc; t.Wc = d.Wc; t.khp = d.khp; t.kwp = d.kwp;
+        t.Mrows = nb * d.Hc * d.Wc; t.Ncols = p.C;
         const int tn = (t.Ncols + BN - 1) / BN;
         t.m0 = (tile / tn) * TC_BM; t.n0 = (tile % tn) * BN;
-        t.nk = (KK * p.Fs + TC_BK - 1) / TC_BK;
+        t.nk = max(1, (d.khp * d.kwp * p.Fs + TC_BK - 1) / TC_BK);
     } else {
         t.Mrows = Kf; t.Ncols = p.F;                      // output rows are kk = (i, j, padded c)
         const int tm = (t.Mrows + TC_BM - 1) / TC_BM, tn = (t.Ncols + BN - 1) / BN;
@@ -297,14 +324,14 @@ inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool
         t.nk = (t.r1 - t.r0 + TC_BK - 1) / TC_BK;
     }
     {
-        const int Ktot = MODE == TC_FWD ? Kend - t.kb0 * TC_BK : (MODE == TC_DGRAD ? KK * p.Fs : t.r1 - t.r0);
-        t.klast = (Ktot - (t.nk - 1) * TC_BK + 15) / 16;
+        const int Ktot = MODE == TC_FWD ? Kend - t.kb0 * TC_BK : (MODE == TC_DGRAD ? t.khp * t.kwp * p.Fs : t.r1 - t.r0);
+        t.klast = max(1, (Ktot - (t.nk - 1) * TC_BK + 15) / 16);
     }
     t.n_umma = min(BN, ((t.Ncols - t.n0 + 15) / 16) * 16);
-    t.fd_rows = make_fastdiv(MODE == TC_DGRAD ? p.H * p.W : HoWo);
-    t.fd_w = make_fastdiv(MODE == TC_DGRAD ? p.W : p.Wo);
+    t.fd_rows = make_fastdiv(MODE == TC_DGRAD ? max(1, t.Hc * t.Wc) : HoWo);
+    t.fd_w = make_fastdiv(MODE == TC_DGRAD ? max(1, t.Wc) : p.Wo);
     t.fd_c = make_fastdiv(MODE == TC_DGRAD ? p.Fs : p.Cs);
-    t.fd_kw = make_fastdiv(p.kw);
+    t.fd_kw = make_fastdiv(MODE == TC_DGRAD ? max(1, t.kwp) : p.kw);
 }
 
 // What the k index of a 16-byte chunk means for a problem: (window position, channel) of the padded reduction space.
@@ -402,6 +429,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
         int t_ldw = 0, t_Cs = 1, t_Fs = 1, t_kw = 1, t_W = 1, t_Wo = 1, t_Ho = 1, t_sh = 1, t_sw = 1;
         int t_Kf = 0, t_n0 = 0, t_out_bs = 0, t_HoWo = 1, t_r0 = 0, t_r1 = 0, t_m0 = 0, t_Cldw = 0, t_C8 = 0;
         bool t_lut = false, t_s1 = true;
+        int t_tap0 = 0, t_tapi = 0, t_tapj = 0, t_dW = 1;        // DGRAD: weight-row offsets of the class's taps, class width
         KGeo geo{};
         FastDiv t_fdrows{}, t_fdw{};
         int lj = 0, lnk = 0, lsub = 1, t_Mrows = 0, lkb0 = 0;
@@ -410,7 +438,10 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
             KGeo g;
             const int KK = p.kh * p.kw;
             g.dense = KK == 1; g.kw = p.kw; g.C = p.C; g.fdc = T.fd_c; g.fdkw = T.fd_kw;
-            if (MODE == TC_DGRAD) { g.cs = p.Fs; g.ww = p.Wo; g.klim = KK * p.Fs; g.bias = ((p.kh - 1) * p.Wo + (p.kw - 1)) * p.Fs; }
+            if (MODE == TC_DGRAD) {      // taps of the tile's residue class
+                g.dense = T.khp * T.kwp == 1; g.kw = max(1, T.kwp);
+                g.cs = p.Fs; g.ww = p.Wo; g.klim = T.khp * T.kwp * p.Fs; g.bias = max(0, (T.khp - 1) * p.Wo + (T.kwp - 1)) * p.Fs;
+            }
             else { g.cs = p.Cs; g.ww = p.W; g.klim = SCALAR_A ? KK : KK * p.Cs; g.bias = 0; }
             return g;
         };
@@ -418,7 +449,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
             if (MODE == TC_WGRAD || SCALAR_A || j >= my_tiles) return;
             const TcTile& T = ring[j % TC_RING];
             const int chunks = (T.kb0 + T.nk) * 8;
-            if (chunks > TC_LUT || T.p.kh * T.p.kw == 1) return;      // Dense entries are cheaper to compute than to look up
+            if (chunks > TC_LUT || (MODE == TC_DGRAD ? T.khp * T.kwp : T.p.kh * T.p.kw) == 1) return;      // Dense entries are cheaper to compute than to look up
             const KGeo g = geo_of(T);
             int2* L = lut + (j & 1) * TC_LUT;
             for (int c = tid; c < chunks; c += TC_LOADERS) L[c] = tc_k_entry<MODE>(g, c);
@@ -439,11 +470,13 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
             t_Cldw = p.C * p.ldw; t_C8 = p.C - T.n0;
             const int KK = p.kh * p.kw;
             t_Kf = SCALAR_A ? KK : KK * p.Cs;
-            t_lut = (T.kb0 + T.nk) * 8 <= TC_LUT && KK != 1;
-            t_s1 = p.sh == 1 && p.sw == 1;
+            t_lut = (T.kb0 + T.nk) * 8 <= TC_LUT && (MODE == TC_DGRAD ? T.khp * T.kwp : KK) != 1;
+            t_s1 = true;
+            t_tap0 = (T.ph * p.kw + T.pw) * t_Cldw; t_tapi = p.sh * p.kw * t_Cldw; t_tapj = p.sw * t_Cldw;
             geo = geo_of(T);
             t_fdrows = T.fd_rows; t_fdw = T.fd_w;
-            const int HW = p.H * p.W;
+            const int HW = MODE == TC_DGRAD ? T.Hc * T.Wc : p.H * p.W;
+            t_dW = T.Wc;
             if (MODE == TC_FWD) {
                 t_cs = (T.nk == 1 && t_Kf <= 32) ? (t_Kf <= 16 ? 1 : 2) : 3;
                 t_items = 1 << (t_cs - 1);
@@ -459,11 +492,10 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                     if (m < T.Mrows) {
                         const int b = fdiv(m, t_fdrows);
                         const int rem = m - b * HW;
-                        a_h[i] = fdiv(rem, t_fdw); a_w[i] = rem - a_h[i] * t_W;
+                        a_h[i] = fdiv(rem, t_fdw); a_w[i] = rem - a_h[i] * t_dW;
                         // stride 1: source element = b * out_bs + ((h - ki) * Wo + (w - kj)) * Fs + kf; the table holds
                         // kf - (ki * Wo + kj) * Fs + bias >= 0
                         a_base[i] = 2 * (b * t_out_bs + (a_h[i] * t_Wo + a_w[i]) * t_Fs - geo.bias);
-                        if (!t_s1) a_base[i] = b * t_out_bs;
                     }
                 }
             } else {
@@ -598,21 +630,12 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     const int hh = a_h[i] - ki, ww = a_w[i] - kj;
-                    bool ok; uint32_t off;
-                    if (t_s1) {
-                        ok = e.y < 0 && (unsigned)hh < (unsigned)t_Ho && (unsigned)ww < (unsigned)t_Wo;
-                        off = (uint32_t)(a_base[i] + e.x);
-                    } else {
-                        // strides are 1 or 2 in practice: shifts for those, a real division otherwise
-                        const int ho = t_sh == 1 ? hh : (t_sh == 2 ? hh >> 1 : hh / t_sh);
-                        const int wo = t_sw == 1 ? ww : (t_sw == 2 ? ww >> 1 : ww / t_sw);
-                        ok = e.y < 0 && hh >= 0 && ww >= 0 && ho * t_sh == hh && wo * t_sw == ww && ho < t_Ho && wo < t_Wo;
-                        off = 2u * (uint32_t)(a_base[i] + (ho * t_Wo + wo) * t_Fs + kf);
-                    }
+                    const bool ok = e.y < 0 && (unsigned)hh < (unsigned)t_Ho && (unsigned)ww < (unsigned)t_Wo;
+                    const uint32_t off = (uint32_t)(a_base[i] + e.x);
                     cp_async16_ca(aS + k_dst + i * 4096, t_gout + (ok ? off : 0u), ok);
                 }
                 // B, K-major: rows n = input channel c, k = (ij, f) contiguous in f
-                const uint32_t wb = 2u * (uint32_t)((ki * t_kw + kj) * t_Cldw + kf + t_n0 * t_ldw);
+                const uint32_t wb = 2u * (uint32_t)(t_tap0 + ki * t_tapi + kj * t_tapj + kf + t_n0 * t_ldw);
 #pragma unroll 4
                 for (int i = 0; i < (BN >> 5); ++i) {
                     const int c = i * 32 + rlo;
@@ -825,11 +848,11 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                     }
                 }
             } else if (MODE == TC_DGRAD) {
-                const int HW = p.H * p.W;
                 __half* drow = nullptr;
                 if (mrow < T.Mrows) {
-                    const int b = fdiv(mrow, T.fd_rows), rem = mrow - b * HW;
-                    drow = p.din + (long long)b * p.in_bs + (long long)rem * Cs;
+                    const int b = fdiv(mrow, T.fd_rows), rem = mrow - b * (T.Hc * T.Wc);
+                    const int hc = fdiv(rem, T.fd_w), wc = rem - hc * T.Wc;
+                    drow = p.din + (long long)b * p.in_bs + (long long)((T.ph + p.sh * hc) * p.W + T.pw + p.sw * wc) * Cs;
                 }
                 const bool accum = p.din_acc != 0;
                 for (int cb = 0; cb < T.n_umma; cb += 32) {
