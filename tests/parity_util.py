@@ -137,3 +137,28 @@ con = Dense(units=50, activation='relu')(con)
 
 loss_balance = 0.35"""
 HANDCRAFTED.append(NET_F)
+
+# genotype first in the concatenation (the image branch lands at an unaligned offset and is compacted: 12 channels),
+# 5x5 and 7x7 first layers (reductions of 32 and 56 over the shared im2col matrix), stride-2 convolution whose input
+# needs a gradient (residue classes with 3, 2 and 2, 1 taps), a long Dense reduction (split along k), per-pixel Dense
+NET_G = """X_layer = Conv2D(filters=12, kernel_size=5, strides=1)(X_layer)
+X_layer = Conv2D(filters=12, kernel_size=(5, 4), strides=2, activation='relu')(X_layer)
+g_layer = Dense(units=6, activation='relu')(g_layer)
+con = concatenate([Reshape((1, -1))(g_layer), Reshape((1, -1))(X_layer)])
+con = Dense(units=90, activation='relu')(con)
+con = Dense(units=20)(con)
+
+loss_balance = 0.6"""
+HANDCRAFTED.append(NET_G)
+
+NET_H = """X_layer = Conv2D(filters=3, kernel_size=7, strides=1)(X_layer)
+X_layer = BatchNormalization()(X_layer)
+X_layer = Conv2D(filters=72, kernel_size=3, strides=2)(X_layer)
+X_layer = Conv2D(filters=16, kernel_size=3, strides=1, activation='relu')(X_layer)
+g_layer = Conv1D(filters=16, kernel_size=3, strides=1)(g_layer)
+g_layer = Dense(units=10)(g_layer)
+con = concatenate([Reshape((1, -1))(X_layer), Reshape((1, -1))(g_layer)])
+con = Dense(units=64, activation='sigmoid')(con)
+
+loss_balance = 0.15"""
+HANDCRAFTED.append(NET_H)
