@@ -732,14 +732,24 @@ extern "C" int srn_set_tensor_cores(int32_t on) {
 }
 
 // ------------------------------------------------------------------ launch plan per batch size
-static int pass_items(const Group& g, const Prob& p, int pass, int nb) {
+// most k-splits a forward bucket asks for: about two tiles per resident CTA over the whole bucket
+static int group_smax(const Group& g, int nb) {
+    if (g.tc != 1) return 1;
+    long long base = 0;
+    for (const Prob& p : g.h) base += tc_fwd_split_tiles(p, nb, TC_BN[g.cfgF]);
+    if (base == 0) return 1;
+    const long long want = (4LL * 148 + base - 1) / base;
+    return (int)std::max(1LL, std::min(32LL, want));
+}
+
+static int pass_items(const Group& g, const Prob& p, int pass, int nb, int smax) {
     const long long in_rows = (long long)nb * p.H * p.W, out_rows = (long long)nb * p.Ho * p.Wo;
     switch (g.kind) {
         case SRN_KIND_DENSE:
         case SRN_KIND_CONV:
             if (pass == P_COL) return col_chunks(out_rows, p.Fs);
             if (g.tc) {
-                if (pass == P_FWD) return tc_tiles_fwd(p, nb, TC_BN[g.cfgF]);
+                if (pass == P_FWD) return tc_tiles_fwd(p, nb, TC_BN[g.cfgF], smax);
                 if (pass == P_DGRAD) return p.din ? tc_tiles_dgrad(p, nb, TC_BN[g.cfgC]) : 0;
                 if (pass == P_WGRAD) return tc_tiles_wgrad(p, nb, TC_BN[g.cfgF]);
                 return 0;
@@ -770,11 +780,12 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
     if (it != g.cache.end()) { *out = &it->second; return SRN_OK; }
     Cached c;
     const int np = (int)g.h.size();
+    const int smax = group_smax(g, nb);
     std::vector<int> host((size_t)P_COUNT * (np + 1));
     for (int pass = 0; pass < P_COUNT; ++pass) {
         int* pre = host.data() + (size_t)pass * (np + 1);
         long long acc = 0;
-        for (int i = 0; i < np; ++i) { pre[i] = (int)acc; acc += pass_items(g, g.h[i], pass, nb); }
+        for (int i = 0; i < np; ++i) { pre[i] = (int)acc; acc += pass_items(g, g.h[i], pass, nb, smax); }
         if (acc > 0x7fffffffLL) return fail(SRN_ERR_LIMIT, "launch grid too large");
         pre[np] = (int)acc;
         c.total[pass] = (int)acc;
@@ -796,12 +807,12 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
                 for (int t = pre[i]; t < pre[i + 1]; ++t) {
                     memset(&tt[t], 0, sizeof(TcTile));
                     tt[t].p = g.h[i];
-                    tc_describe_tile(tt[t], t - pre[i], nb, BN, mode, g.tc == 2);
+                    tc_describe_tile(tt[t], t - pre[i], nb, BN, mode, g.tc == 2, smax);
                 }
             if (pass == P_FWD && g.tc == 1) {
                 // split-K scratch: zeroed once, every launch leaves it zeroed (srn_gemm_tc.cuh)
                 for (int i = 0; i < np; ++i) {
-                    if (tc_fwd_split(g.h[i], nb, BN) <= 1) continue;
+                    if (tc_fwd_split(g.h[i], nb, BN, smax) <= 1) continue;
                     const Prob& p = g.h[i];
                     const size_t rows = (size_t)nb * p.Ho * p.Wo;
                     const size_t acc_bytes = rows * p.Fs * sizeof(float);

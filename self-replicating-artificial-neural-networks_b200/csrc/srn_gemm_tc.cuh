@@ -70,14 +70,21 @@ __host__ __device__ inline int tc_fwd_sub(const Prob& p, int nb) {
 }
 // Forward problems with few output tiles and a long reduction (Dense on a flattened feature map: 750 rows, K up to
 // 25 000) are split along k so that the reduction runs on many SMs; the partial sums meet in an fp32 scratch tile.
-__host__ __device__ inline int tc_fwd_split(const Prob& p, int nb, int BN) {
+__host__ __device__ inline int tc_fwd_split_tiles(const Prob& p, int nb, int BN) {     // output tiles of a splittable problem, else 0
     const int mt = (nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM, tn = (p.F + BN - 1) / BN, nk = (tc_k_fwd(p) + TC_BK - 1) / TC_BK;
-    if (mt * tn > 48 || nk < 16) return 1;
-    return nk / 8 < 32 ? nk / 8 : 32;
+    return (mt * tn > 48 || nk < 16) ? 0 : mt * tn;
 }
-__host__ __device__ inline int tc_tiles_fwd(const Prob& p, int nb, int BN) {
+// smax = the most splits the launch bucket wants (enough tiles to fill the machine about twice; every split costs an
+// fp32 atomic pass over the output tile, so a bucket that already has many tiles splits little)
+__host__ __device__ inline int tc_fwd_split(const Prob& p, int nb, int BN, int smax) {
+    if (tc_fwd_split_tiles(p, nb, BN) == 0) return 1;
+    const int nk = (tc_k_fwd(p) + TC_BK - 1) / TC_BK;
+    const int s = nk / 8 < smax ? nk / 8 : smax;
+    return s < 1 ? 1 : s;
+}
+__host__ __device__ inline int tc_tiles_fwd(const Prob& p, int nb, int BN, int smax) {
     const int mt = (nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM, sub = tc_fwd_sub(p, nb);
-    return ((mt + sub - 1) / sub) * ((p.F + BN - 1) / BN) * tc_fwd_split(p, nb, BN);
+    return ((mt + sub - 1) / sub) * ((p.F + BN - 1) / BN) * tc_fwd_split(p, nb, BN, smax);
 }
 // The input gradient of a strided convolution is computed per residue class (ph, pw) of the input position: a pixel
 // h = ph + sh h' only receives the taps ki = ph + sh ki', so each class is a stride-1 problem over Hc x Wc pixels with
@@ -278,7 +285,7 @@ static_assert(sizeof(TcTile) == TC_TILE_BYTES, "TcTile is one table entry / ring
 // index in the table of the j-th tile of CTA c (G CTAs): rounds alternate direction so that costs even out
 __host__ __device__ inline int tc_tile_index(int c, int j, int G) { return j * G + ((j & 1) ? G - 1 - c : c); }
 
-inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool SCALAR_A) {
+inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool SCALAR_A, int smax) {
     const Prob& p = t.p;
     const int HoWo = p.Ho * p.Wo;
     const int KK = p.kh * p.kw;
@@ -293,7 +300,7 @@ inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool
         t.m0 = (tile / tn) * sub * TC_BM; t.n0 = (tile % tn) * BN;
         t.nsub = min(sub, mt - (tile / tn) * sub);
         t.nk = (Kf + TC_BK - 1) / TC_BK;
-        t.nsplit = SCALAR_A ? 1 : tc_fwd_split(p, nb, BN);
+        t.nsplit = SCALAR_A ? 1 : tc_fwd_split(p, nb, BN, smax);
         if (t.nsplit > 1) {
             const int base = t.nk / t.nsplit, rem = t.nk % t.nsplit;
             t.kb0 = split * base + min(split, rem);
