@@ -934,14 +934,27 @@ static int fwd_group(srn_engine* h, Group& g, int nb, const Inputs& I, bool trai
 
 static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
     const int mode = (I.x_istride == 0 && I.g_istride == 0) ? 1 : 2;
-    if (mode == 1) {
-        for (const Im2colGeo& e0 : h->geos) {
-            Im2colGeo e = e0;
-            const bool img = e0.in_bs == -1;
+    if (mode == 1 && !h->geos.empty()) {
+        // one small launch per window geometry: independent, so they go out on all streams at once
+        const bool fan = h->multi_stream && h->geos.size() > 1;
+        if (fan) {
+            cudaEventRecord(h->ev_fork, h->stream);
+            for (int i = 0; i < srn_engine::NSIDE; ++i) cudaStreamWaitEvent(h->side[i], h->ev_fork, 0);
+        }
+        bool used[srn_engine::NSIDE] = {};
+        for (size_t k = 0; k < h->geos.size(); ++k) {
+            Im2colGeo e = h->geos[k];
+            const bool img = e.in_bs == -1;
             e.in = img ? I.x : I.g; e.in_bs = img ? I.x_bs : I.g_bs;
             const long long total = (long long)nb * e.Ho * e.Wo * (e.Kp >> 3);
+            const int lane = fan ? (int)(k % (srn_engine::NSIDE + 1)) : 0;
+            h->cur = lane == 0 ? h->stream : h->side[lane - 1];
+            if (lane) used[lane - 1] = true;
             LAUNCH(SRN_CAT_GATHER, k_im2col, (unsigned)((total + 255) / 256), 256, e, nb);
         }
+        h->cur = h->stream;
+        for (int i = 0; i < srn_engine::NSIDE; ++i)
+            if (used[i]) { cudaEventRecord(h->ev_join[i], h->side[i]); cudaStreamWaitEvent(h->stream, h->ev_join[i], 0); }
     }
     // buckets of one depth level are independent: spread them over the side streams so that the tail of one
     // persistent launch overlaps the ramp-up of the next; levels are separated by events
