@@ -17,6 +17,8 @@
 #include <tuple>
 #include <vector>
 
+#include <cuda.h>          // CUtensorMap and the encode entry point (fetched through the runtime, libcuda is not linked)
+
 #include "../../include/serann_b200.h"
 #include "srn_gemm_simt.cuh"
 #include "srn_gemm_tc.cuh"
@@ -732,6 +734,51 @@ extern "C" int srn_set_tensor_cores(int32_t on) {
 }
 
 // ------------------------------------------------------------------ launch plan per batch size
+// ------------------------------------------------------------------ TMA tensor maps of Dense problems
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (getenv("SRN_NO_TMA") == nullptr &&
+            cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(f);
+    }
+    return fn;
+}
+// row-major fp16 matrix [rows][cols] with a row pitch (elements), box = 64 columns x box_rows rows, swizzle-128B
+static bool encode_matrix(CUtensorMap* m, const void* base, long long rows, long long cols, long long pitch, int box_rows) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn || !base || rows <= 0 || cols <= 0 || (pitch * 2) % 16 != 0 || ((uintptr_t)base & 15) != 0) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
+    const cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1u, 1u};
+    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+// The two maps (A operand, B operand) of one pass of a Dense problem whose operands are plain matrices; false = gather path
+static bool dense_tensor_maps(const Prob& p, int nb, int mode, int BN, CUtensorMap* m) {
+    static const int mask = getenv("SRN_TMA_MASK") ? atoi(getenv("SRN_TMA_MASK")) : 7;     // bit per pass (fwd, dgrad, wgrad): experiments
+    if (!((mask >> mode) & 1)) return false;
+    if (p.kh * p.kw != 1 || p.sh != 1 || p.sw != 1 || p.in_sel != 0) return false;
+    const int HW = p.H * p.W, HoWo = p.Ho * p.Wo;
+    if (HW != HoWo) return false;
+    const bool a_ok = HW == 1 || p.in_bs == HW * p.Cs, g_ok = HoWo == 1 || p.out_bs == HoWo * p.Fs;
+    const long long M = (long long)nb * HW;
+    const long long a_pitch = HW == 1 ? p.in_bs : p.Cs, g_pitch = HoWo == 1 ? p.out_bs : p.Fs;
+    if (mode == TC_FWD)
+        return a_ok && encode_matrix(&m[0], p.in, M, p.Cs, a_pitch, 128) && encode_matrix(&m[1], p.w, p.C, p.ldw, p.ldw, 64);
+    if (mode == TC_DGRAD)
+        return g_ok && encode_matrix(&m[0], p.gout, M, p.Fs, g_pitch, 128) && encode_matrix(&m[1], p.w, p.C, p.ldw, p.ldw, BN);
+    return a_ok && g_ok && encode_matrix(&m[0], p.in, M, p.Cs, a_pitch, 64) && encode_matrix(&m[1], p.gout, M, p.Fs, g_pitch, 64);
+}
+
 // most k-splits a forward bucket asks for: about two tiles per resident CTA over the whole bucket
 static int group_smax(const Group& g, int nb) {
     if (g.tc != 1) return 1;
@@ -826,6 +873,25 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
                         tt[t].sk_acc = reinterpret_cast<float*>(buf);
                         tt[t].sk_cnt = reinterpret_cast<int*>(buf + acc_bytes);
                     }
+                }
+            }
+            if (g.tc == 1 && g.kind == SRN_KIND_DENSE) {
+                std::vector<CUtensorMap> maps;
+                std::vector<int> first(np, -1);
+                CUtensorMap pair[2];
+                for (int i = 0; i < np; ++i)
+                    if (pre[i + 1] > pre[i] && dense_tensor_maps(g.h[i], nb, mode, BN, pair)) {
+                        first[i] = (int)maps.size();
+                        maps.push_back(pair[0]); maps.push_back(pair[1]);
+                    }
+                if (!maps.empty()) {
+                    CUtensorMap* dm = nullptr;
+                    CK(cudaMalloc(&dm, maps.size() * sizeof(CUtensorMap)));
+                    CK(cudaMemcpy(dm, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+                    h->scratch_prefix.push_back(reinterpret_cast<int*>(dm));
+                    for (int i = 0; i < np; ++i)
+                        if (first[i] >= 0)
+                            for (int t = pre[i]; t < pre[i + 1]; ++t) tt[t].tm = dm + first[i];
                 }
             }
             std::stable_sort(tt.begin(), tt.end(), [](const TcTile& a, const TcTile& b) { return a.nk * a.nsub > b.nk * b.nsub; });

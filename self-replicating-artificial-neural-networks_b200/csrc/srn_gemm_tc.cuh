@@ -139,6 +139,15 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar) : "memory");
 }
+// TMA: the issuing thread arrives on the stage's "full" barrier with the byte count of its copies, the copies
+// complete the transaction count when they land
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n"
+                 ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
 __device__ __forceinline__ void loaders_sync() { asm volatile("bar.sync 1, 256;\n" ::: "memory"); }   // the loader warps only
 // try_wait suspends the thread until the phase completes or the time hint (ns) runs out, so a long hint means few
 // polls: every poll is a shared-memory access that competes with the copies and the operand reads
@@ -278,7 +287,10 @@ struct __align__(16) TcTile {
     float* sk_acc;
     int* sk_cnt;
     int ph, pw, Hc, Wc, khp, kwp;     // dgrad: residue class of this tile (tc_dgrad_class)
-    unsigned char pad[TC_TILE_BYTES - sizeof(Prob) - 20 * sizeof(int) - 4 * sizeof(FastDiv) - 2 * sizeof(void*)];
+    // Dense problems whose operands are plain row-major matrices are loaded by TMA (2-D tiled mode, swizzle-128B):
+    // tm -> two 128-byte tensor maps (A operand, B operand) of this pass, nullptr = cp.async gather path
+    const void* tm;
+    unsigned char pad[TC_TILE_BYTES - sizeof(Prob) - 20 * sizeof(int) - 4 * sizeof(FastDiv) - 3 * sizeof(void*)];
 };
 static_assert(sizeof(TcTile) == TC_TILE_BYTES, "TcTile is one table entry / ring slot");
 
@@ -290,6 +302,7 @@ inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool
     const int HoWo = p.Ho * p.Wo;
     const int KK = p.kh * p.kw;
     const int Kf = SCALAR_A ? KK : KK * p.Cs;
+    t.tm = nullptr;
     t.r0 = 0; t.r1 = 0; t.nsub = 1; t.kb0 = 0; t.nsplit = 1; t.sk_tile = 0; t.sk_pad = 0; t.sk_acc = nullptr; t.sk_cnt = nullptr;
     int Kend = 0;                                           // end of this tile's part of the reduction (elements)
     if (MODE == TC_FWD) {
@@ -440,6 +453,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
         KGeo geo{};
         FastDiv t_fdrows{}, t_fdw{};
         int lj = 0, lnk = 0, lsub = 1, t_Mrows = 0, lkb0 = 0;
+        const char* t_tm = nullptr;
         auto geo_of = [&](const TcTile& T) {
             const Prob& p = T.p;
             KGeo g;
@@ -469,7 +483,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
             fill_lut(lj + 1);
             const Prob& p = T.p;
             { const __half* in = resolve_in(p, I, l_in_bs); l_in = reinterpret_cast<const char*>(in); }
-            lnk = T.nk; lsub = T.nsub; t_Mrows = T.Mrows; lkb0 = T.kb0;
+            lnk = T.nk; lsub = T.nsub; t_Mrows = T.Mrows; lkb0 = T.kb0; t_tm = reinterpret_cast<const char*>(T.tm);
             t_w = reinterpret_cast<const char*>(p.w); t_gout = reinterpret_cast<const char*>(p.gout);
             t_ldw = p.ldw; t_Cs = p.Cs; t_Fs = p.Fs; t_kw = p.kw; t_W = p.W;
             t_Wo = p.Wo; t_Ho = p.Ho; t_sh = p.sh; t_sw = p.sw; t_n0 = T.n0; t_out_bs = p.out_bs; t_HoWo = p.Ho * p.Wo;
@@ -717,9 +731,37 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                 if (MODE == TC_FWD) fwd_rows(t_m0 + s * TC_BM);
                 for (int kb = lkb0; kb < lkb0 + lnk; ++kb) {
                     mbar_wait(sEmpty + sb * 8, ph);
-                    load_stage(sb, kb);
-                    if (SCALAR_A) fence_proxy_async();       // the element-wise gather used ordinary shared-memory stores
-                    cp_async_arrive_noinc(sFull + sb * 8);   // fires when this thread's copies for the stage have landed
+                    if (t_tm) {
+                        // row-major operands: one thread issues the tile copies, everybody else just arrives
+                        const uint32_t bar = sFull + sb * 8;
+                        if (tid == 0) {
+                            const uint32_t aS = sA + sb * TC_A_BYTES, bS = sB + sb * B_BYTES;
+                            constexpr int G = BN >= 64 ? BN / 64 : 1;
+                            if (MODE == TC_FWD) {
+                                mbar_arrive_expect_tx(bar, TC_A_BYTES + G * 8192);
+                                tma_load_2d(aS, t_tm, kb * TC_BK, t_m0 + s * TC_BM, bar);
+#pragma unroll
+                                for (int g = 0; g < G; ++g) tma_load_2d(bS + g * 8192, t_tm + 128, t_n0 + g * 64, kb * TC_BK, bar);
+                            } else if (MODE == TC_DGRAD) {
+                                mbar_arrive_expect_tx(bar, TC_A_BYTES + BN * 128);
+                                tma_load_2d(aS, t_tm, kb * TC_BK, t_m0, bar);
+                                tma_load_2d(bS, t_tm + 128, kb * TC_BK, t_n0, bar);
+                            } else {
+                                mbar_arrive_expect_tx(bar, 2 * 8192 + G * 8192);
+                                const int r = t_r0 + kb * TC_BK;
+                                tma_load_2d(aS, t_tm, t_m0, r, bar);
+                                tma_load_2d(aS + 8192, t_tm, t_m0 + 64, r, bar);
+#pragma unroll
+                                for (int g = 0; g < G; ++g) tma_load_2d(bS + g * 8192, t_tm + 128, t_n0 + g * 64, r, bar);
+                            }
+                        } else {
+                            mbar_arrive(bar);
+                        }
+                    } else {
+                        load_stage(sb, kb);
+                        if (SCALAR_A) fence_proxy_async();       // the element-wise gather used ordinary shared-memory stores
+                        cp_async_arrive_noinc(sFull + sb * 8);   // fires when this thread's copies for the stage have landed
+                    }
                     if (++sb == STAGES) { sb = 0; ph ^= 1u; }
                 }
             }
