@@ -448,7 +448,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
         int w_koff[2] = {0, 0}; bool w_kok[2] = {false, false};    // WGRAD (vector): offsets of this thread's two kk chunks inside the window
         int t_ldw = 0, t_Cs = 1, t_Fs = 1, t_kw = 1, t_W = 1, t_Wo = 1, t_Ho = 1, t_sh = 1, t_sw = 1;
         int t_Kf = 0, t_n0 = 0, t_out_bs = 0, t_HoWo = 1, t_r0 = 0, t_r1 = 0, t_m0 = 0, t_Cldw = 0, t_C8 = 0;
-        bool t_lut = false, t_s1 = true;
+        bool t_lut = false, t_s1 = true, t_flat = false;
         int t_tap0 = 0, t_tapi = 0, t_tapj = 0, t_dW = 1;        // DGRAD: weight-row offsets of the class's taps, class width
         KGeo geo{};
         FastDiv t_fdrows{}, t_fdw{};
@@ -493,6 +493,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
             t_Kf = SCALAR_A ? KK : KK * p.Cs;
             t_lut = (T.kb0 + T.nk) * 8 <= TC_LUT && (MODE == TC_DGRAD ? T.khp * T.kwp : KK) != 1;
             t_s1 = true;
+            t_flat = MODE == TC_FWD && KK == 1 && p.sh == 1 && p.sw == 1 && l_in_bs == p.H * p.W * p.Cs;
             t_tap0 = (T.ph * p.kw + T.pw) * t_Cldw; t_tapi = p.sh * p.kw * t_Cldw; t_tapj = p.sw * t_Cldw;
             geo = geo_of(T);
             t_fdrows = T.fd_rows; t_fdw = T.fd_w;
@@ -542,9 +543,11 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
             const int rpw = 32 >> t_cs, subr = lane >> t_cs;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
+                if (i >= t_items) { a_ok[i] = false; continue; }
                 const int m = m0 + i * rpw * 8 + warp * rpw + subr;
-                a_ok[i] = i < t_items && m < t_Mrows;
+                a_ok[i] = m < t_Mrows;
                 const int mc = a_ok[i] ? m : 0;
+                if (t_flat) { a_off[i] = 2u * (uint32_t)mc * (uint32_t)t_Cs; continue; }      // rows back to back: no decomposition
                 const int b = fdiv(mc, t_fdrows), rem = mc - b * t_HoWo;
                 const int ho = fdiv(rem, t_fdw), wo = rem - ho * t_Wo;
                 a_off[i] = 2u * ((uint32_t)b * (uint32_t)l_in_bs + (uint32_t)(((ho * t_sh) * t_W + wo * t_sw) * t_Cs));
