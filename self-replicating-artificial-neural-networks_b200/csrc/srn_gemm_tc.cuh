@@ -52,9 +52,13 @@ constexpr int TC_LUT = 512;            // 16-byte k chunks per lookup table: red
 __host__ __device__ constexpr int tc_stages(int BN) { return BN <= 64 ? 4 : (BN <= 128 ? 3 : 4); }
 // B tiles are stored with 128-byte rows (swizzle-128B atoms), so a 32-wide MN-major tile takes the room of a 64-wide one
 __host__ __device__ constexpr int tc_b_bytes(int BN) { return (BN < 64 ? 64 : BN) * TC_BK * 2; }
-__host__ __device__ constexpr int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + tc_b_bytes(BN)) + 256 + TC_RING * TC_TILE_BYTES + 2 * TC_LUT * 8; }
+__host__ __device__ constexpr int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + tc_b_bytes(BN)) + 384 + TC_RING * TC_TILE_BYTES + 2 * TC_LUT * 8; }
 __host__ __device__ constexpr int tc_acc_cols(int BN) { return BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256)); }
-__host__ __device__ constexpr int tc_tmem_cols(int BN) { return 2 * tc_acc_cols(BN); }     // two accumulators
+// TMEM accumulators per CTA: 256 columns (two CTAs share the SM's 512) hold 8, 4 or 2 of them; a CTA that has the SM
+// alone (BN = 256) takes all 512 columns for two.  Short tiles (one or two k-blocks) are bound by the round trip
+// MMA -> epilogue -> MMA over an accumulator, so more accumulators mean more tiles in flight.
+__host__ __device__ constexpr int tc_num_acc(int BN) { return BN <= 128 ? 256 / tc_acc_cols(BN) : 2; }
+__host__ __device__ constexpr int tc_tmem_cols(int BN) { return tc_num_acc(BN) * tc_acc_cols(BN); }
 __host__ __device__ inline int round_up8(int v) { return (v + 7) & ~7; }
 
 // reduction length of each pass as the kernel sees it: over padded channels
@@ -389,13 +393,13 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
     const uint32_t sFull = sRing + TC_RING * TC_TILE_BYTES;         // barriers: full[S], empty[S], tmem_full[2], tmem_empty[2]
     const uint32_t sEmpty = sFull + TC_MAX_STAGES * 8;
     const uint32_t sTFull = sEmpty + TC_MAX_STAGES * 8;
-    const uint32_t sTEmpty = sTFull + 2 * 8;
-    const uint32_t sSlot = sTEmpty + 2 * 8;
-    const uint32_t sLut = sFull + 256;                    // two k-chunk tables of TC_LUT entries (this tile, next tile)
+    const uint32_t sTEmpty = sTFull + 8 * 8;
+    const uint32_t sSlot = sTEmpty + 8 * 8;
+    const uint32_t sLut = sFull + 384;                    // two k-chunk tables of TC_LUT entries (this tile, next tile)
     TcTile* ring = reinterpret_cast<TcTile*>(sgen + (sRing - sbase));
     volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(sgen + (sSlot - sbase));
     int2* lut = reinterpret_cast<int2*>(sgen + (sLut - sbase));
-    constexpr int acc_cols = tc_acc_cols(BN), tmem_cols = tc_tmem_cols(BN);
+    constexpr int acc_cols = tc_acc_cols(BN), tmem_cols = tc_tmem_cols(BN), NACC = tc_num_acc(BN);
 
     const int G = gridDim.x, cta = blockIdx.x;
     int my_tiles = ntiles / G;                                      // full rounds, plus maybe one of the last round
@@ -413,7 +417,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
 
     if (tid == 0) {
         for (int i = 0; i < STAGES; ++i) { mbar_init(sFull + i * 8, TC_LOADERS); mbar_init(sEmpty + i * 8, 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(sTFull + i * 8, 1); mbar_init(sTEmpty + i * 8, 128); }
+        for (int i = 0; i < NACC; ++i) { mbar_init(sTFull + i * 8, 1); mbar_init(sTEmpty + i * 8, 128); }
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
     }
     if (warp == TC_LW) tmem_alloc(sSlot, (uint32_t)tmem_cols);
@@ -782,8 +786,8 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
             for (int j = 0; j < my_tiles; ++j) {
                 int nk = 1, klast = 4, nsub = 1; uint32_t idesc = 0;
                 for (int s = 0; s < nsub; ++s, ++jj) {
-                    const int acc = jj & 1;
-                    if (jj >= 2) mbar_wait(sTEmpty + acc * 8, (uint32_t)(((jj >> 1) - 1) & 1));   // epilogue drained this accumulator
+                    const int acc = jj % NACC;
+                    if (jj >= NACC) mbar_wait(sTEmpty + acc * 8, (uint32_t)((jj / NACC - 1) & 1));   // epilogue drained this accumulator
                     const uint32_t tacc = tmem + (uint32_t)(acc * acc_cols);
                     for (int kb = 0; kb < nk; ++kb) {
                         mbar_wait(sFull + st * 8, fph);
@@ -970,10 +974,10 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
             const TcTile& T = ring[j % TC_RING];
             const int nsub = T.nsub;
             for (int s = 0; s < nsub; ++s, ++jj) {
-                const int acc = jj & 1;
+                const int acc = jj % NACC;
                 // long tiles: back off while waiting so that the spin does not take issue slots from the loaders
-                if (T.nk > 32) mbar_wait_relaxed(sTFull + acc * 8, (uint32_t)((jj >> 1) & 1));
-                else mbar_wait(sTFull + acc * 8, (uint32_t)((jj >> 1) & 1));
+                if (T.nk > 32) mbar_wait_relaxed(sTFull + acc * 8, (uint32_t)((jj / NACC) & 1));
+                else mbar_wait(sTFull + acc * 8, (uint32_t)((jj / NACC) & 1));
                 tc_fence_after();
                 epilogue(T, s, tmem + (uint32_t)(acc * acc_cols), ewarp);
                 tc_fence_before();
