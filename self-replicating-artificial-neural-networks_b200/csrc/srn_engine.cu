@@ -107,6 +107,10 @@ struct srn_engine {
     static constexpr int NSIDE = 7;
     cudaStream_t side[NSIDE] = {};        // independent launch buckets of one depth level overlap their tails on these
     cudaEvent_t ev_fork = nullptr, ev_join[NSIDE] = {};
+    // the optimiser pass runs on its own stream so that the next step's batch gather and im2col overlap it
+    cudaStream_t adam_stream = nullptr;
+    cudaEvent_t ev_adam_go = nullptr, ev_adam_done = nullptr;
+    bool adam_pending = false;
     bool multi_stream = true;
     int num_sms = 148;
     std::vector<Im2colGeo> geos;         // shared im2col buffers of the first layers (one per window geometry)
@@ -225,6 +229,9 @@ extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
         CK(cudaEventCreateWithFlags(&h->ev_join[i], cudaEventDisableTiming));
     }
     CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+    CK(cudaStreamCreateWithFlags(&h->adam_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&h->ev_adam_go, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->ev_adam_done, cudaEventDisableTiming));
     h->multi_stream = getenv("SRN_SINGLE_STREAM") == nullptr;
     h->cur = h->stream;
     h->xe = cfg->image_h * cfg->image_w;
@@ -245,6 +252,9 @@ extern "C" void srn_destroy(srn_engine* h) {
     free_population(h);
     for (int i = 0; i < srn_engine::NSIDE; ++i) { if (h->side[i]) cudaStreamDestroy(h->side[i]); if (h->ev_join[i]) cudaEventDestroy(h->ev_join[i]); }
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_adam_go) cudaEventDestroy(h->ev_adam_go);
+    if (h->ev_adam_done) cudaEventDestroy(h->ev_adam_done);
+    if (h->adam_stream) cudaStreamDestroy(h->adam_stream);
     for (int s = 0; s < 2; ++s) { cudaFree(h->x[s]); cudaFree(h->y[s]); cudaFree(h->gb[s]); }
     cudaFree(h->xin); cudaFree(h->gin); cudaFree(h->lab);
     delete h;
@@ -998,6 +1008,11 @@ static int fwd_group(srn_engine* h, Group& g, int nb, const Inputs& I, bool trai
     return SRN_OK;
 }
 
+// the main stream must not touch parameters or gradient accumulators before the last optimiser pass is done
+static void wait_adam(srn_engine* h) {
+    if (h->adam_pending) { cudaStreamWaitEvent(h->stream, h->ev_adam_done, 0); h->adam_pending = false; }
+}
+
 static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
     const int mode = (I.x_istride == 0 && I.g_istride == 0) ? 1 : 2;
     if (mode == 1 && !h->geos.empty()) {
@@ -1022,6 +1037,7 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
         for (int i = 0; i < srn_engine::NSIDE; ++i)
             if (used[i]) { cudaEventRecord(h->ev_join[i], h->side[i]); cudaStreamWaitEvent(h->stream, h->ev_join[i], 0); }
     }
+    wait_adam(h);
     // buckets of one depth level are independent: spread them over the side streams so that the tail of one
     // persistent launch overlaps the ramp-up of the next; levels are separated by events
     size_t gi = 0;
@@ -1153,7 +1169,17 @@ static int train_step(srn_engine* h, const int* d_idx, int start, int nb, int sl
     if (apply_adam) {
         h->adam_t += 1;
         const long long n8 = h->p_elems / 8;
+        if (h->multi_stream) {
+            cudaEventRecord(h->ev_adam_go, h->stream);
+            cudaStreamWaitEvent(h->adam_stream, h->ev_adam_go, 0);
+            h->cur = h->adam_stream;
+        }
         LAUNCH(SRN_CAT_ADAM, k_adam, (unsigned)((n8 + 255) / 256), 256, h->P, h->M, h->V, h->Gr, n8, adam_scalars(h->adam_t));
+        if (h->multi_stream) {
+            cudaEventRecord(h->ev_adam_done, h->adam_stream);
+            h->cur = h->stream;
+            h->adam_pending = true;
+        }
     }
     return SRN_OK;
 }
@@ -1225,6 +1251,7 @@ extern "C" int srn_fit(srn_engine* h, int32_t epochs, int32_t batch, int32_t n_v
             if (rc) { cudaFree(d_perm); return rc; }
             if (max_steps > 0 && ++steps_done >= max_steps) { stop = true; break; }
         }
+        wait_adam(h);
         CK(cudaEventRecord(ev1, h->stream));
         if (n_val && !stop) {
             rc = eval_rows(h, 0, n_fit, n_val, batch, epochs * S + e * Vc);
@@ -1395,6 +1422,7 @@ extern "C" int srn_debug_step(srn_engine* h, const int32_t* rows, int32_t nb, in
     rc = ensure_metrics(h, 1);
     cudaMemsetAsync(h->Gr, 0, (size_t)h->p_elems * sizeof(float), h->stream);
     if (!rc) rc = train_step(h, d_idx, 0, nb, 0, apply_adam != 0);
+    wait_adam(h);
     cudaError_t e = cudaStreamSynchronize(h->stream);
     cudaFree(d_idx);
     if (rc) return rc;
