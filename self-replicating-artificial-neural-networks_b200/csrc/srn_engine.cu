@@ -885,7 +885,7 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
                     }
                 }
             }
-            if (g.tc == 1 && g.kind == SRN_KIND_DENSE) {
+            if (g.tc == 1) {        // any problem with a 1 x 1 window over row-major operands (Dense, first layers over the shared im2col matrix)
                 std::vector<CUtensorMap> maps;
                 std::vector<int> first(np, -1);
                 CUtensorMap pair[2];
