@@ -27,6 +27,7 @@
 // use the SCALAR_A variant: the im2col operand is gathered element by element and stored to shared memory
 // with ordinary 16-byte stores; everything else is identical.
 #pragma once
+#include <type_traits>
 #include "srn_common.cuh"
 
 namespace srn {
@@ -452,7 +453,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
         int w_koff[2] = {0, 0}; bool w_kok[2] = {false, false};    // WGRAD (vector): offsets of this thread's two kk chunks inside the window
         int t_ldw = 0, t_Cs = 1, t_Fs = 1, t_kw = 1, t_W = 1, t_Wo = 1, t_Ho = 1, t_sh = 1, t_sw = 1;
         int t_Kf = 0, t_n0 = 0, t_out_bs = 0, t_HoWo = 1, t_r0 = 0, t_r1 = 0, t_m0 = 0, t_Cldw = 0, t_C8 = 0;
-        bool t_lut = false, t_s1 = true, t_flat = false;
+        bool t_lut = false, t_s1 = true, t_flat = false, t_fast = false;
         int t_tap0 = 0, t_tapi = 0, t_tapj = 0, t_dW = 1;        // DGRAD: weight-row offsets of the class's taps, class width
         KGeo geo{};
         FastDiv t_fdrows{}, t_fdw{};
@@ -542,6 +543,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                     }
                 }
             }
+            t_fast = MODE == TC_FWD ? (!SCALAR_A && t_lut && t_cs == 3) : (MODE == TC_DGRAD ? t_lut : (!SCALAR_A && t_cs == 3));
         };
         auto fwd_rows = [&](int m0) {        // FWD: this thread's rows of the sub-tile starting at row m0
             const int rpw = 32 >> t_cs, subr = lane >> t_cs;
@@ -557,8 +559,10 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                 a_off[i] = 2u * ((uint32_t)b * (uint32_t)l_in_bs + (uint32_t)(((ho * t_sh) * t_W + wo * t_sw) * t_Cs));
             }
         };
-        auto k_entry = [&](int chunk) -> int2 {
-            if (t_lut) return lut[(lj & 1) * TC_LUT + chunk];
+        // FAST = the tile's k table is in shared memory and the tile uses the standard 4 rows x 8 chunks mapping: the k
+        // loop of such tiles (all convolutions of the benchmark) is compiled without the fallback branches
+        auto k_entry = [&](int chunk, auto FAST) -> int2 {
+            if (decltype(FAST)::value || t_lut) return lut[(lj & 1) * TC_LUT + chunk];
             return tc_k_entry<MODE>(geo, chunk);
         };
         // MN-major B tile (k rows x n chunks): BN = 32 has four chunks per row, so a quarter warp takes rows r and
@@ -603,13 +607,14 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                 }
             }
         };
-        auto load_stage = [&](int stage, int kb) {
+        auto load_stage = [&](int stage, int kb, auto FAST) {
+            constexpr bool fast = decltype(FAST)::value;
             const uint32_t aS = sA + stage * TC_A_BYTES, bS = sB + stage * B_BYTES;
             if (MODE == TC_FWD) {
                 // A, K-major: four rows, one k chunk
                 if (!SCALAR_A) {
-                    const int2 e = k_entry(kb * 8 + t_ch);
-                    if (t_cs == 3) {
+                    const int2 e = k_entry(kb * 8 + (fast ? ch : t_ch), FAST);
+                    if (fast || t_cs == 3) {
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
                             const bool ok = a_ok[i] && e.y < 0;
@@ -647,13 +652,13 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                 load_b_mn(bS, min(64, (t_Kf - kb * TC_BK + 15) & ~15), [&](int kl, int& left) -> const char* {
                     int wrow; bool kok;
                     if (SCALAR_A) { wrow = kb * TC_BK + kl; kok = wrow < t_Kf; }
-                    else { const int2 eb = k_entry(kb * 8 + (kl >> 3)); wrow = (eb.y & 0xFFFFF) + (kl & 7); kok = (kl & 7) < ((eb.y >> 20) & 15); }
+                    else { const int2 eb = k_entry(kb * 8 + (kl >> 3), FAST); wrow = (eb.y & 0xFFFFF) + (kl & 7); kok = (kl & 7) < ((eb.y >> 20) & 15); }
                     left = kok ? 2 * (t_ldw - t_n0) : 0;
                     return t_w + (kok ? 2u * (uint32_t)(wrow * t_ldw + t_n0) : 0u);
                 });
             } else if (MODE == TC_DGRAD) {
                 // k = (ij, f) over the padded filters: one chunk per thread and k-block, four rows
-                const int2 e = k_entry(kb * 8 + ch);
+                const int2 e = k_entry(kb * 8 + ch, FAST);
                 const int ki = e.y & 255, kj = (e.y >> 8) & 255, kf = ((e.y >> 16) & 0x7FFF) * 8;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
@@ -704,7 +709,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                     left = rok ? 2 * (t_Fs - t_n0) : 0;
                     return t_gout + 2 * ((long long)b * t_out_bs + (long long)rem * t_Fs + t_n0);
                 };
-                if (t_cs == 3) {
+                if (fast || t_cs == 3) {
                     const char* go_row[2]; int go_left[2];
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
@@ -765,7 +770,8 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                             mbar_arrive(bar);
                         }
                     } else {
-                        load_stage(sb, kb);
+                        if (t_fast) load_stage(sb, kb, std::true_type{});
+                        else load_stage(sb, kb, std::false_type{});
                         if (SCALAR_A) fence_proxy_async();       // the element-wise gather used ordinary shared-memory stores
                         cp_async_arrive_noinc(sFull + sb * 8);   // fires when this thread's copies for the stage have landed
                     }
