@@ -241,3 +241,67 @@ def test_decoder_argmax_bit_exact():
     with pytest.raises(IndexError):
         ae.decode_to_sequence(np.full((1, 100), np.nan))
     ae.close()
+
+
+@pytest.mark.parametrize('seed', [101, 202, 303])
+def test_generated_population_fuzz(seed):
+    """Wider net over the generator's architecture space than the fixture's population: eight generated individuals per
+    seed, inference logits and the losses of the first training steps against the oracle (tensor-core product path)."""
+    from serann_b200 import generator
+    from serann_b200.engine import set_tensor_cores
+    set_tensor_cores(True)
+    pop = generator.sample_population(8, seed=seed, max_flops_per_sample=4.0e6)
+    irs = [ir for _, ir in pop]
+    data = U.small_dataset(seed=seed)
+    eng, inds = U.make_engine_and_oracle(irs, data)
+    try:
+        logits = eng.forward_logits(1, 0, 64, training=False)
+        lines = [f'== fuzz seed {seed} ==']
+        for i, ind in enumerate(inds):
+            with torch.no_grad():
+                xi, gi = O.prepare_inputs(data['x_test'], data['g_test'])
+                ref = O.forward(ind, xi, gi, training=False).numpy()
+            e = U.relerr(logits[i], ref)
+            lines.append(f'net {i} inference logits relerr {e:.3e}')
+            assert e < ACT_TOL, (lines[-1], pop[i][0])
+        n_val, batch = 40, 40
+        perms = np.stack([np.random.default_rng(seed).permutation(160 - n_val)])
+        res = eng.fit(1, batch, n_val, perms=perms)
+        ref = O.fit(inds, data['x_train'], data['y_train'], data['g_train'], list(perms), batch, n_val, record_steps=3)
+        for i in range(len(irs)):
+            for s in range(3):
+                ce, mse = res['train_loss'][0, s, i]
+                r = ref[i]['steps'][s]
+                lines.append(f'net {i} step {s}: ce {ce:.4f}/{r["ce"]:.4f} mse {mse:.4f}/{r["mse"]:.4f}')
+                if np.isnan(r['ce']) or np.isnan(r['mse']):
+                    continue                      # a NaN on the oracle side is the F6 selection pressure; bits are compared elsewhere
+                assert abs(ce - r['ce']) <= 3e-2 * max(1.0, abs(r['ce'])), (lines[-1], pop[i][0])
+                assert abs(mse - r['mse']) <= 3e-2 * max(0.05, abs(r['mse'])), (lines[-1], pop[i][0])
+        U.report(lines)
+    finally:
+        eng.close()
+
+
+def test_full_batch_row_independence():
+    """Size-independent property at the benchmark's batch (750 rows): inference is row-wise, so the logits of one pass
+    over 750 rows equal those of passes over 64-row pieces (other tile counts, split factors and sub-tile groupings)
+    up to the fp32 summation order of split reductions; both agree with the oracle on the first 64 rows."""
+    from serann_b200 import generator
+    from serann_b200.engine import Engine, set_tensor_cores
+    set_tensor_cores(True)
+    srcs = [U.NET_A, U.NET_E, U.NET_G, U.NET_H] + [s for s, _ in generator.sample_population(4, seed=77, max_flops_per_sample=4.0e6)]
+    irs = [frontend.compile_source(s) for s in srcs]
+    data = U.small_dataset(n_train=64, n_test=750, seed=9)
+    eng, inds = U.make_engine_and_oracle(irs, data, max_batch=750)
+    try:
+        whole = eng.forward_logits(1, 0, 750, training=False).astype(np.float32)
+        pieces = np.concatenate([eng.forward_logits(1, s, min(64, 750 - s), training=False) for s in range(0, 750, 64)], axis=1).astype(np.float32)
+        for i in range(len(irs)):
+            e = U.relerr(whole[i], pieces[i])
+            assert e < 2e-3, (i, e)
+            with torch.no_grad():
+                xi, gi = O.prepare_inputs(data['x_test'][:64], data['g_test'][:64])
+                ref = O.forward(inds[i], xi, gi, training=False).numpy()
+            assert U.relerr(whole[i][:64], ref) < ACT_TOL, i
+    finally:
+        eng.close()
