@@ -759,10 +759,11 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                                 tma_load_2d(aS, t_tm, kb * TC_BK, t_m0, bar);
                                 tma_load_2d(bS, t_tm + 128, kb * TC_BK, t_n0, bar);
                             } else {
-                                mbar_arrive_expect_tx(bar, 2 * 8192 + G * 8192);
+                                // accumulator rows 64..127 are only loaded when the tile has them (their garbage is never stored)
+                                mbar_arrive_expect_tx(bar, t_ga * 8192 + G * 8192);
                                 const int r = t_r0 + kb * TC_BK;
                                 tma_load_2d(aS, t_tm, t_m0, r, bar);
-                                tma_load_2d(aS + 8192, t_tm, t_m0 + 64, r, bar);
+                                if (t_ga == 2) tma_load_2d(aS + 8192, t_tm, t_m0 + 64, r, bar);
 #pragma unroll
                                 for (int g = 0; g < G; ++g) tma_load_2d(bS + g * 8192, t_tm + 128, t_n0 + g * 64, r, bar);
                             }
