@@ -53,6 +53,11 @@ struct Tensor {
     bool view = false;
     int inplace_of = -1;       // concat tensor whose buffer this tensor is written into directly (no copy)
     long long inplace_off = 0;
+    // Padded concatenation (a (1, F) concatenate read only by Dense layers): every member sits at an offset that is a
+    // multiple of 8 and a member produced in place keeps its padded [row][Cs] layout, so no member is compacted; the
+    // readers' kernels get zero rows at the pad positions.  phys_C = physical row length, colmap[logical] = physical.
+    long long phys_C = 0;
+    std::vector<int> colmap;
     bool needs_grad = false;
     int depth = 0;
     int consumers = 0;         // consumers needing din (counted on the root)
@@ -68,6 +73,9 @@ struct LayerRt {
     long long mov_off = -1;                                   // moving-statistics arena
     long long save_off = -1;                                  // fp32 BN scratch arena
     bool copy = false, dead = false;                          // reshape that needs a compacting copy / is never read
+    std::vector<long long> in_poff;                           // padded concatenate: physical offset of every member
+    std::vector<int> rowmap;                                  // Dense on a padded concatenation: logical kernel row -> arena row
+    int w_rows_log = 0;                                       // kernel rows as Keras counts them
 };
 
 struct Indiv {
@@ -386,6 +394,25 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
         }
         used[1 + nl] += 1;
         used_src[chase(1 + nl)] += 1;
+        // readers of a tensor (through reshapes) that are not Dense layers on a one-row view: a concatenation with none
+        // of them can take the padded layout
+        std::vector<int> other_readers(2 + nl, 0);
+        for (int l = 0; l < nl; ++l) {
+            const srn_layer_desc& d = layers[off[i] + l];
+            if (d.kind == SRN_KIND_RESHAPE) continue;
+            for (int j = 0; j < d.n_in && j < SRN_MAX_CONCAT_INPUTS; ++j) {
+                bool flat = d.kind == SRN_KIND_DENSE;
+                int t = d.in[j];
+                while (t >= 2 && layers[off[i] + t - 2].kind == SRN_KIND_RESHAPE) {
+                    const srn_layer_desc& r = layers[off[i] + t - 2];
+                    if ((long long)r.out_h * r.out_w != 1) flat = false;
+                    t = r.in[0];
+                }
+                if (!flat) other_readers[t] += 1;
+            }
+        }
+        other_readers[chase(1 + nl)] += 1;
+        const bool allow_padded = getenv("SRN_NO_PADDED_CONCAT") == nullptr;
         for (int l = 0; l < nl; ++l) {
             LayerRt& L = ind.layers[l];
             L.d = layers[off[i] + l];
@@ -416,13 +443,44 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                 }
             }
             to.bs = to.view ? ti.bs : to.rows * to.Cs;
+            if (to.view && ti.phys_C) { to.phys_C = ti.phys_C; to.colmap = ti.colmap; }
+            if (d.kind == SRN_KIND_CONCAT && to.rows == 1 && allow_padded && other_readers[2 + l] == 0) {
+                long long poff = 0;
+                to.colmap.resize((size_t)to.C);
+                long long e0 = 0;
+                for (int j = 0; j < d.n_in; ++j) {
+                    const int si = chase(d.in[j]);
+                    Tensor& S = ind.tensors[si];
+                    const bool cand = si >= 2 && !S.view && S.inplace_of < 0 && used_src[si] == 1 &&
+                                      ind.layers[si - 2].d.kind != SRN_KIND_CONCAT && ind.layers[si - 2].d.kind != SRN_KIND_RESHAPE;
+                    L.in_poff.push_back(poff);
+                    long long plen = S.elems;
+                    if (cand) {
+                        plen = S.rows * S.Cs;
+                        S.inplace_of = 2 + l; S.inplace_off = poff;
+                        for (long long r = 0; r < S.rows; ++r)
+                            for (int c = 0; c < S.C; ++c) to.colmap[(size_t)(e0 + r * S.C + c)] = (int)(poff + r * S.Cs + c);
+                    } else {
+                        for (long long e = 0; e < S.elems; ++e) to.colmap[(size_t)(e0 + e)] = (int)(poff + e);
+                    }
+                    e0 += S.elems;
+                    poff += align_up(plen, 8);
+                }
+                to.phys_C = poff; to.Cs = (int)poff; to.bs = poff;
+                for (int j = 0; j < d.n_in; ++j) {
+                    Tensor& S = ind.tensors[chase(d.in[j])];
+                    if (S.inplace_of == 2 + l) S.bs = poff;
+                }
+            }
             if (d.kind == SRN_KIND_DENSE || d.kind == SRN_KIND_CONV) {
                 L.w_rows = d.kind == SRN_KIND_DENSE ? d.in_c : d.kh * d.kw * d.in_c;
+                L.w_rows_log = L.w_rows;
+                if (d.kind == SRN_KIND_DENSE && ti.phys_C) { L.w_rows = (int)ti.phys_C; L.rowmap = ti.colmap; }
                 L.w_cols = d.units; L.ldw = (int)align_up(d.units, 8);
                 L.w_cnt = (long long)L.w_rows * L.ldw; L.b_cnt = d.units;
                 L.w_off = p_off; p_off = align_up(p_off + L.w_cnt, 8);
                 L.b_off = p_off; p_off = align_up(p_off + L.b_cnt, 8);
-                ind.pcount += (long long)L.w_rows * L.w_cols + L.b_cnt;
+                ind.pcount += (long long)L.w_rows_log * L.w_cols + L.b_cnt;
             } else if (d.kind == SRN_KIND_BN) {
                 L.w_cnt = L.b_cnt = d.in_c; L.w_rows = 1; L.w_cols = L.ldw = d.in_c;
                 L.w_off = p_off; p_off = align_up(p_off + L.w_cnt, 8);
@@ -440,7 +498,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
         // slice copy disappear; the producers and gradient readers honour the buffer's batch stride
         for (int l = 0; l < nl; ++l) {
             const srn_layer_desc& d = ind.layers[l].d;
-            if (d.kind != SRN_KIND_CONCAT || ind.tensors[2 + l].rows != 1) continue;
+            if (d.kind != SRN_KIND_CONCAT || ind.tensors[2 + l].rows != 1 || ind.tensors[2 + l].phys_C) continue;
             long long coff = 0;
             for (int j = 0; j < d.n_in; ++j) {
                 const int si = chase(d.in[j]);
@@ -513,6 +571,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
             for (int j = 0; j < d.n_in; ++j) {
                 const int tin = d.kind == SRN_KIND_CONCAT ? chase(d.in[j]) : d.in[j];
                 Tensor& ti = ind.tensors[tin];
+                if (d.kind == SRN_KIND_CONCAT && !L.in_poff.empty()) coff = (int)L.in_poff[j];     // padded concatenation: aligned physical offsets
                 if (d.kind == SRN_KIND_CONCAT && ti.inplace_of == (int)(2 + l)) { coff += (int)ti.elems; continue; }   // already in place
                 Tensor& troot = ind.tensors[ti.root];
                 Prob p{};
@@ -533,6 +592,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                 if (d.kind == SRN_KIND_DENSE || d.kind == SRN_KIND_CONV) {
                     if (d.kind == SRN_KIND_CONV) { p.kh = d.kh; p.kw = d.kw; p.sh = d.sh; p.sw = d.sw; }
                     else { p.H = (int)ti.rows; p.W = 1; p.Ho = p.H; p.Wo = 1; }
+                    if (d.kind == SRN_KIND_DENSE && ti.phys_C) p.C = (int)ti.phys_C;      // zero kernel rows at the pad positions
                     p.w = h->P + L.w_off; p.bias = h->P + L.b_off;
                     p.gw = h->Gr + L.w_off; p.gb = h->Gr + L.b_off;
                     p.ldw = L.ldw;
@@ -554,6 +614,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                 } else if (is_copy) {
                     kind = SRN_KIND_CONCAT;
                     p.n_el = (int)ti.elems;
+                    if (to.phys_C) p.F = (int)to.phys_C;
                     p.Cj = (int)(ti.elems / to.rows);
                     p.coff = coff;
                     coff += p.Cj;
@@ -649,6 +710,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
     CK(cudaMalloc(&h->d_lb, n * sizeof(float)));
     CK(cudaMemcpyAsync(h->d_lb, loss_balance, n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
     // ---- Keras default initialisation on the device
+    std::vector<long long> pad_off; std::vector<int> pad_len;     // kernel rows to clear afterwards (padded concatenations)
     for (int i = 0; i < n; ++i) {
         Indiv& ind = h->inds[i];
         for (size_t l = 0; l < ind.layers.size(); ++l) {
@@ -668,13 +730,28 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                     la = lbm = (float)std::sqrt(6.0 / (fan_in + (double)d.units * rf));
                 }
                 LAUNCH(SRN_CAT_OTHER, k_init_uniform, (unsigned)((L.w_cnt + 255) / 256), 256, h->P + L.w_off, L.w_cnt, d.units, L.ldw, split, la, lbm, tseed);
+                if (!L.rowmap.empty()) {      // kernel rows of pad positions are zero and stay zero (zero activations -> zero gradient -> no update)
+                    std::vector<char> live((size_t)L.w_rows, 0);
+                    for (int r : L.rowmap) live[(size_t)r] = 1;
+                    for (int r = 0; r < L.w_rows; ++r)
+                        if (!live[(size_t)r]) { pad_off.push_back(L.w_off + (long long)r * L.ldw); pad_len.push_back(L.ldw); }
+                }
             } else if (d.kind == SRN_KIND_BN) {
                 LAUNCH(SRN_CAT_OTHER, k_fill_f16, (unsigned)((L.w_cnt + 255) / 256), 256, h->P + L.w_off, L.w_cnt, 1.0f);          // gamma
                 LAUNCH(SRN_CAT_OTHER, k_fill_f16, (unsigned)((d.in_c + 255) / 256), 256, h->S + L.mov_off + d.in_c, (long long)d.in_c, 1.0f);  // moving variance
             }
         }
     }
+    long long* d_pad_off = nullptr; int* d_pad_len = nullptr;
+    if (!pad_off.empty()) {
+        CK(cudaMalloc(&d_pad_off, pad_off.size() * sizeof(long long)));
+        CK(cudaMalloc(&d_pad_len, pad_len.size() * sizeof(int)));
+        CK(cudaMemcpyAsync(d_pad_off, pad_off.data(), pad_off.size() * sizeof(long long), cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(d_pad_len, pad_len.data(), pad_len.size() * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+        LAUNCH(SRN_CAT_OTHER, k_zero_spans, (unsigned)pad_off.size(), 64, h->P, d_pad_off, d_pad_len);
+    }
     CK(cudaStreamSynchronize(h->stream));
+    cudaFree(d_pad_off); cudaFree(d_pad_len);
     CK(cudaGetLastError());
     h->n = n;
     h->adam_t = 0;
@@ -690,7 +767,8 @@ extern "C" int64_t srn_parameters_count(srn_engine* h, int32_t i) {
 extern "C" int64_t srn_device_bytes(srn_engine* h) { return h ? h->device_bytes : -1; }
 
 // weight `which` of a layer as a [rows][cols] matrix with leading dimension ld inside the arena
-static int locate_weights(srn_engine* h, int ind, int layer, int which, __half** ptr, int64_t* cnt, int* rows, int* cols, int* ld) {
+static int locate_weights(srn_engine* h, int ind, int layer, int which, __half** ptr, int64_t* cnt, int* rows, int* cols, int* ld,
+                          const std::vector<int>** rowmap = nullptr) {
     if (!h || !h->built) return fail(SRN_ERR_STATE, "weights: engine has no population");
     if (ind < 0 || ind >= h->n) return fail(SRN_ERR_ARG, "weights: individual %d", ind);
     Indiv& I = h->inds[ind];
@@ -698,8 +776,10 @@ static int locate_weights(srn_engine* h, int ind, int layer, int which, __half**
     const LayerRt& L = I.layers[layer];
     const int kind = L.d.kind;
     *ptr = nullptr;
+    if (rowmap) *rowmap = nullptr;
     if (kind == SRN_KIND_DENSE || kind == SRN_KIND_CONV) {
-        if (which == 0) { *ptr = h->P + L.w_off; *rows = L.w_rows; *cols = L.w_cols; *ld = L.ldw; }
+        // a Dense on a padded concatenation keeps zero rows at the pad positions: callers see the Keras rows through rowmap
+        if (which == 0) { *ptr = h->P + L.w_off; *rows = L.w_rows_log; *cols = L.w_cols; *ld = L.ldw; if (rowmap && !L.rowmap.empty()) *rowmap = &L.rowmap; }
         if (which == 1) { *ptr = h->P + L.b_off; *rows = 1; *cols = (int)L.b_cnt; *ld = (int)L.b_cnt; }
     } else if (kind == SRN_KIND_BN) {
         const int C = L.d.in_c;
@@ -714,28 +794,50 @@ static int locate_weights(srn_engine* h, int ind, int layer, int which, __half**
     return SRN_OK;
 }
 
+// rows of a [rows][cols] matrix between the host (dense) and the arena (leading dimension ld, optional row map)
+static int copy_rows(void* host, char* dev, int rows, int cols, int ld, size_t esz, const std::vector<int>* rowmap, bool to_host) {
+    if (!rowmap) {
+        if (to_host) CK(cudaMemcpy2D(host, cols * esz, dev, ld * esz, cols * esz, rows, cudaMemcpyDeviceToHost));
+        else CK(cudaMemcpy2D(dev, ld * esz, host, cols * esz, cols * esz, rows, cudaMemcpyHostToDevice));
+        return SRN_OK;
+    }
+    int prows = 0;
+    for (int r : *rowmap) prows = std::max(prows, r + 1);
+    std::vector<char> tmp((size_t)prows * cols * esz, 0);
+    if (to_host) {
+        CK(cudaMemcpy2D(tmp.data(), cols * esz, dev, ld * esz, cols * esz, prows, cudaMemcpyDeviceToHost));
+        for (int r = 0; r < rows; ++r) memcpy((char*)host + (size_t)r * cols * esz, tmp.data() + (size_t)(*rowmap)[r] * cols * esz, cols * esz);
+    } else {
+        // pad rows are rewritten with zeros, which is what they hold anyway
+        for (int r = 0; r < rows; ++r) memcpy(tmp.data() + (size_t)(*rowmap)[r] * cols * esz, (const char*)host + (size_t)r * cols * esz, cols * esz);
+        CK(cudaMemcpy2D(dev, ld * esz, tmp.data(), cols * esz, cols * esz, prows, cudaMemcpyHostToDevice));
+    }
+    return SRN_OK;
+}
+
 extern "C" int srn_get_weights(srn_engine* h, int32_t ind, int32_t layer, int32_t which, uint16_t* buf, int64_t* count) {
-    __half* p; int64_t c; int rows, cols, ld;
-    int rc = locate_weights(h, ind, layer, which, &p, &c, &rows, &cols, &ld);
+    __half* p; int64_t c; int rows, cols, ld; const std::vector<int>* rm;
+    int rc = locate_weights(h, ind, layer, which, &p, &c, &rows, &cols, &ld, &rm);
     if (rc) return rc;
     if (count) *count = c;
     if (buf) {
         CK(cudaSetDevice(h->cfg.device));
         CK(cudaStreamSynchronize(h->stream));
-        CK(cudaMemcpy2D(buf, (size_t)cols * sizeof(__half), p, (size_t)ld * sizeof(__half), (size_t)cols * sizeof(__half), rows, cudaMemcpyDeviceToHost));
+        CK(cudaStreamSynchronize(h->adam_stream));
+        return copy_rows(buf, reinterpret_cast<char*>(p), rows, cols, ld, sizeof(__half), rm, true);
     }
     return SRN_OK;
 }
 
 extern "C" int srn_set_weights(srn_engine* h, int32_t ind, int32_t layer, int32_t which, const uint16_t* buf, int64_t count) {
-    __half* p; int64_t c; int rows, cols, ld;
-    int rc = locate_weights(h, ind, layer, which, &p, &c, &rows, &cols, &ld);
+    __half* p; int64_t c; int rows, cols, ld; const std::vector<int>* rm;
+    int rc = locate_weights(h, ind, layer, which, &p, &c, &rows, &cols, &ld, &rm);
     if (rc) return rc;
     if (!buf || count != c) return fail(SRN_ERR_ARG, "set_weights: expected %lld elements, got %lld", (long long)c, (long long)count);
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
-    CK(cudaMemcpy2D(p, (size_t)ld * sizeof(__half), buf, (size_t)cols * sizeof(__half), (size_t)cols * sizeof(__half), rows, cudaMemcpyHostToDevice));
-    return SRN_OK;
+    CK(cudaStreamSynchronize(h->adam_stream));
+    return copy_rows(const_cast<uint16_t*>(buf), reinterpret_cast<char*>(p), rows, cols, ld, sizeof(__half), rm, false);
 }
 
 extern "C" int srn_set_tensor_cores(int32_t on) {
@@ -1440,22 +1542,29 @@ extern "C" int srn_debug_get_tensor(srn_engine* h, int32_t ind, int32_t tensor, 
     if (!src) return fail(SRN_ERR_ARG, "srn_debug_get_tensor: tensor %d has no %s buffer", tensor, grad ? "gradient" : "activation");
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
-    if (T.bs == T.rows * T.Cs)
+    if (T.phys_C) {             // padded concatenation (or a view of one): gather the logical columns
+        std::vector<uint16_t> tmp((size_t)nb * T.phys_C);
+        CK(cudaMemcpy2D(tmp.data(), (size_t)T.phys_C * 2, src, (size_t)T.bs * 2, (size_t)T.phys_C * 2, (size_t)nb, cudaMemcpyDeviceToHost));
+        for (int b = 0; b < nb; ++b)
+            for (long long e = 0; e < T.elems; ++e) buf[(size_t)b * T.elems + e] = tmp[(size_t)b * T.phys_C + T.colmap[(size_t)e]];
+    } else if (T.bs == T.rows * T.Cs) {
         CK(cudaMemcpy2D(buf, (size_t)T.C * sizeof(__half), src, (size_t)T.Cs * sizeof(__half), (size_t)T.C * sizeof(__half), (size_t)nb * T.rows, cudaMemcpyDeviceToHost));
-    else        // produced in place inside a concatenation buffer: dense rows (Cs == C), the buffer's batch stride
-        CK(cudaMemcpy2D(buf, (size_t)T.elems * sizeof(__half), src, (size_t)T.bs * sizeof(__half), (size_t)T.elems * sizeof(__half), (size_t)nb, cudaMemcpyDeviceToHost));
+    } else {                    // produced in place inside a concatenation buffer: rows of Cs, the buffer's batch stride
+        for (int b = 0; b < nb; ++b)
+            CK(cudaMemcpy2D(buf + (size_t)b * T.elems, (size_t)T.C * sizeof(__half), src + (size_t)b * T.bs, (size_t)T.Cs * sizeof(__half),
+                            (size_t)T.C * sizeof(__half), (size_t)T.rows, cudaMemcpyDeviceToHost));
+    }
     return SRN_OK;
 }
 
 extern "C" int srn_debug_get_grad(srn_engine* h, int32_t ind, int32_t layer, int32_t which, float* buf, int64_t count) {
-    __half* p; int64_t c; int rows, cols, ld;
-    int rc = locate_weights(h, ind, layer, which, &p, &c, &rows, &cols, &ld);
+    __half* p; int64_t c; int rows, cols, ld; const std::vector<int>* rm;
+    int rc = locate_weights(h, ind, layer, which, &p, &c, &rows, &cols, &ld, &rm);
     if (rc) return rc;
     if (which > 1 || count != c) return fail(SRN_ERR_ARG, "srn_debug_get_grad: bad which/count");
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
-    CK(cudaMemcpy2D(buf, (size_t)cols * sizeof(float), h->Gr + (p - h->P), (size_t)ld * sizeof(float), (size_t)cols * sizeof(float), rows, cudaMemcpyDeviceToHost));
-    return SRN_OK;
+    return copy_rows(buf, reinterpret_cast<char*>(h->Gr + (p - h->P)), rows, cols, ld, sizeof(float), rm, true);
 }
 
 extern "C" int srn_debug_launch_groups(srn_engine* h) { return h && h->built ? (int)h->groups.size() : -1; }

@@ -686,6 +686,13 @@ k_copy(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob
     }
 }
 
+// clears spans of the parameter arena (one block per span): kernel rows that stand for pad positions of a padded
+// concatenation
+static __global__ void k_zero_spans(__half* __restrict__ P, const long long* __restrict__ off, const int* __restrict__ len) {
+    __half* p = P + off[blockIdx.x];
+    for (int i = threadIdx.x; i < len[blockIdx.x]; i += blockDim.x) p[i] = __float2half_rn(0.f);
+}
+
 // ------------------------------------------------------------------ shared im2col of a one-channel model input
 // In training and evaluation every individual sees the same image / genotype batch, so the patch matrix of a
 // first layer depends only on its window geometry: it is written once per batch and geometry as
