@@ -51,7 +51,7 @@ __device__ __forceinline__ float col_block_sum(const float* sm, const ColGeom& g
 
 // ------------------------------------------------------------------ activation backward + bias gradient
 // gout <- fp16(gout * act'(out)) in place (TF's ReluGrad / SigmoidGrad); gb[f] += column sums of the result.
-static __global__ void __launch_bounds__(COL_THREADS)
+static __global__ void __launch_bounds__(COL_THREADS, 4)
 k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb) {
     __shared__ float sm[COL_THREADS * 8];
     const int pi = find_prob(prefix, nprob, blockIdx.x);
@@ -120,7 +120,7 @@ constexpr float BN_DECAY16 = 0.01000213623046875f;        // fp16(1 - 0.99)
 constexpr float BN_ONE_EPS16 = 1.0009765625f;             // fp16(1 + 1e-3)
 
 // forward: shifted sums (x - x0), (x - x0)^2 around the first row; backward: sum dy, sum dy * (x - mean16)
-static __global__ void __launch_bounds__(COL_THREADS)
+static __global__ void __launch_bounds__(COL_THREADS, 4)
 k_bn_partial(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, Inputs I, int bwd) {
     __shared__ float sm1[COL_THREADS * 8];
     __shared__ float sm2[COL_THREADS * 8];
