@@ -602,6 +602,8 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                         // model input, im2col gathered element by element
                         if (p.Cs % 8 == 0 && p.Fs % 8 == 0) tc = 1;
                         else if (p.in_sel != 0 && p.Cs == 1 && p.C == 1 && p.Fs % 8 == 0) tc = 2;   // only the model inputs have Cs == 1
+                        // 3: Dense / 1 x 1 convolution on a one-channel model input: an outer product, elementwise kernels
+                        if (tc == 2 && p.kh * p.kw == 1) tc = 3;
                         if (tc) { cfgF = tc_cfg_for(p.F); cfgC = tc_cfg_for(p.C); }
                     }
                 } else if (d.kind == SRN_KIND_MAXPOOL) {
@@ -907,6 +909,7 @@ static int pass_items(const Group& g, const Prob& p, int pass, int nb, int smax)
         case SRN_KIND_DENSE:
         case SRN_KIND_CONV:
             if (pass == P_COL) return col_chunks(out_rows, p.Fs);
+            if (g.tc == 3) return pass == P_FWD ? ew_blocks(out_rows, p.Fs) : 0;      // wgrad rides on the bias-gradient pass
             if (g.tc) {
                 if (pass == P_FWD) return tc_tiles_fwd(p, nb, TC_BN[g.cfgF], smax);
                 if (pass == P_DGRAD) return p.din ? tc_tiles_dgrad(p, nb, TC_BN[g.cfgC]) : 0;
@@ -955,7 +958,7 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
     CK(cudaStreamSynchronize(h->stream));      // host vector goes out of scope
     h->scratch_prefix.push_back(dev);
     for (int pass = 0; pass < P_COUNT; ++pass) c.prefix[pass] = dev + (size_t)pass * (np + 1);
-    if (g.tc) {
+    if (g.tc == 1 || g.tc == 2) {
         for (int pass : {P_FWD, P_DGRAD, P_WGRAD}) {
             if (!c.total[pass]) continue;
             const int* pre = host.data() + (size_t)pass * (np + 1);
@@ -1081,6 +1084,10 @@ static int fwd_group(srn_engine* h, Group& g, int nb, const Inputs& I, bool trai
     switch (g.kind) {
         case SRN_KIND_DENSE:
         case SRN_KIND_CONV:
+            if (g.tc == 3) {
+                LAUNCH(SRN_CAT_GEMM_FWD, k_dense_k1_fwd, c->total[P_FWD], EW_THREADS, g.d, c->prefix[P_FWD], np, nb, I);
+                break;
+            }
             if (g.tc) {
                 const int BN = TC_BN[g.cfgF];
                 if (g.tc == 1) LAUNCH_TC(SRN_CAT_GEMM_FWD, TC_FWD, false, P_FWD, BN);
@@ -1166,7 +1173,11 @@ static int bwd_group(srn_engine* h, Group& g, int nb, const Inputs& I) {
     switch (g.kind) {
         case SRN_KIND_DENSE:
         case SRN_KIND_CONV:
-            LAUNCH(SRN_CAT_ACT_BWD, k_act_bwd_bias, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb);
+            if (g.tc == 3) {
+                LAUNCH(SRN_CAT_ACT_BWD, k_act_bwd_bias<true>, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I);
+                break;
+            }
+            LAUNCH(SRN_CAT_ACT_BWD, k_act_bwd_bias<false>, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I);
             if (g.tc) {
                 const int BNf = TC_BN[g.cfgF], BNc = TC_BN[g.cfgC];
                 if (g.tc == 1) LAUNCH_TC(SRN_CAT_GEMM_WGRAD, TC_WGRAD, false, P_WGRAD, BNf);

@@ -51,8 +51,11 @@ __device__ __forceinline__ float col_block_sum(const float* sm, const ColGeom& g
 
 // ------------------------------------------------------------------ activation backward + bias gradient
 // gout <- fp16(gout * act'(out)) in place (TF's ReluGrad / SigmoidGrad); gb[f] += column sums of the result.
+// K1: Dense (or 1 x 1 convolution) on a one-channel model input - the kernel is a single row, its gradient
+// gw[f] = sum_r x[r] * dZ[r][f] is one more column sum of the same pass (no GEMM launch for these layers).
+template <bool K1>
 static __global__ void __launch_bounds__(COL_THREADS, 4)
-k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb) {
+k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, Inputs I) {
     __shared__ float sm[COL_THREADS * 8];
     const int pi = find_prob(prefix, nprob, blockIdx.x);
     const Prob p = probs[pi];
@@ -67,9 +70,13 @@ k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
         const int rl = g.nq <= COL_THREADS ? tid / g.nq : 0;
         const bool active = rl < g.RL && cq < g.nq;
         float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        float sx[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        int in_bs = 0;
+        const __half* xin = K1 ? resolve_in(p, I, in_bs) : nullptr;
         if (active) {
             for (long long r = r0 + rl; r < r1; r += g.RL) {
                 const long long o = out_row_off(r, p.Ho * p.Wo, p.out_bs, Fs) + (long long)cq * g.cw;
+                const float xr = K1 ? __half2float(xin[in_row_off(r, p.H * p.W, in_bs, 1)]) : 0.f;
                 if (g.cw == 8) {
                     Half8 gv = ld8(p.gout + o);
                     if (p.act == 1) {
@@ -87,18 +94,23 @@ k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
                         st8(p.gout + o, gv);
                     }
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) s[j] += __half2float(gv.v[j]);
+                    for (int j = 0; j < 8; ++j) { const float gj = __half2float(gv.v[j]); s[j] += gj; if (K1) sx[j] += gj * xr; }
                 } else {
                     float gg = __half2float(p.gout[o]);
                     if (p.act == 1) { gg = __half2float(p.out[o]) > 0.f ? gg : 0.f; p.gout[o] = __float2half_rn(gg); }
                     else if (p.act == 2) { const float yy = __half2float(p.out[o]); gg = rh(rh(gg * yy) * rh(1.f - yy)); p.gout[o] = __float2half_rn(gg); }
                     s[0] += gg;
+                    if (K1) sx[0] += gg * xr;
                 }
             }
         }
         if (g.RL == 1) {
             if (active)
-                for (int j = 0; j < g.cw; ++j) { const int f = cq * g.cw + j; if (f < F && s[j] != 0.f) atomicAdd(&p.gb[f], s[j]); }
+                for (int j = 0; j < g.cw; ++j) {
+                    const int f = cq * g.cw + j;
+                    if (f < F && s[j] != 0.f) atomicAdd(&p.gb[f], s[j]);
+                    if (K1 && f < F && sx[j] != 0.f) atomicAdd(&p.gw[f], sx[j]);
+                }
         } else {
 #pragma unroll
             for (int j = 0; j < 8; ++j) sm[tid * 8 + j] = active ? s[j] : 0.f;
@@ -108,6 +120,16 @@ k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
                 if (ch < F && t != 0.f) atomicAdd(&p.gb[ch], t);
             }
             __syncthreads();
+            if (K1) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sm[tid * 8 + j] = active ? sx[j] : 0.f;
+                __syncthreads();
+                for (int ch = tid; ch < g.nq * g.cw; ch += COL_THREADS) {
+                    const float t = col_block_sum(sm, g, ch);
+                    if (ch < F && t != 0.f) atomicAdd(&p.gw[ch], t);
+                }
+                __syncthreads();
+            }
         }
     }
 }
@@ -565,6 +587,36 @@ k_maxpool_bwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
             if (p.din_acc) v = rh(v) + __half2float(*d);
             *d = __float2half_rn(v);
         }
+    }
+}
+
+// ------------------------------------------------------------------ Dense on a one-channel model input (K = 1)
+// out[r][f] = act(fp16(fp16(x[r] * w[f]) + b[f])): an outer product, bound by the output write.  One thread per row and
+// chunk of 8 units; bit-identical to the GEMM path (one exact fp32 product, then the same roundings).
+static __global__ void __launch_bounds__(EW_THREADS)
+k_dense_k1_fwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, Inputs I) {
+    const int pi = find_prob(prefix, nprob, blockIdx.x);
+    const Prob p = probs[pi];
+    const int blk = blockIdx.x - prefix[pi];
+    const int Fs = p.Fs, rps = p.Ho * p.Wo, nq = Fs >> 3;
+    const unsigned total = (unsigned)nb * (unsigned)rps * (unsigned)nq;
+    int in_bs;
+    const __half* in = resolve_in(p, I, in_bs);
+    unsigned q = (unsigned)blk * EW_PER_CTA + threadIdx.x;
+#pragma unroll
+    for (int i = 0; i < EW_PER_THREAD; ++i, q += EW_THREADS) {
+        if (q >= total) break;
+        const unsigned r = q / (unsigned)nq; const int c0 = (int)(q - r * (unsigned)nq) * 8;
+        const float x = __half2float(in[in_row_off(r, p.H * p.W, in_bs, 1)]);
+        const Half8 w = ld8(p.w + c0), b = ld8(p.bias + c0);
+        Half8 o;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float z = 0.f;
+            if (c0 + j < p.F) z = act_forward(rh(rh(x * __half2float(w.v[j])) + __half2float(b.v[j])), p.act);
+            o.v[j] = __float2half_rn(z);
+        }
+        st8(p.out + out_row_off(r, rps, p.out_bs, Fs) + c0, o);
     }
 }
 
