@@ -963,6 +963,11 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
 #pragma unroll
                         for (int j = 0; j < 16; j += 4)
                             *reinterpret_cast<float4*>(grow + n0 + cb + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    } else if (!single && n0 + cb + 16 <= p.ldw) {   // split reduction: four-wide fp32 atomics (pad columns add zeros)
+#pragma unroll
+                        for (int j = 0; j < 16; j += 4)
+                            if (n0 + cb + j < Ncols)
+                                atomicAdd(reinterpret_cast<float4*>(grow + n0 + cb + j), make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
                     } else {
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
