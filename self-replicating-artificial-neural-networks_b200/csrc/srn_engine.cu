@@ -96,6 +96,7 @@ struct Group {
     int mode = 3;                  // bit 0: runs when the inputs are a shared batch, bit 1: when they are per individual
     std::vector<Prob> h;
     Prob* d = nullptr;
+    int* done = nullptr;           // BatchNorm buckets: per-problem chunk counters of the fused finalize
     std::map<int, Cached> cache;
 };
 
@@ -195,7 +196,7 @@ extern "C" uint64_t srn_launch_count(void) { return g_launches.load(); }
 
 // ------------------------------------------------------------------ create / destroy
 static void free_population(srn_engine* h) {
-    for (auto& g : h->groups) cudaFree(g.d);
+    for (auto& g : h->groups) { cudaFree(g.d); cudaFree(g.done); }
     for (int* p : h->scratch_prefix) cudaFree(p);
     h->scratch_prefix.clear();
     h->groups.clear();
@@ -704,6 +705,10 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
         }
     }
     for (auto& g : h->groups) {
+        if (g.kind == SRN_KIND_BN) {
+            CK(cudaMalloc(&g.done, g.h.size() * sizeof(int)));
+            CK(cudaMemsetAsync(g.done, 0, g.h.size() * sizeof(int), h->stream));
+        }
         CK(cudaMalloc(&g.d, g.h.size() * sizeof(Prob)));
         CK(cudaMemcpyAsync(g.d, g.h.data(), g.h.size() * sizeof(Prob), cudaMemcpyHostToDevice, h->stream));
     }
@@ -1103,8 +1108,7 @@ static int fwd_group(srn_engine* h, Group& g, int nb, const Inputs& I, bool trai
             break;
         case SRN_KIND_BN:
             if (training) {
-                LAUNCH(SRN_CAT_BN, k_bn_partial, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I, 0);
-                LAUNCH(SRN_CAT_BN, k_bn_finalize_fwd, np, 128, g.d, nb, I);
+                LAUNCH(SRN_CAT_BN, k_bn_partial, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I, 0, g.done);
             } else {
                 LAUNCH(SRN_CAT_BN, k_bn_prepare_infer, np, 128, g.d);
             }
@@ -1194,8 +1198,7 @@ static int bwd_group(srn_engine* h, Group& g, int nb, const Inputs& I) {
             LAUNCH(SRN_CAT_POOL, k_maxpool_bwd, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I);
             break;
         case SRN_KIND_BN:
-            LAUNCH(SRN_CAT_BN, k_bn_partial, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I, 1);
-            LAUNCH(SRN_CAT_BN, k_bn_finalize_bwd, np, 128, g.d, nb);
+            LAUNCH(SRN_CAT_BN, k_bn_partial, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I, 1, g.done);
             LAUNCH(SRN_CAT_BN, k_bn_bwd_apply, c->total[P_BWD_EW], EW_THREADS, g.d, c->prefix[P_BWD_EW], np, nb, I);
             break;
         case SRN_KIND_CONCAT:

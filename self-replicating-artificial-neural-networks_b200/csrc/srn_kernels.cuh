@@ -142,8 +142,12 @@ constexpr float BN_DECAY16 = 0.01000213623046875f;        // fp16(1 - 0.99)
 constexpr float BN_ONE_EPS16 = 1.0009765625f;             // fp16(1 + 1e-3)
 
 // forward: shifted sums (x - x0), (x - x0)^2 around the first row; backward: sum dy, sum dy * (x - mean16)
+static __device__ void bn_finalize_fwd_dev(const Prob& p, int nb, const Inputs& I);
+static __device__ void bn_finalize_bwd_dev(const Prob& p, int nb);
+// done != nullptr: the CTA that finishes a problem's last chunk also combines the partials (no separate finalize launch);
+// done[problem] counts finished chunks and is left at zero
 static __global__ void __launch_bounds__(COL_THREADS, 4)
-k_bn_partial(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, Inputs I, int bwd) {
+k_bn_partial(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, Inputs I, int bwd, int* done = nullptr) {
     __shared__ float sm1[COL_THREADS * 8];
     __shared__ float sm2[COL_THREADS * 8];
     const int pi = find_prob(prefix, nprob, blockIdx.x);
@@ -234,6 +238,18 @@ k_bn_partial(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
             __syncthreads();
         }
     }
+    if (done) {
+        __shared__ int last;
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) last = atomicAdd(&done[pi], 1) == prefix[pi + 1] - prefix[pi] - 1;
+        __syncthreads();
+        if (last) {
+            __threadfence();
+            if (bwd) bn_finalize_bwd_dev(p, nb); else bn_finalize_fwd_dev(p, nb, I);
+            if (tid == 0) done[pi] = 0;
+        }
+    }
 }
 
 __device__ __forceinline__ void bn_scale_shift(float mean16, float var16, float gamma, float beta,
@@ -263,6 +279,9 @@ __device__ __forceinline__ void bn_chunk_sums(const float* part, int chunks, int
 static __global__ void __launch_bounds__(128)
 k_bn_finalize_fwd(const Prob* __restrict__ probs, int nb, Inputs I) {
     const Prob p = probs[blockIdx.x];
+    bn_finalize_fwd_dev(p, nb, I);
+}
+static __device__ void bn_finalize_fwd_dev(const Prob& p, int nb, const Inputs& I) {
     const int C = p.C, Cs = p.Cs;
     const long long rows = (long long)nb * p.H * p.W;
     const int chunks = col_chunks(rows, Cs);
@@ -355,6 +374,9 @@ k_bn_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, int n
 static __global__ void __launch_bounds__(128)
 k_bn_finalize_bwd(const Prob* __restrict__ probs, int nb) {
     const Prob p = probs[blockIdx.x];
+    bn_finalize_bwd_dev(p, nb);
+}
+static __device__ void bn_finalize_bwd_dev(const Prob& p, int nb) {
     const int C = p.C, Cs = p.Cs;
     const long long rows = (long long)nb * p.H * p.W;
     const int chunks = col_chunks(rows, Cs);
