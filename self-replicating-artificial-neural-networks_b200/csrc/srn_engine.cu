@@ -117,6 +117,13 @@ struct srn_engine {
     cudaStream_t side[NSIDE] = {};        // independent launch buckets of one depth level overlap their tails on these
     cudaEvent_t ev_fork = nullptr, ev_join[NSIDE] = {};
     // the optimiser pass runs on its own stream so that the next step's batch gather and im2col overlap it
+    // weight-gradient launches float: they only need their layer's activation backward, nothing in the backward pass
+    // needs them, so they run on their own streams, fill the idle SMs of the latency-bound deep levels and are joined
+    // before the optimiser
+    static constexpr int NWG = 3;
+    cudaStream_t wg_stream[NWG] = {};
+    cudaEvent_t ev_wg = nullptr, ev_wg_done[NWG] = {};
+    int wg_next = 0; bool wg_used[NWG] = {};
     cudaStream_t adam_stream = nullptr;
     cudaEvent_t ev_adam_go = nullptr, ev_adam_done = nullptr;
     bool adam_pending = false;
@@ -239,6 +246,11 @@ extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
     }
     CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
     CK(cudaStreamCreateWithFlags(&h->adam_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&h->ev_wg, cudaEventDisableTiming));
+    for (int i = 0; i < srn_engine::NWG; ++i) {
+        CK(cudaStreamCreateWithFlags(&h->wg_stream[i], cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&h->ev_wg_done[i], cudaEventDisableTiming));
+    }
     CK(cudaEventCreateWithFlags(&h->ev_adam_go, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->ev_adam_done, cudaEventDisableTiming));
     h->multi_stream = getenv("SRN_SINGLE_STREAM") == nullptr;
@@ -264,6 +276,11 @@ extern "C" void srn_destroy(srn_engine* h) {
     if (h->ev_adam_go) cudaEventDestroy(h->ev_adam_go);
     if (h->ev_adam_done) cudaEventDestroy(h->ev_adam_done);
     if (h->adam_stream) cudaStreamDestroy(h->adam_stream);
+    if (h->ev_wg) cudaEventDestroy(h->ev_wg);
+    for (int i = 0; i < srn_engine::NWG; ++i) {
+        if (h->ev_wg_done[i]) cudaEventDestroy(h->ev_wg_done[i]);
+        if (h->wg_stream[i]) cudaStreamDestroy(h->wg_stream[i]);
+    }
     for (int s = 0; s < 2; ++s) { cudaFree(h->x[s]); cudaFree(h->y[s]); cudaFree(h->gb[s]); }
     cudaFree(h->xin); cudaFree(h->gin); cudaFree(h->lab);
     delete h;
@@ -1182,14 +1199,28 @@ static int bwd_group(srn_engine* h, Group& g, int nb, const Inputs& I) {
                 break;
             }
             LAUNCH(SRN_CAT_ACT_BWD, k_act_bwd_bias<false>, c->total[P_COL], COL_THREADS, g.d, c->prefix[P_COL], np, nb, I);
+            {
+                // the weight gradient goes to a floating stream behind this bucket's activation backward
+                cudaStream_t lane = h->cur;
+                if (h->multi_stream) {
+                    const int w = h->wg_next; h->wg_next = (w + 1) % srn_engine::NWG; h->wg_used[w] = true;
+                    cudaEventRecord(h->ev_wg, lane);
+                    cudaStreamWaitEvent(h->wg_stream[w], h->ev_wg, 0);
+                    h->cur = h->wg_stream[w];
+                }
+                if (g.tc) {
+                    const int BNf = TC_BN[g.cfgF];
+                    if (g.tc == 1) LAUNCH_TC(SRN_CAT_GEMM_WGRAD, TC_WGRAD, false, P_WGRAD, BNf);
+                    else LAUNCH_TC(SRN_CAT_GEMM_WGRAD, TC_WGRAD, true, P_WGRAD, BNf);
+                } else {
+                    LAUNCH(SRN_CAT_GEMM_WGRAD, k_conv_wgrad, c->total[P_WGRAD], SIMT_THREADS, g.d, c->prefix[P_WGRAD], np, nb, I);
+                }
+                h->cur = lane;
+            }
             if (g.tc) {
-                const int BNf = TC_BN[g.cfgF], BNc = TC_BN[g.cfgC];
-                if (g.tc == 1) LAUNCH_TC(SRN_CAT_GEMM_WGRAD, TC_WGRAD, false, P_WGRAD, BNf);
-                else LAUNCH_TC(SRN_CAT_GEMM_WGRAD, TC_WGRAD, true, P_WGRAD, BNf);
-                LAUNCH_TC(SRN_CAT_GEMM_DGRAD, TC_DGRAD, false, P_DGRAD, BNc);
+                LAUNCH_TC(SRN_CAT_GEMM_DGRAD, TC_DGRAD, false, P_DGRAD, TC_BN[g.cfgC]);
                 break;
             }
-            LAUNCH(SRN_CAT_GEMM_WGRAD, k_conv_wgrad, c->total[P_WGRAD], SIMT_THREADS, g.d, c->prefix[P_WGRAD], np, nb, I);
             if (g.cfgC == 0) launch_dgrad_cfg<0>(h, g, c, nb);
             else if (g.cfgC == 1) launch_dgrad_cfg<1>(h, g, c, nb);
             else launch_dgrad_cfg<2>(h, g, c, nb);
@@ -1224,6 +1255,12 @@ static int backward_pass(srn_engine* h, int nb, const Inputs& I) {
         for (Group* g : later) { rc = bwd_group(h, *g, nb, I); if (rc) return rc; }    // accumulation order matters
         gi = ge;
     }
+    for (int w = 0; w < srn_engine::NWG; ++w)      // every weight gradient is in before the optimiser (and the next batch) starts
+        if (h->wg_used[w]) {
+            cudaEventRecord(h->ev_wg_done[w], h->wg_stream[w]);
+            cudaStreamWaitEvent(h->stream, h->ev_wg_done[w], 0);
+            h->wg_used[w] = false;
+        }
     return SRN_OK;
 }
 
