@@ -88,7 +88,7 @@ struct Indiv {
 struct Cached {
     int* prefix[P_COUNT] = {};
     int total[P_COUNT] = {};
-    TcTile* tiles[P_COUNT] = {};   // tensor-core passes: one 256-byte descriptor per tile, heaviest first
+    TcTile* tiles[P_COUNT] = {};   // tensor-core passes: one descriptor per tile, heaviest first
 };
 
 struct Group {

@@ -382,7 +382,6 @@ static __global__ void __launch_bounds__(TC_THREADS, (BN <= 128 ? 2 : 1))
 k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int l8 = lane & 7, lq = lane >> 3;              // row inside a core matrix, chunk inside a quad
     const uint32_t sraw = smem_u32(smem_raw);
     const uint32_t sbase = sraw;
     if (sraw & 1023u) __trap();                           // swizzle-128B atoms need 1024-byte alignment (the dynamic window starts on one)
@@ -405,7 +404,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
     const int G = gridDim.x, cta = blockIdx.x;
     int my_tiles = ntiles / G;                                      // full rounds, plus maybe one of the last round
     if (tc_tile_index(cta, my_tiles, G) < ntiles) ++my_tiles;
-    // 256-byte descriptors travel global -> registers (one tile early) -> ring slot j % TC_RING, 16 bytes per thread
+    // tile descriptors travel global -> registers (one tile early) -> ring slot j % TC_RING, 16 bytes per thread
     // of the first half-warp; the load of the next one is in flight while the current tile is being gathered
     uint4 dreg = make_uint4(0, 0, 0, 0);
     auto desc_load = [&](int j) {
