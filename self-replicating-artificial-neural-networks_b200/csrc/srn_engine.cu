@@ -666,6 +666,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
                     s2.H = e.Ho * e.Wo; s2.W = 1; s2.C = e.KK; s2.Cs = e.Kp; s2.Ho = s2.H; s2.Wo = 1;
                     s2.kh = s2.kw = s2.sh = s2.sw = 1;
                     s2.coff = gi;                            // geometry index, used for the fix-up
+                    s2.Cj = e.KK < e.Kp ? 1 : 0;             // the matrix has a ones column: bias gradient from the weight-gradient GEMM
                     const int cF = tc_cfg_for(s2.F), cC = tc_cfg_for(s2.C);
                     auto key2 = std::make_tuple(to.depth, kind, cF + 16 * 1 + 64 * 1, cC, ordinal);
                     Group& g2 = gmap[key2];

@@ -951,7 +951,11 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                 float* grow = nullptr;
                 if (mrow < T.Mrows) {
                     if (SCALAR_A) grow = p.gw + (long long)mrow * p.ldw;
-                    else { const int ij = fdiv(mrow, T.fd_c), cp = mrow - ij * Cs; if (cp < p.C) grow = p.gw + ((long long)ij * p.C + cp) * p.ldw; }
+                    else {
+                        const int ij = fdiv(mrow, T.fd_c), cp = mrow - ij * Cs;
+                        if (cp < p.C) grow = p.gw + ((long long)ij * p.C + cp) * p.ldw;
+                        else if (p.Cj == 1 && mrow == p.C) grow = p.gb;       // ones column of the shared im2col matrix: the bias gradient
+                    }
                 }
                 const bool single = (nb * p.Ho * p.Wo) <= TC_WGRAD_ROWS;     // one split: plain stores, else fp32 atomics
                 for (int cb = 0; cb < T.n_umma; cb += 16) {

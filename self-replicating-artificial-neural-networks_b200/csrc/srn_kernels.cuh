@@ -59,6 +59,10 @@ k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
     __shared__ float sm[COL_THREADS * 8];
     const int pi = find_prob(prefix, nprob, blockIdx.x);
     const Prob p = probs[pi];
+    // first layers over the shared im2col matrix get their bias gradient from the weight-gradient GEMM (Cj == 1 marks
+    // the ones column): a linear layer has nothing to do here, an activation still needs its mask applied
+    const bool bias_here = K1 || p.Cj != 1;
+    if (!bias_here && p.act == 0) return;
     const int chunk = blockIdx.x - prefix[pi];
     const int F = p.F, Fs = p.Fs;
     const ColGeom g = col_geom(Fs);
@@ -108,7 +112,7 @@ k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
             if (active)
                 for (int j = 0; j < g.cw; ++j) {
                     const int f = cq * g.cw + j;
-                    if (f < F && s[j] != 0.f) atomicAdd(&p.gb[f], s[j]);
+                    if (bias_here && f < F && s[j] != 0.f) atomicAdd(&p.gb[f], s[j]);
                     if (K1 && f < F && sx[j] != 0.f) atomicAdd(&p.gw[f], sx[j]);
                 }
         } else {
@@ -117,7 +121,7 @@ k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
             __syncthreads();
             for (int ch = tid; ch < g.nq * g.cw; ch += COL_THREADS) {
                 const float t = col_block_sum(sm, g, ch);
-                if (ch < F && t != 0.f) atomicAdd(&p.gb[ch], t);
+                if (bias_here && ch < F && t != 0.f) atomicAdd(&p.gb[ch], t);
             }
             __syncthreads();
             if (K1) {
@@ -791,7 +795,9 @@ k_im2col(Im2colGeo g, int nb) {
     int ki = k0 / g.kw, kj = k0 - ki * g.kw;
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-        v.v[e] = (k0 + e < g.KK) ? src[ki * g.W + kj] : __float2half_rn(0.f);
+        // column KK (the first pad column, when there is one) holds 1: the weight-gradient GEMM over this matrix then
+        // yields the bias gradient in its row KK, and the forward pass is unaffected (there is no kernel row KK)
+        v.v[e] = (k0 + e < g.KK) ? src[ki * g.W + kj] : __float2half_rn(k0 + e == g.KK ? 1.f : 0.f);
         if (++kj == g.kw) { kj = 0; ++ki; }
     }
     st8(g.out + pos * g.Kp + k0, v);
