@@ -11,6 +11,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <map>
 #include <random>
 #include <string>
@@ -89,6 +90,7 @@ struct Cached {
     int* prefix[P_COUNT] = {};
     int total[P_COUNT] = {};
     TcTile* tiles[P_COUNT] = {};   // tensor-core passes: one descriptor per tile, heaviest first
+    std::vector<TcTile> host_fwd;  // forward tiles kept on the host for the per-level merged tables
 };
 
 struct Group {
@@ -154,6 +156,9 @@ struct srn_engine {
     // metric buffers
     int* met_correct = nullptr; float* met_ce = nullptr; float* met_mse = nullptr; long long met_slots = 0;
     std::vector<int*> scratch_prefix;   // all cached prefix arrays, for cleanup
+    // forward launches of one depth level that run the same kernel (same N tile) share one tile table: key (nb, depth, BN, mode)
+    struct MergedFwd { TcTile* dev = nullptr; int total = 0; int first_group = -1; };
+    std::map<std::tuple<int, int, int, int>, MergedFwd> merged_fwd;
 };
 
 #define CK(call)                                                                                   \
@@ -206,6 +211,7 @@ static void free_population(srn_engine* h) {
     for (auto& g : h->groups) { cudaFree(g.d); cudaFree(g.done); }
     for (int* p : h->scratch_prefix) cudaFree(p);
     h->scratch_prefix.clear();
+    h->merged_fwd.clear();
     h->groups.clear();
     h->inds.clear();
     cudaFree(h->d_loss); h->d_loss = nullptr;
@@ -1038,6 +1044,7 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
             CK(cudaMemcpy(dt, tt.data(), tt.size() * sizeof(TcTile), cudaMemcpyHostToDevice));
             h->scratch_prefix.push_back(reinterpret_cast<int*>(dt));
             c.tiles[pass] = dt;
+            if (pass == P_FWD && g.tc == 1) c.host_fwd = tt;
         }
     }
     g.cache[nb] = c;
@@ -1091,6 +1098,28 @@ static int run_level(srn_engine* h, std::vector<Group*>& level, F&& body) {
         h->cur = lane == 0 ? h->stream : h->side[lane - 1];
         if (lane) used[lane - 1] = true;
         rc = body(*level[k]);
+    }
+    h->cur = h->stream;
+    for (int i = 0; i < srn_engine::NSIDE; ++i)
+        if (used[i]) { cudaEventRecord(h->ev_join[i], h->side[i]); cudaStreamWaitEvent(h->stream, h->ev_join[i], 0); }
+    return rc;
+}
+
+// same fan-out for arbitrary launch closures
+static int run_tasks(srn_engine* h, std::vector<std::function<int()>>& tasks) {
+    if (tasks.empty()) return SRN_OK;
+    const bool fan = h->multi_stream && tasks.size() > 1;
+    if (fan) {
+        cudaEventRecord(h->ev_fork, h->stream);
+        for (int i = 0; i < srn_engine::NSIDE; ++i) cudaStreamWaitEvent(h->side[i], h->ev_fork, 0);
+    }
+    bool used[srn_engine::NSIDE] = {};
+    int rc = SRN_OK;
+    for (size_t k = 0; k < tasks.size() && !rc; ++k) {
+        const int lane = fan ? (int)(k % (srn_engine::NSIDE + 1)) : 0;
+        h->cur = lane == 0 ? h->stream : h->side[lane - 1];
+        if (lane) used[lane - 1] = true;
+        rc = tasks[k]();
     }
     h->cur = h->stream;
     for (int i = 0; i < srn_engine::NSIDE; ++i)
@@ -1179,7 +1208,56 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
             if (h->groups[ge].mode & mode) level.push_back(&h->groups[ge]);
             ++ge;
         }
-        int rc = run_level(h, level, [&](Group& g) { return fwd_group(h, g, nb, I, training); });
+        static const bool merge = getenv("SRN_NO_MERGE_FWD") == nullptr;
+        int rc = SRN_OK;
+        if (!merge) {
+            rc = run_level(h, level, [&](Group& g) { return fwd_group(h, g, nb, I, training); });
+        } else {
+            // tensor-core GEMM buckets with the same N tile run the same kernel: one launch over their joined tile tables
+            std::vector<std::function<int()>> tasks;
+            std::vector<Group*> by_bn[4];
+            for (Group* g : level) {
+                if ((g->kind == SRN_KIND_DENSE || g->kind == SRN_KIND_CONV) && g->tc == 1) by_bn[g->cfgF].push_back(g);
+                else tasks.push_back([=, &I]() { return fwd_group(h, *g, nb, I, training); });
+            }
+            for (int b = 0; b < 4; ++b) {
+                if (by_bn[b].empty()) continue;
+                if (by_bn[b].size() == 1) { Group* g = by_bn[b][0]; tasks.push_back([=, &I]() { return fwd_group(h, *g, nb, I, training); }); continue; }
+                auto key = std::make_tuple(nb, by_bn[b][0]->depth, b, mode);
+                auto it = h->merged_fwd.find(key);
+                if (it == h->merged_fwd.end()) {
+                    std::vector<TcTile> all;
+                    for (Group* g : by_bn[b]) {
+                        Cached* c; rc = plan_for(h, *g, nb, &c); if (rc) return rc;
+                        all.insert(all.end(), c->host_fwd.begin(), c->host_fwd.end());
+                    }
+                    std::stable_sort(all.begin(), all.end(), [](const TcTile& x, const TcTile& y) { return x.nk * x.nsub > y.nk * y.nsub; });
+                    srn_engine::MergedFwd m;
+                    m.total = (int)all.size();
+                    m.first_group = (int)(by_bn[b][0] - h->groups.data());
+                    if (m.total) {
+                        CK(cudaMalloc(&m.dev, all.size() * sizeof(TcTile)));
+                        CK(cudaMemcpy(m.dev, all.data(), all.size() * sizeof(TcTile), cudaMemcpyHostToDevice));
+                        h->scratch_prefix.push_back(reinterpret_cast<int*>(m.dev));
+                    }
+                    it = h->merged_fwd.emplace(key, m).first;
+                }
+                const srn_engine::MergedFwd m = it->second;
+                if (!m.total) continue;
+                const int BN = TC_BN[b];
+                tasks.push_back([=, &I]() {
+                    h->cur_group = m.first_group;
+                    switch (BN) {
+                        case 32: LAUNCH_SMEM(SRN_CAT_GEMM_FWD, (k_gemm_tc<TC_FWD, false, 32>), tc_grid(h, m.total, 32), TC_THREADS, tc_smem_bytes(32), m.dev, m.total, nb, I); break;
+                        case 64: LAUNCH_SMEM(SRN_CAT_GEMM_FWD, (k_gemm_tc<TC_FWD, false, 64>), tc_grid(h, m.total, 64), TC_THREADS, tc_smem_bytes(64), m.dev, m.total, nb, I); break;
+                        case 128: LAUNCH_SMEM(SRN_CAT_GEMM_FWD, (k_gemm_tc<TC_FWD, false, 128>), tc_grid(h, m.total, 128), TC_THREADS, tc_smem_bytes(128), m.dev, m.total, nb, I); break;
+                        default: LAUNCH_SMEM(SRN_CAT_GEMM_FWD, (k_gemm_tc<TC_FWD, false, 256>), tc_grid(h, m.total, 256), TC_THREADS, tc_smem_bytes(256), m.dev, m.total, nb, I); break;
+                    }
+                    return (int)SRN_OK;
+                });
+            }
+            rc = run_tasks(h, tasks);
+        }
         if (rc) return rc;
         gi = ge;
     }
