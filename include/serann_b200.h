@@ -196,9 +196,12 @@ int srn_bn_train_forward(int32_t device, const uint16_t* x, int64_t rows, int32_
  * storage (per-channel statistics, per-block partial sums, the launch descriptor) is a fixed array of
  * SRN_NOALLOC_SCRATCH_BYTES that is part of the library image - every GPU that loads the library holds
  * those bytes until the process exits.
- *   - All d_* pointers are DEVICE pointers that the caller allocated; d_moving_variance must be
- *     d_moving_mean + C (one [2][C] fp16 array).  `stream` is a cudaStream_t (NULL = default stream);
- *     the call returns after the stream has finished the work.
+ *   - All d_* pointers are DEVICE pointers on `device` that the caller allocated; d_moving_variance must be
+ *     d_moving_mean + C (one [2][C] fp16 array).  When C is a multiple of 8 the kernels move 16-byte groups of
+ *     8 channels, so d_x and d_y must then be 16-byte aligned (a slice of a larger tensor that starts at an
+ *     odd element offset is refused with SRN_ERR_ARG instead of faulting inside the caller's CUDA context).
+ *     `stream` is a cudaStream_t created on `device` (NULL = that device's default stream); the call returns
+ *     after the stream has finished the work and leaves the calling thread's current device as it found it.
  *   - Limit: C * (4 + 2 * ceil(rows / R)) floats must fit in SRN_NOALLOC_SCRATCH_BYTES - 512, where R is the
  *     number of rows one thread block reduces: R = 16 * max(1, 256 / n) with n = C / 8 when C is a multiple
  *     of 8, else n = C (e.g. 750*784 rows x 128 channels fits; 16M rows x 64 channels does not).  Larger

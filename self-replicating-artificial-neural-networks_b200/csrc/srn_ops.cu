@@ -1,5 +1,6 @@
 // Stand-alone entry points: ribosomal-autoencoder decode, genotype readout, BatchNormalizationF16 forward.
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstddef>
 #include <vector>
@@ -292,7 +293,10 @@ static_assert(sizeof(Prob) + 8 * sizeof(int) <= NOALLOC_HEADER_BYTES, "descripto
 static __device__ __align__(256) unsigned char g_noalloc_scratch[SRN_NOALLOC_SCRATCH_BYTES];
 
 constexpr int NOALLOC_MAX_DEVICES = 64;
-static unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};      // device address of the array, per device
+// device address of the array, per device; written once per device (atomically: two host threads may make the first
+// call at the same time and would store the same value).  cudaDeviceReset invalidates it - a process that resets a
+// device must not call this entry point on that device afterwards.
+static std::atomic<unsigned char*> g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
 
 extern "C" int srn_bn_train_forward_noalloc(int32_t device, void* stream, const uint16_t* d_x, int64_t rows, int32_t C,
                                             const uint16_t* d_gamma, const uint16_t* d_beta,
@@ -303,23 +307,36 @@ extern "C" int srn_bn_train_forward_noalloc(int32_t device, void* stream, const 
     if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(SRN_ERR_ARG, "srn_bn_train_forward_noalloc: device %d", device);
     if (d_moving_variance != d_moving_mean + C)
         return fail(SRN_ERR_ARG, "srn_bn_train_forward_noalloc: moving_variance must directly follow moving_mean (one [2][C] array)");
+    // With C a multiple of 8 the kernels move 16-byte groups of 8 channels; a buffer that starts at an odd element
+    // offset (a slice of a framework tensor) would fault there and poison the caller's CUDA context, so it is refused.
+    if (C % 8 == 0 && ((reinterpret_cast<uintptr_t>(d_x) | reinterpret_cast<uintptr_t>(d_y)) & 15u) != 0)
+        return fail(SRN_ERR_ARG, "srn_bn_train_forward_noalloc: with C a multiple of 8, d_x and d_y must be 16-byte aligned");
+    if (((reinterpret_cast<uintptr_t>(d_x) | reinterpret_cast<uintptr_t>(d_y) | reinterpret_cast<uintptr_t>(d_gamma) |
+          reinterpret_cast<uintptr_t>(d_beta) | reinterpret_cast<uintptr_t>(d_moving_mean)) & 1u) != 0)
+        return fail(SRN_ERR_ARG, "srn_bn_train_forward_noalloc: fp16 buffers must be 2-byte aligned");
     const int chunks = col_chunks(rows, C);
     const size_t need = 4 * (size_t)C + 2 * (size_t)C * chunks;
     if (need > NOALLOC_FLOATS)
         return fail(SRN_ERR_LIMIT, "srn_bn_train_forward_noalloc: C * (4 + 2 * ceil(rows / %d)) = %zu floats exceeds the built-in "
                     "scratch of %zu floats (%zu bytes); use srn_bn_train_forward for this size", col_geom(C).rows_per_cta, need,
                     NOALLOC_FLOATS, (size_t)SRN_NOALLOC_SCRATCH_BYTES);
+    // the caller's current device is put back before returning, whatever happens below
+    struct DeviceGuard {
+        int prev = -1;
+        DeviceGuard() { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; }
+        ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    } guard;
     int rc = check_device(device);
     if (rc) return rc;
-    if (!g_noalloc_ptr[device]) {
+    if (!g_noalloc_ptr[device].load(std::memory_order_acquire)) {
         // In host code the array's name is only a handle for the runtime; the address kernels can use comes from
         // cudaGetSymbolAddress, asked once per device while that device is current.
         void* p = nullptr;
         cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
         if (e != cudaSuccess || !p) return fail(SRN_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch) on device %d: %s", device, cudaGetErrorString(e));
-        g_noalloc_ptr[device] = static_cast<unsigned char*>(p);
+        g_noalloc_ptr[device].store(static_cast<unsigned char*>(p), std::memory_order_release);
     }
-    unsigned char* base = g_noalloc_ptr[device];
+    unsigned char* base = g_noalloc_ptr[device].load(std::memory_order_acquire);
     Prob* d_prob = reinterpret_cast<Prob*>(base);
     int* d_prefix = reinterpret_cast<int*>(base + sizeof(Prob));
     float* d_save = reinterpret_cast<float*>(base + NOALLOC_HEADER_BYTES);

@@ -16,7 +16,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def _run_noalloc(lib, x, gamma, beta, mm, mv):
+def _run_noalloc(lib, x, gamma, beta, mm, mv, stream=None):
     import torch
     dev = torch.device('cuda', 0)
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.int16)).to(dev)
@@ -25,7 +25,7 @@ def _run_noalloc(lib, x, gamma, beta, mm, mv):
     d_y = torch.empty_like(d_x)
     torch.cuda.synchronize()
     rows, ch = x.shape
-    rc = lib.srn_bn_train_forward_noalloc(0, None, d_x.data_ptr(), rows, ch, d_g.data_ptr(), d_b.data_ptr(),
+    rc = lib.srn_bn_train_forward_noalloc(0, stream, d_x.data_ptr(), rows, ch, d_g.data_ptr(), d_b.data_ptr(),
                                           d_mov.data_ptr(), d_mov.data_ptr() + 2 * ch, d_y.data_ptr())
     assert rc == 0, lib.srn_last_error().decode()
     y = d_y.cpu().numpy().view(np.float16)
@@ -50,6 +50,52 @@ def test_noalloc_matches_allocating_entry_point_twice_in_a_row():
         assert float(np.abs(y.astype(np.float32) - y_ref.astype(np.float32)).max()) <= 2e-3 * scale
         assert np.array_equal(y, y_ref)
         assert np.array_equal(mm2, mm_ref) and np.array_equal(mv2, mv_ref)
+        # and against the CPU oracle directly, so that this file is a parity test in its own right
+        import torch
+        from oracle import serann_oracle as O
+        t = lambda a: torch.tensor(a.astype(np.float32))
+        tm, tv = t(mm), t(mv)
+        ref = O._bn_train(t(x), t(gamma), t(beta), tm, tv).numpy()
+        assert float(np.abs(y.astype(np.float32) - ref).max()) <= 2e-3 * float(np.abs(ref).max())
+        assert np.allclose(mm2.astype(np.float32), tm.numpy(), rtol=2e-3, atol=1e-4)
+        assert np.allclose(mv2.astype(np.float32), tv.numpy(), rtol=2e-3, atol=1e-4)
+
+
+def test_noalloc_on_a_caller_stream_and_current_device_untouched():
+    """A caller inside a framework passes the framework's own stream; the call must run there and must not
+    change which device is current for the calling thread."""
+    import torch
+    from serann_b200.engine import bn_train_forward, load_library
+    lib = load_library()
+    r = np.random.default_rng(5)
+    x = r.standard_normal((3000, 16)).astype(np.float16)
+    gamma, beta = np.ones(16, np.float16), np.zeros(16, np.float16)
+    mm, mv = np.zeros(16, np.float16), np.ones(16, np.float16)
+    y_ref, mm_ref, mv_ref = bn_train_forward(x, gamma, beta, mm, mv)
+    st = torch.cuda.Stream(device=0)
+    before = torch.cuda.current_device()
+    y, mm2, mv2 = _run_noalloc(lib, x, gamma, beta, mm, mv, stream=C.c_void_p(st.cuda_stream))
+    assert torch.cuda.current_device() == before
+    assert np.array_equal(y, y_ref) and np.array_equal(mm2, mm_ref) and np.array_equal(mv2, mv_ref)
+
+
+def test_noalloc_refuses_a_misaligned_tensor_slice():
+    """With C % 8 == 0 the kernels use 16-byte accesses: a view that starts at an odd element offset is turned
+    down with SRN_ERR_ARG before any kernel runs (a fault would poison the caller's CUDA context)."""
+    import torch
+    from serann_b200.engine import load_library
+    lib = load_library()
+    buf = torch.zeros(4096, dtype=torch.int16, device='cuda')
+    par = torch.zeros(64, dtype=torch.int16, device='cuda')
+    p = buf.data_ptr()
+    rc = lib.srn_bn_train_forward_noalloc(0, None, p + 2, 64, 16, par.data_ptr(), par.data_ptr(), par.data_ptr(),
+                                          par.data_ptr() + 32, p + 2048)
+    assert rc == -1 and b'16-byte aligned' in lib.srn_last_error()
+    # C not a multiple of 8 runs the scalar path: the same offset is fine there
+    rc = lib.srn_bn_train_forward_noalloc(0, None, p + 2, 64, 7, par.data_ptr(), par.data_ptr(), par.data_ptr(),
+                                          par.data_ptr() + 14, p + 2048)
+    assert rc == 0, lib.srn_last_error().decode()
+    torch.cuda.synchronize()
 
 
 def test_noalloc_rejects_sizes_beyond_the_builtin_scratch():
