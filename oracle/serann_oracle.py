@@ -90,6 +90,35 @@ class _SigmoidQ(torch.autograd.Function):
 sigmoid_q = _SigmoidQ.apply
 
 
+class _SqDiffQ(torch.autograd.Function):
+    """tf.math.squared_difference in fp16 with TF's registered gradient ``scalar_mul(2.0, grad) * (x - y)``, each op
+    rounding to fp16 [TF2.6 math_grad._SquaredDifferenceGrad]."""
+
+    @staticmethod
+    def forward(ctx, x, y):
+        ctx.save_for_backward(x, y)
+        return ((x - y) ** 2).half().float()
+
+    @staticmethod
+    def backward(ctx, g):
+        x, y = ctx.saved_tensors
+        g2 = (2.0 * g.half().float()).half().float()
+        d = (x - y).half().float()
+        return (g2 * d).half().float(), None
+
+
+def _first_argmax(a: torch.Tensor) -> torch.Tensor:
+    """argmax over the last axis, first maximum wins; an all-NaN row gives 0 (as tf.argmax)."""
+    a = a.float()
+    best = a[:, 0].clone()
+    arg = torch.zeros(a.shape[0], dtype=torch.long)
+    for j in range(1, a.shape[1]):
+        better = a[:, j] > best
+        best = torch.where(better, a[:, j], best)
+        arg = torch.where(better, torch.full_like(arg, j), arg)
+    return arg
+
+
 class _MaxPoolFirst(torch.autograd.Function):
     """Max pooling whose gradient goes to the first maximum of each window in row-major scan order
     and is summed per input element in window order [TF2.6: MaxPoolGrad tie rule unverified]."""
@@ -216,19 +245,77 @@ def _bn_scale_shift(mean16, var16, gamma, beta):
     return inv, shift
 
 
-def _bn_train(x, gamma, beta, mov_mean, mov_var):
-    """BatchNormalizationF16.call, training branch (BatchNormalizationF16.py:130-153).
+class _BNTrainCentered(torch.autograd.Function):
+    """Training-mode normalisation with the gradient in its centred closed form
 
-    moments in fp32 for fp16 input then cast back [TF2.6]; the value fed to the
-    moving variance is var * n / (n - (1 + eps)) with n cast to fp16 first, which
-    is inf/inf = NaN once B * spatial > 65504.
-    """
+        dx = inv (dy - mean(dy)) - (x - mean32) gamma inv_raw^3 mean(dy (x - mean16)),  dgamma = inv_raw sum dy (x - mean16),
+        dbeta = sum dy
+
+    (reductions in fp32, one rounding of dx at the producer's boundary).  This is what differentiating the forward
+    graph gives - the variance is taken around the fp32 mean, the shift uses the fp16 mean - but with the two terms
+    of d inv = sum(dy x) - mean16 sum(dy) combined before any rounding.  TF's op-by-op graph (and ``_bn_train_graph``
+    below) rounds sum(dy) to fp16 first and multiplies by mean16 afterwards, which on channels whose spread is small
+    against the fp16 spacing of their mean (|mean| / std in the hundreds: features of near-constant inputs) leaves
+    cancellation noise of relative size 2^-11 |mean| / std in every upstream gradient.  The kernels and this oracle use
+    the centred form; the deviation from the TF graph is documented in DESIGN.md section 2 and measured in
+    tests/test_oracle_numpy.py."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta):
+        dims = tuple(range(x.dim() - 1))
+        n = 1
+        for d in dims:
+            n *= x.shape[d]
+        mean32 = x.mean(dims)
+        var32 = ((x - mean32) ** 2).mean(dims)
+        mean16, var16 = f16(mean32), f16(var32)
+        inv_raw = f16(torch.rsqrt(f16(var16 + f16(BN_EPS))))
+        inv = f16(inv_raw * gamma)
+        shift = f16(beta - f16(mean16 * inv))
+        y = f16(f16(x * inv) + shift)
+        ctx.save_for_backward(x, mean32, mean16, inv_raw, inv, gamma)
+        ctx.n = n
+        ctx.mark_non_differentiable(mean16, var16)
+        return y, mean16, var16
+
+    @staticmethod
+    def backward(ctx, gy, _gm, _gv):
+        x, mean32, mean16, inv_raw, inv, gamma = ctx.saved_tensors
+        dims = tuple(range(x.dim() - 1))
+        g = gy.half().float()
+        s1 = g.double().sum(dims)
+        s2 = (g.double() * (x.double() - mean16.double())).sum(dims)
+        coef = gamma.double() * inv_raw.double() ** 3 * s2 / ctx.n
+        dx = inv.double() * (g.double() - s1 / ctx.n) - (x.double() - mean32.double()) * coef
+        return dx.float(), (s2 * inv_raw.double()).float(), s1.float()
+
+
+def _bn_train_graph(x, gamma, beta):
+    """The same forward as a plain autograd graph (TF's op structure with one rounding per tensor boundary): kept for
+    the cross-check against the NumPy op-by-op restatement."""
     dims = tuple(range(x.dim() - 1))
     mean32 = x.mean(dims)
     var32 = ((x - mean32.detach()) ** 2).mean(dims)
     mean16, var16 = q(mean32), q(var32)
     inv, shift = _bn_scale_shift(mean16, var16, gamma, beta)
-    y = q(q(x * inv) + shift)
+    return q(q(x * inv) + shift), mean16.detach(), var16.detach()
+
+
+BN_BACKWARD = 'centered'        # 'graph' differentiates the op graph instead (see _BNTrainCentered)
+
+
+def _bn_train(x, gamma, beta, mov_mean, mov_var):
+    """BatchNormalizationF16.call, training branch (BatchNormalizationF16.py:130-153).
+
+    moments in fp32 for fp16 input then cast back [TF2.6]; the value fed to the
+    moving variance is var * n / (n - (1 + eps)) with n cast to fp16 first, which
+    is inf/inf = NaN once B * spatial >= 65520.
+    """
+    dims = tuple(range(x.dim() - 1))
+    if BN_BACKWARD == 'centered':
+        y, mean16, var16 = _BNTrainCentered.apply(x, gamma, beta)
+    else:
+        y, mean16, var16 = _bn_train_graph(x, gamma, beta)
     with torch.no_grad():
         n = 1
         for d in dims:
@@ -236,9 +323,13 @@ def _bn_train(x, gamma, beta, mov_mean, mov_var):
         n16 = f16(float(n))                                          # inf above 65504
         bessel = f16(n16 / f16(n16 - f16(1.0 + BN_EPS)))             # NaN when n16 is inf
         var_unbiased = f16(var16 * bessel)
-        decay = f16(1.0 - BN_MOMENTUM)                               # 0.01000213623046875
-        mov_mean.copy_(f16(mov_mean - f16(f16(mov_mean - mean16) * decay)))
-        mov_var.copy_(f16(mov_var - f16(f16(mov_var - var_unbiased) * decay)))
+        # [TF2.6] keras/backend.py moving_average_update, TF2 branch: x.assign(x * momentum + value * (1 - momentum))
+        # with momentum cast to the variable's dtype (fp16(0.99) = 0.990234375, 1 - that = 0.009765625 exactly).  TF <= 2.4
+        # used assign_sub((x - value) * (1 - momentum)) instead; the two differ in decay and in rounding order.
+        mom = f16(BN_MOMENTUM)
+        one_minus = f16(1.0 - mom)
+        mov_mean.copy_(f16(f16(mov_mean * mom) + f16(mean16 * one_minus)))
+        mov_var.copy_(f16(f16(mov_var * mom) + f16(var_unbiased * one_minus)))
     return y
 
 
@@ -284,8 +375,14 @@ def losses(logits: torch.Tensor, labels: torch.Tensor, bits: torch.Tensor, n_cla
     zc, zr = logits[:, :n_classes], logits[:, n_classes:]
     ce = q(torch.logsumexp(zc, dim=1) - zc.gather(1, labels[:, None]).squeeze(1))
     s = sigmoid_q(zr)
-    mse = q((q((s - bits) ** 2)).mean(dim=1))
-    correct = (zc.argmax(dim=1) == labels)            # first maximum wins, as tf.argmax
+    mse = q(_SqDiffQ.apply(s, bits).mean(dim=1))
+    # categorical_accuracy compares argmax(y_true) with argmax(y_pred) where y_pred is the model's fp16 softmax
+    # OUTPUT [TF2.6 keras/metrics.py]: near-equal top probabilities can round to a tie, the first index wins
+    with torch.no_grad():
+        zmax = zc.max(dim=1, keepdim=True).values
+        e = torch.exp(zc - zmax)
+        y_pred = (e / e.sum(dim=1, keepdim=True)).half()
+        correct = (_first_argmax(y_pred) == labels)
     return ce, mse, correct, s
 
 

@@ -1473,6 +1473,9 @@ extern "C" int srn_fit(srn_engine* h, int32_t epochs, int32_t batch, int32_t n_v
     float ms_total = 0.f;
     int steps_done = 0;
     bool stop = false;
+    // gradient accumulators start at zero (a debug step without the optimiser leaves its sums behind)
+    wait_adam(h);
+    CK(cudaMemsetAsync(h->Gr, 0, (size_t)h->p_elems * sizeof(float), h->stream));
     // warm the launch plans outside the timed region
     for (auto& g : h->groups) { Cached* c; rc = plan_for(h, g, batch, &c); if (rc) { cudaFree(d_perm); return rc; } }
     for (int e = 0; e < epochs && !stop; ++e) {

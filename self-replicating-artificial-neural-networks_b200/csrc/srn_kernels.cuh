@@ -139,10 +139,11 @@ k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
 }
 
 // ------------------------------------------------------------------ BatchNormalizationF16
-// save layout per problem: [0][Cs] mean16, [1][Cs] inv_raw (rsqrt(var16 + eps), fp16-valued), [2][Cs] inv
+// save layout per problem: [0][Cs] mean32 (the fp32 batch mean; mean16 = its fp16 rounding), [1][Cs] inv_raw (rsqrt(var16 + eps), fp16-valued), [2][Cs] inv
 // (times gamma), [3][Cs] shift; then partial sums [chunks][Cs][2].
 constexpr float BN_EPS16 = 0.0010004043579101562f;       // fp16(1e-3)
-constexpr float BN_DECAY16 = 0.01000213623046875f;        // fp16(1 - 0.99)
+constexpr float BN_MOM16 = 0.990234375f;                  // fp16(0.99): tf.cast(momentum, fp16)
+constexpr float BN_ONE_MINUS_MOM16 = 0.009765625f;        // 1 - fp16(0.99), exact in fp16
 constexpr float BN_ONE_EPS16 = 1.0009765625f;             // fp16(1 + 1e-3)
 
 // forward: shifted sums (x - x0), (x - x0)^2 around the first row; backward: sum dy, sum dy * (x - mean16)
@@ -172,7 +173,7 @@ k_bn_partial(const Prob* __restrict__ probs, const int* __restrict__ prefix, int
         float s1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, s2[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (active) {
             float pivot[8];
-            for (int j = 0; j < g.cw; ++j) pivot[j] = bwd ? p.save[cq * g.cw + j] : __half2float(in[cq * g.cw + j]);
+            for (int j = 0; j < g.cw; ++j) pivot[j] = bwd ? rh(p.save[cq * g.cw + j]) : __half2float(in[cq * g.cw + j]);      // backward: mean16 = fp16(mean32)
             long long r = r0 + rl;
             if (g.cw == 8) {
                 // four rows per trip: the loads of a trip are independent, so four (eight backward) are in flight per thread
@@ -306,14 +307,15 @@ static __device__ void bn_finalize_fwd_dev(const Prob& p, int nb, const Inputs& 
         const float mean16 = rh(mean32), var16 = rh(var32);
         float inv_raw, inv, shift;
         bn_scale_shift(mean16, var16, __half2float(p.w[c]), __half2float(p.bias[c]), inv_raw, inv, shift);
-        p.save[c] = mean16; p.save[Cs + c] = inv_raw; p.save[2 * Cs + c] = inv; p.save[3 * Cs + c] = shift;
+        p.save[c] = mean32; p.save[Cs + c] = inv_raw; p.save[2 * Cs + c] = inv; p.save[3 * Cs + c] = shift;
         // moving statistics: variance * n16 / (n16 - (1 + eps)) with n cast to fp16 (inf/inf = NaN above 65504)
         const float n16 = rh((float)rows);
         const float bessel = rh(n16 / rh(n16 - BN_ONE_EPS16));
         const float var_unb = rh(var16 * bessel);
         float mm = __half2float(p.mov[c]), mv = __half2float(p.mov[C + c]);
-        mm = rh(mm - rh(rh(mm - mean16) * BN_DECAY16));
-        mv = rh(mv - rh(rh(mv - var_unb) * BN_DECAY16));
+        // keras 2.6 backend.moving_average_update (TF2 branch): x.assign(x * momentum + value * (1 - momentum)), fp16 op by op
+        mm = rh(rh(mm * BN_MOM16) + rh(mean16 * BN_ONE_MINUS_MOM16));
+        mv = rh(rh(mv * BN_MOM16) + rh(var_unb * BN_ONE_MINUS_MOM16));
         p.mov[c] = __float2half_rn(mm);
         p.mov[C + c] = __float2half_rn(mv);
     }
@@ -398,7 +400,10 @@ static __device__ void bn_finalize_bwd_dev(const Prob& p, int nb) {
     }
 }
 
-// dx = inv * (dy - mean(dy)) - (x - mean16) * gamma * inv_raw^3 * mean(dy * (x - mean16))
+// dx = inv * (dy - mean(dy)) - (x - mean32) * gamma * inv_raw^3 * mean(dy * (x - mean16)).
+// The two means differ on purpose: TF's moments() takes the variance around the fp32 mean (its gradient carries
+// x - mean32), while the normalisation y = x * inv + (beta - mean16 * inv) uses the fp16 mean (d inv = sum dy * (x - mean16)).
+// On channels whose spread is small against the fp16 spacing of their mean the difference is a visible share of dx.
 static __global__ void __launch_bounds__(EW_THREADS)
 k_bn_bwd_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, int nprob, int nb, Inputs I) {
     const int pi = find_prob(prefix, nprob, blockIdx.x);
@@ -410,7 +415,7 @@ k_bn_bwd_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
     const long long total = (long long)nb * rps * nq;
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
-    const float* mean16 = p.save;
+    const float* mean32 = p.save;
     const float* inv = p.save + 2 * Cs;
     const float* coef = p.save + 4 * Cs;
     long long q = (long long)blk * EW_PER_CTA + threadIdx.x;
@@ -426,14 +431,14 @@ k_bn_bwd_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const int c = c0 + j;
-                float dx = inv[c] * (__half2float(dy.v[j]) - coef[c * 2]) - (__half2float(x.v[j]) - mean16[c]) * coef[c * 2 + 1];
+                float dx = inv[c] * (__half2float(dy.v[j]) - coef[c * 2]) - (__half2float(x.v[j]) - mean32[c]) * coef[c * 2 + 1];
                 if (c >= p.C) dx = 0.f;
                 if (p.din_acc) dx = rh(dx) + __half2float(d.v[j]);
                 d.v[j] = __float2half_rn(dx);
             }
             st8(p.din + io, d);
         } else {
-            float dx = inv[c0] * (__half2float(p.gout[oo]) - coef[c0 * 2]) - (__half2float(in[io]) - mean16[c0]) * coef[c0 * 2 + 1];
+            float dx = inv[c0] * (__half2float(p.gout[oo]) - coef[c0 * 2]) - (__half2float(in[io]) - mean32[c0]) * coef[c0 * 2 + 1];
             if (p.din_acc) dx = rh(dx) + __half2float(p.din[io]);
             p.din[io] = __float2half_rn(dx);
         }
@@ -839,6 +844,16 @@ k_loss(const Prob* __restrict__ probs, int nprob, int nb, LossArgs a) {
     float se = 0.f;
     for (int j = 0; j < a.ncls; ++j) se += expf(__half2float(z[j]) - zmax);
     const float lse = zmax + logf(se);
+    // categorical_accuracy takes argmax over the model's fp16 softmax OUTPUT: probabilities that round to the same
+    // half tie and the first index wins (an all-NaN row keeps index 0, as tf.argmax does)
+    {
+        float pbest = rh(expf(__half2float(z[0]) - zmax) / se);
+        arg = 0;
+        for (int j = 1; j < a.ncls; ++j) {
+            const float pj = rh(expf(__half2float(z[j]) - zmax) / se);
+            if (pj > pbest) { pbest = pj; arg = j; }
+        }
+    }
     const float ce = rh(lse - __half2float(z[label]));
     // ---- replication: sigmoid + squared error
     const float lb16 = rh(a.loss_balance[p.indiv]);
@@ -852,7 +867,8 @@ k_loss(const Prob* __restrict__ probs, int nprob, int nb, LossArgs a) {
         float d = s - __half2float(t[j]);
         sq_sum += rh(d * d);
         if (a.training) {
-            float dy = 2.f * d * g2;
+            // SquaredDifference's gradient scalar_mul(2, grad) * (x - y) and SigmoidGrad, one rounding per op
+            float dy = rh(rh(2.f * g2) * rh(d));
             float ga = rh(dy * s), gb = rh(1.f - s);
             p.gout[(long long)b * p.out_bs + a.ncls + j] = __float2half_rn(ga * gb);
         }

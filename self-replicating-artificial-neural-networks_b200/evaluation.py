@@ -15,7 +15,9 @@ from typing import Dict, List, Optional
 import numpy as np
 
 from . import engine as _engine
-from .frontend import InvalidSerann, compile_source, is_valid_serann
+import copy
+
+from .frontend import InvalidSerann, compile_cached, is_valid_serann
 from .worker import VALIDATION_SPLIT, _chunks, f16_accuracy, genotype_bits
 
 _LOSS_BALANCE_RE = re.compile(r'loss_balance *= *([0-9]+\.[0-9]+?)(\s|$)')    # serann_evaluation/logic.py:165
@@ -69,8 +71,13 @@ class B200SerannEvaluator:
         """``ast.parse`` + a model build (reference ``logic.py:139-151``)."""
         return is_valid_serann(source_code, **self._kwargs())
 
-    def evaluate(self, genotype, source_code: Optional[str] = None, loss_balance: Optional[float] = None) -> dict:
-        """Reference ``SerannEvaluator.evaluate`` (``logic.py:153-231``)."""
+    def evaluate(self, genotype, source_code: Optional[str] = None, loss_balance: Optional[float] = None,
+                 initial_weights=None, perms=None) -> dict:
+        """Reference ``SerannEvaluator.evaluate`` (``logic.py:153-231``).
+
+        ``initial_weights`` (one Keras-layout weight list per copy) and ``perms`` (row order per epoch) replace the
+        random initialisation and Keras' unseeded shuffle when given - the parity tests feed the same values to the
+        CPU oracle."""
         genotype = np.array(genotype)
         if source_code is None:
             if self._ae is None:
@@ -83,7 +90,7 @@ class B200SerannEvaluator:
                 return empty_result()
             loss_balance = float(m.group(1))
         try:
-            ir = compile_source(source_code, **self._kwargs())
+            ir = copy.copy(compile_cached(source_code, **self._kwargs()))     # the cached IR is shared: do not edit it
         except InvalidSerann:
             # the reference lets the Keras build exception escape here; an invalid source has no offspring either way
             return empty_result()
@@ -92,13 +99,17 @@ class B200SerannEvaluator:
         eng.build([ir] * k, seed=int(self._rng.integers(0, 2 ** 63)))
         n_fit = int(self._n_train * (1.0 - VALIDATION_SPLIT))
         n_val = self._n_train - n_fit
-        res = eng.fit(int(self._params['training_epochs']), self._batch, n_val,
+        if initial_weights is not None:
+            for i, w in enumerate(initial_weights):
+                eng.set_weights(i, w)
+        res = eng.fit(int(self._params['training_epochs']), self._batch, n_val, perms=perms,
                       shuffle_seed=int(self._rng.integers(0, 2 ** 63)))
         val_sizes = _chunks(n_val, self._batch)
         accuracies = [f16_accuracy(res['val_correct'][-1, :, i], val_sizes) for i in range(k)]
         # predict([x_test[:R], genotype repeated R times]) for every copy (logic.py:188-191)
         parents = np.repeat(genotype_bits(genotype)[None], k, axis=0)
         probs, _, _ = eng.replicate(parents, r, image_index=np.tile(np.arange(r), k))
+        self.last_probs = probs
         genotypes = np.round(np.clip(probs.reshape(k * r, -1).astype(np.float32), 0, 1))
         fixed = probabilistic_proofreading(genotype, genotypes, self._params['error_correction_probability'])
         if self._ae is None:
@@ -109,9 +120,12 @@ class B200SerannEvaluator:
             micro: Dict[int, int] = {}
             for j in range(r):
                 s = sources[i * r + j]
-                valid = self._validity_cache.get(s) or int(self.is_valid_serann(s, loss_balance))
+                # the reference's `cache.get(s) or ...` re-validates every cached invalid source (logic.py:216);
+                # a proper lookup gives the same counts without the rebuilds
+                valid = self._validity_cache.get(s)
+                if valid is None:
+                    valid = self._validity_cache[s] = int(self.is_valid_serann(s, loss_balance))
                 micro[valid] = micro.get(valid, 0) + 1
-                self._validity_cache[s] = valid
             survival.append(micro)
             # the reference slices [i : i + R], not [i*R : (i+1)*R] (logic.py:223) - kept for parity
             mutations = np.sum(fixed[i: i + r] != genotype, axis=1)

@@ -440,6 +440,42 @@ def compile_source(source_code: str, image_dims=(28, 28), genotype_size: int = 1
     return ir
 
 
+# Front-end cache keyed by the source string.  The reference rebuilds a Keras model per
+# individual per generation (experiment_worker.py:232-246) and per distinct offspring source for validity
+# (serann_evaluation/logic.py:139-151,216-219); populations are clonal at generation 0 and dominated by a few clones
+# later, so the same string is compiled once.  Entries are the IR or the InvalidSerann that the build raised.
+_COMPILE_CACHE: 'OrderedDict[tuple, object]' = None
+_COMPILE_CACHE_MAX = 1 << 15
+compile_cache_stats = {'hits': 0, 'misses': 0}
+
+
+def compile_cached(source_code: str, image_dims=(28, 28), genotype_size: int = 100, n_classes: int = 10) -> SerannIR:
+    """``compile_source`` memoised by (source, geometry).  The returned IR is shared: treat it as read-only."""
+    global _COMPILE_CACHE
+    if _COMPILE_CACHE is None:
+        from collections import OrderedDict
+        _COMPILE_CACHE = OrderedDict()
+    key = (source_code, tuple(image_dims), int(genotype_size), int(n_classes))
+    hit = _COMPILE_CACHE.get(key)
+    if hit is not None:
+        _COMPILE_CACHE.move_to_end(key)
+        compile_cache_stats['hits'] += 1
+        if isinstance(hit, InvalidSerann):
+            raise hit
+        return hit
+    compile_cache_stats['misses'] += 1
+    try:
+        out = compile_source(source_code, image_dims=image_dims, genotype_size=genotype_size, n_classes=n_classes)
+    except InvalidSerann as e:
+        out = e
+    _COMPILE_CACHE[key] = out
+    if len(_COMPILE_CACHE) > _COMPILE_CACHE_MAX:
+        _COMPILE_CACHE.popitem(last=False)
+    if isinstance(out, InvalidSerann):
+        raise out
+    return out
+
+
 def is_valid_serann(source_code: str, **kwargs) -> bool:
     """Reference ``serann_evaluation/logic.py:139-151``: ``ast.parse`` then a model build."""
     try:
@@ -447,7 +483,7 @@ def is_valid_serann(source_code: str, **kwargs) -> bool:
     except (SyntaxError, ValueError):
         return False
     try:
-        compile_source(source_code, **kwargs)
+        compile_cached(source_code, **kwargs)
         return True
     except InvalidSerann:
         return False

@@ -20,7 +20,7 @@ import numpy as np
 import pandas as pd
 
 from . import engine as _engine
-from .frontend import InvalidSerann, SerannIR, compile_source
+from .frontend import InvalidSerann, SerannIR, compile_cached
 
 VALIDATION_SPLIT = 0.05          # experiment_worker.py:118
 EVALUATE_BATCH = 32              # Keras default batch size of Model.evaluate (experiment_worker.py:87)
@@ -112,7 +112,8 @@ class B200PopulationWorker:
         info = pd.DataFrame(index=seranns_info.index).assign(parameters_count=np.nan, loss_balance=np.nan)
         for serann_id, row in seranns_info.iterrows():
             try:
-                ir = compile_source(row['source_code'], image_dims=tuple(p['classification_image_dimensions']),
+                # memoised by source string: a clonal population compiles one program, not N (row f2)
+                ir = compile_cached(row['source_code'], image_dims=tuple(p['classification_image_dimensions']),
                                     genotype_size=int(p['genotype_size']), n_classes=int(p['num_classification_classes']))
                 _engine.layer_descs(ir)
             except (InvalidSerann, _engine.EngineError):

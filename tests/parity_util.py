@@ -95,6 +95,20 @@ def relerr(a, b):
     return float(d.max() / (np.abs(np.where(np.isnan(b), 0, b)).max() + 1e-12)) if d.size else 0.0
 
 
+def weights_close(x, y):
+    """fp16 Adam divides by eps + sqrt(v) with v often flushed to zero, so a one-ulp gradient difference can move one
+    element by a whole step (<= 1e-3 per step).  Judge the tensor by how many elements are off, not by the worst one:
+    returns (fraction of elements further than 1e-2 of the tensor's scale, mean error relative to the scale)."""
+    x = np.asarray(x, np.float32)
+    y = np.asarray(y, np.float32)
+    both_nan = np.isnan(x) & np.isnan(y)
+    d = np.where(both_nan, 0.0, np.abs(x - y))
+    if np.isnan(d).any():
+        return 1.0, float('inf')
+    scale = float(np.abs(np.where(np.isnan(y), 0, y)).max()) + 1e-6
+    return float((d > 1e-2 * scale).mean()), float(d.mean() / scale)
+
+
 def report(lines):
     path = os.environ.get('SRN_REPORT')
     if path:

@@ -129,11 +129,17 @@ def test_fit_curves_and_metrics(setup):
             for li, (a, b) in enumerate(zip(w_gpu, w_ref)):
                 for which, (x, y) in enumerate(zip(a, b)):
                     # fp16 Adam divides by eps + sqrt(v) with v often flushed to 0, which amplifies one-ulp
-                    # gradient differences; after 6 steps bound the worst element loosely and the mean tightly
-                    e = U.relerr(x, y)
-                    em = float(np.abs(x.astype(np.float32) - y.astype(np.float32)).mean() / (np.abs(y.astype(np.float32)).max() + 1e-12))
-                    lines.append(f'net {i} layer {li} weight {which} after fit relerr max {e:.3e} mean {em:.3e}')
-                    assert e < 0.3 and em < 1e-2, lines[-1]
+                    # gradient differences by a whole step: count the elements further than 1e-2 of the tensor's scale, bound the mean
+                    frac, em = U.weights_close(x, y)
+                    d = float(np.abs(x.astype(np.float32) - y.astype(np.float32)).max())
+                    lines.append(f'net {i} layer {li} weight {which} after fit: max diff {d:.2e} off-fraction {frac:.4f} mean {em:.3e}')
+                    # two correct fp16-Adam runs are at most 2 * steps * lr apart per element (each step moves an element by
+                    # at most about lr, in a direction that is rounding noise where the gradient is); the mean stays tight
+                    bound = 2.2 * (epochs * res['steps_per_epoch']) * 1e-3 + 2e-3 * float(np.abs(y.astype(np.float32)).max())
+                    if which < 2:
+                        assert d <= bound and em < 5e-3, lines[-1]
+                    else:                           # BN moving statistics: averages of the batch moments, no optimiser
+                        assert frac <= 0.03 and em < 5e-3, lines[-1]
         U.report(['== fit =='] + lines)
     finally:
         eng.close()
