@@ -75,9 +75,10 @@ const char* srn_last_error(void);
 /* Number of CUDA kernels this library has launched in the calling process (bench.py's gpu_launches). */
 uint64_t srn_launch_count(void);
 
-/* Process-wide switch read by srn_build: 1 (default) runs aligned Dense/Conv problems on the tcgen05 tensor-core
- * kernels, 0 routes every GEMM through the general CUDA-core kernels (A/B parity tests). */
-int srn_set_tensor_cores(int32_t on);
+/* Number of cudaMalloc calls this library has made in the calling process.  Device memory of a handle is grow-only:
+ * a steady-state generation (same population size, similar architectures) allocates nothing, which this counter lets
+ * a caller verify (bench.py reports the allocations per generation). */
+uint64_t srn_alloc_count(void);
 
 /* Replaces EvolutionaryExperimentWorker.__init__ (experiment_worker.py:24-43). */
 int srn_create(const srn_config* cfg, srn_engine** out);
@@ -97,6 +98,12 @@ int srn_set_dataset(srn_engine* h,
  * `seed`.  A second build discards the first. */
 int srn_build(srn_engine* h, const srn_layer_desc* layers, const int32_t* layer_offsets,
               const float* loss_balance, int32_t n, uint64_t seed);
+/* The same with one initialisation seed per individual, so that an individual's initial weights do not depend on
+ * which shard (GPU) it lands in or on its position there: a generation sharded over 1, 2, 4 or 8 GPUs starts every
+ * individual from the same weights (the reference draws them from TF's unseeded global generator,
+ * experiment_worker.py:63-70, so any assignment is equally faithful). */
+int srn_build_seeded(srn_engine* h, const srn_layer_desc* layers, const int32_t* layer_offsets,
+                     const float* loss_balance, int32_t n, const uint64_t* individual_seeds);
 
 /* Weights in Keras layouts (Dense (in, out); Conv2D HWIO; Conv1D (k, in, out); BN gamma, beta,
  * moving_mean, moving_variance), fp16.  `which` indexes layer.get_weights().  *count receives the

@@ -30,6 +30,12 @@ namespace srn {
 
 thread_local std::string g_error;
 std::atomic<unsigned long long> g_launches{0};
+std::atomic<unsigned long long> g_allocs{0};      // cudaMalloc calls made by this library (srn_alloc_count)
+
+cudaError_t dmalloc(void** p, size_t bytes) {
+    g_allocs.fetch_add(1, std::memory_order_relaxed);
+    return cudaMalloc(p, bytes);
+}
 
 int fail(int code, const char* fmt, ...) {
     char buf[1024];
@@ -84,6 +90,63 @@ struct Indiv {
     std::vector<Tensor> tensors;
     float lb = 0.f;
     long long pcount = 0;
+};
+
+// Device memory owned by an engine handle is grow-only: a buffer is reallocated (with some headroom) only when a call
+// needs more than it holds, so that a steady-state generation - same population size, similar architectures - makes
+// no cudaMalloc / cudaFree at all (both synchronise the whole device).
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    template <class T> T* as() const { return static_cast<T*>(p); }
+};
+static cudaError_t buf_reserve(DevBuf& b, size_t bytes, double headroom = 1.0) {
+    if (bytes <= b.cap && b.p) return cudaSuccess;
+    if (b.p) { cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+    size_t want = (size_t)((double)bytes * headroom);
+    want = (std::max(want, bytes) + 255) & ~(size_t)255;
+    cudaError_t e = dmalloc(&b.p, want);
+    if (e != cudaSuccess && want > bytes) { cudaGetLastError(); want = (bytes + 255) & ~(size_t)255; e = dmalloc(&b.p, want); }
+    if (e != cudaSuccess) { b.p = nullptr; return e; }
+    b.cap = want;
+    return cudaSuccess;
+}
+static void buf_free(DevBuf& b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+
+// Bump allocator for everything a build and its launch plans create (problem tables, prefix sums, tile tables, tensor
+// maps, split-K scratch): nothing is freed one by one, the pool is rewound by the next build; if it ever needed a
+// second block the next rewind replaces the blocks by one of their combined size.
+struct DevPool {
+    std::vector<DevBuf> blocks;
+    size_t off = 0;          // offset in the last block
+    void* alloc(size_t bytes, cudaError_t* err) {
+        bytes = (bytes + 255) & ~(size_t)255;
+        if (blocks.empty() || off + bytes > blocks.back().cap) {
+            DevBuf b;
+            *err = buf_reserve(b, std::max(bytes, (size_t)8 << 20));
+            if (*err != cudaSuccess) return nullptr;
+            blocks.push_back(b);
+            off = 0;
+        }
+        void* r = static_cast<char*>(blocks.back().p) + off;
+        off += bytes;
+        *err = cudaSuccess;
+        return r;
+    }
+    cudaError_t rewind() {
+        if (blocks.size() > 1) {
+            size_t total = 0;
+            for (auto& b : blocks) { total += b.cap; buf_free(b); }
+            blocks.clear();
+            DevBuf b;
+            cudaError_t e = buf_reserve(b, total + total / 4);
+            if (e != cudaSuccess) return e;
+            blocks.push_back(b);
+        }
+        off = 0;
+        return cudaSuccess;
+    }
+    void release() { for (auto& b : blocks) buf_free(b); blocks.clear(); off = 0; }
 };
 
 struct Cached {
@@ -155,7 +218,11 @@ struct srn_engine {
     bool built = false;
     // metric buffers
     int* met_correct = nullptr; float* met_ce = nullptr; float* met_mse = nullptr; long long met_slots = 0;
-    std::vector<int*> scratch_prefix;   // all cached prefix arrays, for cleanup
+    // grow-only device memory (see DevBuf / DevPool)
+    DevBuf bP, bM, bV, bGr, bS, bSave, bAct, bIm2col, bMetC, bMetCe, bMetMse;
+    DevBuf bPerm, bLogits, bIdx, bRepX, bRepG, bRepPar, bRepProbs, bRepPacked, bRepMut;
+    DevPool pool;
+    cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;      // srn_fit's timing events
     // forward launches of one depth level that run the same kernel (same N tile) share one tile table: key (nb, depth, BN, mode)
     struct MergedFwd { TcTile* dev = nullptr; int total = 0; int first_group = -1; };
     std::map<std::tuple<int, int, int, int>, MergedFwd> merged_fwd;
@@ -165,6 +232,14 @@ struct srn_engine {
     do {                                                                                           \
         cudaError_t e_ = (call);                                                                   \
         if (e_ != cudaSuccess) return fail(SRN_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+// device memory from the handle's pool (rewound by the next build)
+#define POOL_ALLOC(ptr, T, bytes)                                                                  \
+    do {                                                                                           \
+        cudaError_t pe_;                                                                           \
+        (ptr) = static_cast<T*>(h->pool.alloc((bytes), &pe_));                                     \
+        if (pe_ != cudaSuccess) return fail(SRN_ERR_CUDA, "device pool: %s (%s:%d)", cudaGetErrorString(pe_), __FILE__, __LINE__); \
     } while (0)
 
 // every launch is counted and, when profiling is on, bracketed by CUDA events tagged with its category
@@ -205,24 +280,29 @@ static ProfRec* prof_begin(srn_engine* h, int cat) {
 
 extern "C" const char* srn_last_error(void) { return g_error.c_str(); }
 extern "C" uint64_t srn_launch_count(void) { return g_launches.load(); }
+extern "C" uint64_t srn_alloc_count(void) { return g_allocs.load(); }
 
 // ------------------------------------------------------------------ create / destroy
-static void free_population(srn_engine* h) {
-    for (auto& g : h->groups) { cudaFree(g.d); cudaFree(g.done); }
-    for (int* p : h->scratch_prefix) cudaFree(p);
-    h->scratch_prefix.clear();
+// Forget the population.  The device buffers stay with the handle for the next build (grow-only); release = true
+// (srn_destroy) gives them back.
+static void free_population(srn_engine* h, bool release = false) {
     h->merged_fwd.clear();
     h->groups.clear();
     h->inds.clear();
-    cudaFree(h->d_loss); h->d_loss = nullptr;
-    cudaFree(h->d_lb); h->d_lb = nullptr;
-    cudaFree(h->im2col); h->im2col = nullptr; h->geos.clear();
-    cudaFree(h->P); cudaFree(h->M); cudaFree(h->V); cudaFree(h->S); cudaFree(h->act); cudaFree(h->Gr); cudaFree(h->save);
+    h->d_loss = nullptr; h->d_lb = nullptr;
+    h->im2col = nullptr; h->geos.clear();
     h->P = h->M = h->V = h->S = h->act = nullptr; h->Gr = h->save = nullptr;
-    cudaFree(h->met_correct); cudaFree(h->met_ce); cudaFree(h->met_mse);
     h->met_correct = nullptr; h->met_ce = h->met_mse = nullptr; h->met_slots = 0;
     h->built = false; h->n = 0; h->device_bytes = 0;
+    if (release) {
+        for (DevBuf* b : {&h->bP, &h->bM, &h->bV, &h->bGr, &h->bS, &h->bSave, &h->bAct, &h->bIm2col, &h->bMetC, &h->bMetCe, &h->bMetMse,
+                          &h->bPerm, &h->bLogits, &h->bIdx, &h->bRepX, &h->bRepG, &h->bRepPar, &h->bRepProbs, &h->bRepPacked, &h->bRepMut})
+            buf_free(*b);
+        h->pool.release();
+    }
 }
+
+static int create_resources(srn_engine* h);
 
 extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
     if (!cfg || !out) return fail(SRN_ERR_ARG, "srn_create: null argument");
@@ -245,6 +325,14 @@ extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
     }
     srn_engine* h = new srn_engine();
     h->cfg = *cfg;
+    int rc = create_resources(h);
+    if (rc) { srn_destroy(h); return rc; }      // streams, events and buffers made so far are given back
+    *out = h;
+    return SRN_OK;
+}
+
+static int create_resources(srn_engine* h) {
+    const srn_config* cfg = &h->cfg;
     CK(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
     for (int i = 0; i < srn_engine::NSIDE; ++i) {
         CK(cudaStreamCreateWithFlags(&h->side[i], cudaStreamNonBlocking));
@@ -265,10 +353,10 @@ extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
     h->G = cfg->genotype_size;
     h->ncls = cfg->n_classes;
     h->NL = h->ncls + h->G;
-    CK(cudaMalloc(&h->xin, (size_t)cfg->max_batch * h->xe * sizeof(__half)));
-    CK(cudaMalloc(&h->gin, (size_t)cfg->max_batch * h->G * sizeof(__half)));
-    CK(cudaMalloc(&h->lab, (size_t)cfg->max_batch));
-    *out = h;
+    CK(cudaEventCreate(&h->ev_t0)); CK(cudaEventCreate(&h->ev_t1));
+    CK(dmalloc((void**)&h->xin, (size_t)cfg->max_batch * h->xe * sizeof(__half)));
+    CK(dmalloc((void**)&h->gin, (size_t)cfg->max_batch * h->G * sizeof(__half)));
+    CK(dmalloc((void**)&h->lab, (size_t)cfg->max_batch));
     return SRN_OK;
 }
 
@@ -276,7 +364,9 @@ extern "C" void srn_destroy(srn_engine* h) {
     if (!h) return;
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
-    free_population(h);
+    free_population(h, true);
+    if (h->ev_t0) cudaEventDestroy(h->ev_t0);
+    if (h->ev_t1) cudaEventDestroy(h->ev_t1);
     for (int i = 0; i < srn_engine::NSIDE; ++i) { if (h->side[i]) cudaStreamDestroy(h->side[i]); if (h->ev_join[i]) cudaEventDestroy(h->ev_join[i]); }
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_adam_go) cudaEventDestroy(h->ev_adam_go);
@@ -308,16 +398,16 @@ extern "C" int srn_set_dataset(srn_engine* h, const float* x_train, const uint8_
         if (!xs[s] || !gs[s]) return fail(SRN_ERR_ARG, "srn_set_dataset: null array for split %d", s);
         const long long ne = (long long)ns[s] * h->xe;
         float* tmp = nullptr;
-        CK(cudaMalloc(&tmp, ne * sizeof(float)));
+        CK(dmalloc((void**)&tmp, ne * sizeof(float)));
         CK(cudaMemcpy(tmp, xs[s], ne * sizeof(float), cudaMemcpyHostToDevice));
-        CK(cudaMalloc(&h->x[s], ne * sizeof(__half)));
+        CK(dmalloc((void**)&h->x[s], ne * sizeof(__half)));
         LAUNCH(SRN_CAT_OTHER, k_f32_to_f16, (unsigned)((ne + 255) / 256), 256, tmp, h->x[s], ne);
         CK(cudaStreamSynchronize(h->stream));
         CK(cudaFree(tmp));
-        CK(cudaMalloc(&h->y[s], ns[s]));
+        CK(dmalloc((void**)&h->y[s], ns[s]));
         if (ys[s]) CK(cudaMemcpy(h->y[s], ys[s], ns[s], cudaMemcpyHostToDevice));
         else CK(cudaMemset(h->y[s], 0, ns[s]));
-        CK(cudaMalloc(&h->gb[s], (size_t)ns[s] * h->G));
+        CK(dmalloc((void**)&h->gb[s], (size_t)ns[s] * h->G));
         CK(cudaMemcpy(h->gb[s], gs[s], (size_t)ns[s] * h->G, cudaMemcpyHostToDevice));
         h->nrows[s] = ns[s];
     }
@@ -331,7 +421,7 @@ static int cfg_for(int n) { return n <= 16 ? 2 : (n <= 32 ? 1 : 0); }
 // tensor-core N tile: 32 / 64 / 128 / 256 columns
 static int tc_cfg_for(int n) { return n <= 32 ? 0 : (n <= 64 ? 1 : (n <= 128 ? 2 : 3)); }
 static const int TC_BN[4] = {32, 64, 128, 256};
-static int g_tensor_cores = 1;      // srn_set_tensor_cores: 0 routes every GEMM through the SIMT kernels
+static int g_tensor_cores = 1;      // srn_debug_set_tensor_cores (test hook): 0 routes every GEMM through the SIMT kernels
 static const int CFG_BM[3] = {64, 128, 256};
 static const int CFG_BN[3] = {64, 32, 16};
 
@@ -386,7 +476,15 @@ static int validate_layer(const srn_layer_desc& d, const std::vector<Tensor>& ts
 
 extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int32_t* off, const float* loss_balance,
                          int32_t n, uint64_t seed) {
-    if (!h || !layers || !off || !loss_balance || n <= 0) return fail(SRN_ERR_ARG, "srn_build: bad argument");
+    if (n <= 0) return fail(SRN_ERR_ARG, "srn_build: bad argument");
+    std::vector<uint64_t> seeds((size_t)n);
+    for (int i = 0; i < n; ++i) seeds[(size_t)i] = seed * 0x9E3779B97F4A7C15ull + ((uint64_t)i << 20);
+    return srn_build_seeded(h, layers, off, loss_balance, n, seeds.data());
+}
+
+extern "C" int srn_build_seeded(srn_engine* h, const srn_layer_desc* layers, const int32_t* off, const float* loss_balance,
+                                int32_t n, const uint64_t* seeds) {
+    if (!h || !layers || !off || !loss_balance || !seeds || n <= 0) return fail(SRN_ERR_ARG, "srn_build: bad argument");
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
     free_population(h);
@@ -547,17 +645,22 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
     h->p_elems = align_up(std::max(p_off, 8LL), 8); h->s_elems = std::max(s_off, 8LL);
     h->act_elems = std::max(a_off, 64LL); h->save_elems = std::max(sv_off, 8LL);
     const size_t pb = (size_t)h->p_elems * sizeof(__half);
-    CK(cudaMalloc(&h->P, pb)); CK(cudaMalloc(&h->M, pb)); CK(cudaMalloc(&h->V, pb));
-    CK(cudaMalloc(&h->Gr, (size_t)h->p_elems * sizeof(float)));
-    CK(cudaMalloc(&h->S, (size_t)h->s_elems * sizeof(__half)));
-    CK(cudaMalloc(&h->save, (size_t)h->save_elems * sizeof(float)));
+    // arenas are kept across builds and only grow (with headroom, so that the next generation's similar population fits)
+    CK(h->pool.rewind());
+    CK(buf_reserve(h->bP, pb, 1.25)); CK(buf_reserve(h->bM, pb, 1.25)); CK(buf_reserve(h->bV, pb, 1.25));
+    CK(buf_reserve(h->bGr, (size_t)h->p_elems * sizeof(float), 1.25));
+    CK(buf_reserve(h->bS, (size_t)h->s_elems * sizeof(__half), 1.25));
+    CK(buf_reserve(h->bSave, (size_t)h->save_elems * sizeof(float), 1.25));
     {
-        cudaError_t e = cudaMalloc(&h->act, (size_t)h->act_elems * sizeof(__half));
+        cudaError_t e = buf_reserve(h->bAct, (size_t)h->act_elems * sizeof(__half), 1.15);
         if (e != cudaSuccess) {
+            cudaGetLastError();
             free_population(h);
             return fail(SRN_ERR_LIMIT, "activation arena of %.2f GB does not fit: %s", h->act_elems * 2.0 / 1e9, cudaGetErrorString(e));
         }
     }
+    h->P = h->bP.as<__half>(); h->M = h->bM.as<__half>(); h->V = h->bV.as<__half>(); h->Gr = h->bGr.as<float>();
+    h->S = h->bS.as<__half>(); h->save = h->bSave.as<float>(); h->act = h->bAct.as<__half>();
     h->device_bytes = 3LL * pb + h->p_elems * 4 + h->s_elems * 2 + h->save_elems * 4 + h->act_elems * 2;
     // everything starts at zero; the channel / row pads of tensors and kernels are never written afterwards
     CK(cudaMemsetAsync(h->P, 0, pb, h->stream)); CK(cudaMemsetAsync(h->M, 0, pb, h->stream)); CK(cudaMemsetAsync(h->V, 0, pb, h->stream));
@@ -694,7 +797,8 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
     h->groups.clear();
     for (auto& kv : gmap) h->groups.push_back(std::move(kv.second));   // std::map iterates in key order
     if (geo_elems > 0) {
-        CK(cudaMalloc(&h->im2col, (size_t)geo_elems * sizeof(__half)));
+        CK(buf_reserve(h->bIm2col, (size_t)geo_elems * sizeof(__half), 1.25));
+        h->im2col = h->bIm2col.as<__half>();
         CK(cudaMemsetAsync(h->im2col, 0, (size_t)geo_elems * sizeof(__half), h->stream));
         h->device_bytes += geo_elems * 2;
         for (auto& e : h->geos) e.out = h->im2col + (e.out - (__half*)nullptr);
@@ -730,15 +834,15 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
     }
     for (auto& g : h->groups) {
         if (g.kind == SRN_KIND_BN) {
-            CK(cudaMalloc(&g.done, g.h.size() * sizeof(int)));
+            POOL_ALLOC(g.done, int, g.h.size() * sizeof(int));
             CK(cudaMemsetAsync(g.done, 0, g.h.size() * sizeof(int), h->stream));
         }
-        CK(cudaMalloc(&g.d, g.h.size() * sizeof(Prob)));
+        POOL_ALLOC(g.d, Prob, g.h.size() * sizeof(Prob));
         CK(cudaMemcpyAsync(g.d, g.h.data(), g.h.size() * sizeof(Prob), cudaMemcpyHostToDevice, h->stream));
     }
-    CK(cudaMalloc(&h->d_loss, n * sizeof(Prob)));
+    POOL_ALLOC(h->d_loss, Prob, n * sizeof(Prob));
     CK(cudaMemcpyAsync(h->d_loss, h->h_loss.data(), n * sizeof(Prob), cudaMemcpyHostToDevice, h->stream));
-    CK(cudaMalloc(&h->d_lb, n * sizeof(float)));
+    POOL_ALLOC(h->d_lb, float, n * sizeof(float));
     CK(cudaMemcpyAsync(h->d_lb, loss_balance, n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
     // ---- Keras default initialisation on the device
     std::vector<long long> pad_off; std::vector<int> pad_len;     // kernel rows to clear afterwards (padded concatenations)
@@ -747,7 +851,7 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
         for (size_t l = 0; l < ind.layers.size(); ++l) {
             const LayerRt& L = ind.layers[l];
             const srn_layer_desc& d = L.d;
-            const uint64_t tseed = seed * 0x9E3779B97F4A7C15ull + ((uint64_t)i << 20) + l;
+            const uint64_t tseed = seeds[i] + l;
             if (d.kind == SRN_KIND_DENSE || d.kind == SRN_KIND_CONV) {
                 const int rf = d.kind == SRN_KIND_CONV ? d.kh * d.kw : 1;
                 const double fan_in = (double)d.in_c * rf;
@@ -775,14 +879,13 @@ extern "C" int srn_build(srn_engine* h, const srn_layer_desc* layers, const int3
     }
     long long* d_pad_off = nullptr; int* d_pad_len = nullptr;
     if (!pad_off.empty()) {
-        CK(cudaMalloc(&d_pad_off, pad_off.size() * sizeof(long long)));
-        CK(cudaMalloc(&d_pad_len, pad_len.size() * sizeof(int)));
+        POOL_ALLOC(d_pad_off, long long, pad_off.size() * sizeof(long long));
+        POOL_ALLOC(d_pad_len, int, pad_len.size() * sizeof(int));
         CK(cudaMemcpyAsync(d_pad_off, pad_off.data(), pad_off.size() * sizeof(long long), cudaMemcpyHostToDevice, h->stream));
         CK(cudaMemcpyAsync(d_pad_len, pad_len.data(), pad_len.size() * sizeof(int), cudaMemcpyHostToDevice, h->stream));
         LAUNCH(SRN_CAT_OTHER, k_zero_spans, (unsigned)pad_off.size(), 64, h->P, d_pad_off, d_pad_len);
     }
     CK(cudaStreamSynchronize(h->stream));
-    cudaFree(d_pad_off); cudaFree(d_pad_len);
     CK(cudaGetLastError());
     h->n = n;
     h->adam_t = 0;
@@ -871,7 +974,7 @@ extern "C" int srn_set_weights(srn_engine* h, int32_t ind, int32_t layer, int32_
     return copy_rows(const_cast<uint16_t*>(buf), reinterpret_cast<char*>(p), rows, cols, ld, sizeof(__half), rm, false);
 }
 
-extern "C" int srn_set_tensor_cores(int32_t on) {
+extern "C" int srn_debug_set_tensor_cores(int32_t on) {
     g_tensor_cores = on ? 1 : 0;
     return SRN_OK;
 }
@@ -982,10 +1085,9 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
         c.total[pass] = (int)acc;
     }
     int* dev = nullptr;
-    CK(cudaMalloc(&dev, host.size() * sizeof(int)));
+    POOL_ALLOC(dev, int, host.size() * sizeof(int));
     CK(cudaMemcpyAsync(dev, host.data(), host.size() * sizeof(int), cudaMemcpyHostToDevice, h->stream));
     CK(cudaStreamSynchronize(h->stream));      // host vector goes out of scope
-    h->scratch_prefix.push_back(dev);
     for (int pass = 0; pass < P_COUNT; ++pass) c.prefix[pass] = dev + (size_t)pass * (np + 1);
     if (g.tc == 1 || g.tc == 2) {
         for (int pass : {P_FWD, P_DGRAD, P_WGRAD}) {
@@ -1009,9 +1111,8 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
                     const size_t acc_bytes = rows * p.Fs * sizeof(float);
                     const size_t cnt_ints = 4 * ((rows + TC_BM - 1) / TC_BM) * ((p.F + BN - 1) / BN);
                     char* buf = nullptr;
-                    CK(cudaMalloc(&buf, acc_bytes + cnt_ints * sizeof(int)));
+                    POOL_ALLOC(buf, char, acc_bytes + cnt_ints * sizeof(int));
                     CK(cudaMemset(buf, 0, acc_bytes + cnt_ints * sizeof(int)));
-                    h->scratch_prefix.push_back(reinterpret_cast<int*>(buf));
                     h->device_bytes += (long long)(acc_bytes + cnt_ints * sizeof(int));
                     for (int t = pre[i]; t < pre[i + 1]; ++t) {
                         tt[t].sk_acc = reinterpret_cast<float*>(buf);
@@ -1030,9 +1131,8 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
                     }
                 if (!maps.empty()) {
                     CUtensorMap* dm = nullptr;
-                    CK(cudaMalloc(&dm, maps.size() * sizeof(CUtensorMap)));
+                    POOL_ALLOC(dm, CUtensorMap, maps.size() * sizeof(CUtensorMap));
                     CK(cudaMemcpy(dm, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
-                    h->scratch_prefix.push_back(reinterpret_cast<int*>(dm));
                     for (int i = 0; i < np; ++i)
                         if (first[i] >= 0)
                             for (int t = pre[i]; t < pre[i + 1]; ++t) tt[t].tm = dm + first[i];
@@ -1040,9 +1140,8 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
             }
             std::stable_sort(tt.begin(), tt.end(), [](const TcTile& a, const TcTile& b) { return a.nk * a.nsub > b.nk * b.nsub; });
             TcTile* dt = nullptr;
-            CK(cudaMalloc(&dt, tt.size() * sizeof(TcTile)));
+            POOL_ALLOC(dt, TcTile, tt.size() * sizeof(TcTile));
             CK(cudaMemcpy(dt, tt.data(), tt.size() * sizeof(TcTile), cudaMemcpyHostToDevice));
-            h->scratch_prefix.push_back(reinterpret_cast<int*>(dt));
             c.tiles[pass] = dt;
             if (pass == P_FWD && g.tc == 1) c.host_fwd = tt;
         }
@@ -1236,9 +1335,8 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
                     m.total = (int)all.size();
                     m.first_group = (int)(by_bn[b][0] - h->groups.data());
                     if (m.total) {
-                        CK(cudaMalloc(&m.dev, all.size() * sizeof(TcTile)));
+                        POOL_ALLOC(m.dev, TcTile, all.size() * sizeof(TcTile));
                         CK(cudaMemcpy(m.dev, all.data(), all.size() * sizeof(TcTile), cudaMemcpyHostToDevice));
-                        h->scratch_prefix.push_back(reinterpret_cast<int*>(m.dev));
                     }
                     it = h->merged_fwd.emplace(key, m).first;
                 }
@@ -1344,11 +1442,11 @@ static int backward_pass(srn_engine* h, int nb, const Inputs& I) {
 }
 
 static int ensure_metrics(srn_engine* h, long long slots) {
-    if (slots > h->met_slots) {
-        cudaFree(h->met_correct); cudaFree(h->met_ce); cudaFree(h->met_mse);
-        CK(cudaMalloc(&h->met_correct, slots * h->n * sizeof(int)));
-        CK(cudaMalloc(&h->met_ce, slots * h->n * sizeof(float)));
-        CK(cudaMalloc(&h->met_mse, slots * h->n * sizeof(float)));
+    if (slots > h->met_slots || !h->met_correct) {
+        CK(buf_reserve(h->bMetC, slots * h->n * sizeof(int), 1.25));
+        CK(buf_reserve(h->bMetCe, slots * h->n * sizeof(float), 1.25));
+        CK(buf_reserve(h->bMetMse, slots * h->n * sizeof(float), 1.25));
+        h->met_correct = h->bMetC.as<int>(); h->met_ce = h->bMetCe.as<float>(); h->met_mse = h->bMetMse.as<float>();
         h->met_slots = slots;
     }
     CK(cudaMemsetAsync(h->met_correct, 0, slots * h->n * sizeof(int), h->stream));
@@ -1462,14 +1560,13 @@ extern "C" int srn_fit(srn_engine* h, int32_t epochs, int32_t batch, int32_t n_v
         for (size_t i = 0; i < (size_t)epochs * n_fit; ++i)
             if (perms[i] < 0 || perms[i] >= n_fit) return fail(SRN_ERR_ARG, "srn_fit: permutation entry %d out of range", perms[i]);
     }
-    int* d_perm = nullptr;
-    CK(cudaMalloc(&d_perm, (size_t)epochs * n_fit * sizeof(int)));
+    CK(buf_reserve(h->bPerm, (size_t)epochs * n_fit * sizeof(int)));
+    int* d_perm = h->bPerm.as<int>();
     CK(cudaMemcpy(d_perm, perms, (size_t)epochs * n_fit * sizeof(int), cudaMemcpyHostToDevice));
     const long long slots = (long long)epochs * (S + Vc);
     rc = ensure_metrics(h, slots);
-    if (rc) { cudaFree(d_perm); return rc; }
-    cudaEvent_t ev0, ev1;
-    CK(cudaEventCreate(&ev0)); CK(cudaEventCreate(&ev1));
+    if (rc) return rc;
+    cudaEvent_t ev0 = h->ev_t0, ev1 = h->ev_t1;
     float ms_total = 0.f;
     int steps_done = 0;
     bool stop = false;
@@ -1477,20 +1574,20 @@ extern "C" int srn_fit(srn_engine* h, int32_t epochs, int32_t batch, int32_t n_v
     wait_adam(h);
     CK(cudaMemsetAsync(h->Gr, 0, (size_t)h->p_elems * sizeof(float), h->stream));
     // warm the launch plans outside the timed region
-    for (auto& g : h->groups) { Cached* c; rc = plan_for(h, g, batch, &c); if (rc) { cudaFree(d_perm); return rc; } }
+    for (auto& g : h->groups) { Cached* c; rc = plan_for(h, g, batch, &c); if (rc) return rc; }
     for (int e = 0; e < epochs && !stop; ++e) {
         CK(cudaEventRecord(ev0, h->stream));
         for (int s = 0; s < S; ++s) {
             const int nb = std::min(batch, n_fit - s * batch);
             rc = train_step(h, d_perm + (size_t)e * n_fit + (size_t)s * batch, 0, nb, e * S + s, true);
-            if (rc) { cudaFree(d_perm); return rc; }
+            if (rc) return rc;
             if (max_steps > 0 && ++steps_done >= max_steps) { stop = true; break; }
         }
         wait_adam(h);
         CK(cudaEventRecord(ev1, h->stream));
         if (n_val && !stop) {
             rc = eval_rows(h, 0, n_fit, n_val, batch, epochs * S + e * Vc);
-            if (rc) { cudaFree(d_perm); return rc; }
+            if (rc) return rc;
         }
         CK(cudaEventSynchronize(ev1));
         float ms = 0.f;
@@ -1499,8 +1596,6 @@ extern "C" int srn_fit(srn_engine* h, int32_t epochs, int32_t batch, int32_t n_v
     }
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaGetLastError());
-    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
-    cudaFree(d_perm);
     const size_t tn = (size_t)epochs * S * h->n, vn = (size_t)epochs * Vc * h->n;
     if (train_correct) CK(cudaMemcpy(train_correct, h->met_correct, tn * sizeof(int), cudaMemcpyDeviceToHost));
     if (train_loss) {
@@ -1568,8 +1663,8 @@ extern "C" int srn_forward_logits(srn_engine* h, int32_t split, int32_t start, i
         return fail(SRN_ERR_ARG, "srn_forward_logits: bad range");
     if (training && rows > h->cfg.max_batch) return fail(SRN_ERR_ARG, "srn_forward_logits: training-mode batch > max_batch");
     CK(cudaSetDevice(h->cfg.device));
-    __half* d_out = nullptr;
-    CK(cudaMalloc(&d_out, (size_t)h->n * rows * h->NL * sizeof(__half)));
+    CK(buf_reserve(h->bLogits, (size_t)h->n * rows * h->NL * sizeof(__half)));
+    __half* d_out = h->bLogits.as<__half>();
     const int MB = h->cfg.max_batch;
     for (int r = 0; r < rows; r += MB) {
         const int nb = std::min(MB, rows - r);
@@ -1577,14 +1672,13 @@ extern "C" int srn_forward_logits(srn_engine* h, int32_t split, int32_t start, i
                h->xin, h->gin, h->lab);
         Inputs I = shared_inputs(h);
         rc = forward_pass(h, nb, I, training != 0);
-        if (rc) { cudaFree(d_out); return rc; }
+        if (rc) return rc;
         dim3 grid(nb, h->n);
         LAUNCH(SRN_CAT_OTHER, k_collect_heads, grid, 128, h->d_loss, h->n, nb, h->NL, h->ncls, r, rows, d_out, (__half*)nullptr);
     }
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaGetLastError());
     CK(cudaMemcpy(logits, d_out, (size_t)h->n * rows * h->NL * sizeof(__half), cudaMemcpyDeviceToHost));
-    cudaFree(d_out);
     return SRN_OK;
 }
 
@@ -1607,19 +1701,21 @@ extern "C" int srn_replicate(srn_engine* h, const uint8_t* parent_bits, int32_t 
         const long long repeat = (rows + h->nrows[1] - 1) / h->nrows[1];
         for (long long r = 0; r < rows; ++r) idx[r] = (int32_t)(r / repeat);
     }
-    int* d_idx = nullptr; __half* d_x = nullptr; __half* d_g = nullptr; uint8_t* d_par = nullptr;
-    __half* d_probs = nullptr; uint32_t* d_packed = nullptr; int* d_mut = nullptr;
-    auto cleanup = [&]() { cudaFree(d_idx); cudaFree(d_x); cudaFree(d_g); cudaFree(d_par); cudaFree(d_probs); cudaFree(d_packed); cudaFree(d_mut); };
+    // staging buffers belong to the handle and only grow: no cudaMalloc / cudaFree per generation
+    auto cleanup = [&]() {};
 #define CKR(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); return fail(SRN_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); } } while (0)
-    CKR(cudaMalloc(&d_idx, rows * sizeof(int)));
+    CKR(buf_reserve(h->bIdx, rows * sizeof(int), 1.25));
+    CKR(buf_reserve(h->bRepX, rows * xe * sizeof(__half), 1.25));
+    CKR(buf_reserve(h->bRepG, (size_t)n * G * sizeof(__half), 1.25));
+    CKR(buf_reserve(h->bRepPar, (size_t)n * G, 1.25));
+    CKR(buf_reserve(h->bRepProbs, rows * G * sizeof(__half), 1.25));
+    CKR(buf_reserve(h->bRepPacked, rows * words * sizeof(uint32_t), 1.25));
+    CKR(buf_reserve(h->bRepMut, rows * sizeof(int), 1.25));
+    int* d_idx = h->bIdx.as<int>(); __half* d_x = h->bRepX.as<__half>(); __half* d_g = h->bRepG.as<__half>();
+    uint8_t* d_par = h->bRepPar.as<uint8_t>(); __half* d_probs = h->bRepProbs.as<__half>();
+    uint32_t* d_packed = h->bRepPacked.as<uint32_t>(); int* d_mut = h->bRepMut.as<int>();
     CKR(cudaMemcpy(d_idx, idx.data(), rows * sizeof(int), cudaMemcpyHostToDevice));
-    CKR(cudaMalloc(&d_x, rows * xe * sizeof(__half)));
-    CKR(cudaMalloc(&d_g, (size_t)n * G * sizeof(__half)));
-    CKR(cudaMalloc(&d_par, (size_t)n * G));
     CKR(cudaMemcpy(d_par, parent_bits, (size_t)n * G, cudaMemcpyHostToDevice));
-    CKR(cudaMalloc(&d_probs, rows * G * sizeof(__half)));
-    CKR(cudaMalloc(&d_packed, rows * words * sizeof(uint32_t)));
-    CKR(cudaMalloc(&d_mut, rows * sizeof(int)));
     LAUNCH(SRN_CAT_GATHER, k_gather_batch, (unsigned)rows, 256, h->x[1], (const uint8_t*)nullptr, (const uint8_t*)nullptr, d_idx, 0, (int)rows, xe, G,
            d_x, (__half*)nullptr, (uint8_t*)nullptr);
     LAUNCH(SRN_CAT_OTHER, k_u8_to_f16, (unsigned)(((long long)n * G + 255) / 256), 256, d_par, d_g, (long long)n * G);
@@ -1651,15 +1747,14 @@ extern "C" int srn_debug_step(srn_engine* h, const int32_t* rows, int32_t nb, in
     if (rc) return rc;
     if (!rows || nb <= 0 || nb > h->cfg.max_batch) return fail(SRN_ERR_ARG, "srn_debug_step: bad batch");
     CK(cudaSetDevice(h->cfg.device));
-    int* d_idx = nullptr;
-    CK(cudaMalloc(&d_idx, nb * sizeof(int)));
+    CK(buf_reserve(h->bIdx, nb * sizeof(int), 1.25));
+    int* d_idx = h->bIdx.as<int>();
     CK(cudaMemcpy(d_idx, rows, nb * sizeof(int), cudaMemcpyHostToDevice));
     rc = ensure_metrics(h, 1);
     cudaMemsetAsync(h->Gr, 0, (size_t)h->p_elems * sizeof(float), h->stream);
     if (!rc) rc = train_step(h, d_idx, 0, nb, 0, apply_adam != 0);
     wait_adam(h);
     cudaError_t e = cudaStreamSynchronize(h->stream);
-    cudaFree(d_idx);
     if (rc) return rc;
     if (e != cudaSuccess) return fail(SRN_ERR_CUDA, "srn_debug_step: %s", cudaGetErrorString(e));
     CK(cudaGetLastError());

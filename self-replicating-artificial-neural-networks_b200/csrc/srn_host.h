@@ -2,6 +2,7 @@
 // the parity tests use (not part of the product ABI in include/serann_b200.h).
 #pragma once
 #include <atomic>
+#include <cuda_runtime.h>
 #include <stdint.h>
 #include <string>
 
@@ -10,10 +11,15 @@ struct srn_engine;
 namespace srn {
 extern thread_local std::string g_error;
 extern std::atomic<unsigned long long> g_launches;
+extern std::atomic<unsigned long long> g_allocs;
+cudaError_t dmalloc(void** p, size_t bytes);      // counted cudaMalloc
 int fail(int code, const char* fmt, ...);
 }  // namespace srn
 
 extern "C" {
+// Test hook, process-wide, read by srn_build: 1 (default) runs aligned Dense/Conv problems on the tcgen05 kernels, 0 routes
+// every GEMM through the general CUDA-core kernels that otherwise only serve odd-stride views (A/B parity tests).
+int srn_debug_set_tensor_cores(int32_t on);
 // one training step on the given rows of the training split; apply_adam = 0 leaves the fp32 gradients in place
 int srn_debug_step(srn_engine* h, const int32_t* rows, int32_t nb, int32_t apply_adam);
 // activation (grad = 0) or activation gradient (grad = 1) of tensor `tensor` of one individual, first nb rows

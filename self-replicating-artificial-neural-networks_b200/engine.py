@@ -82,7 +82,9 @@ def load_library(rebuild: bool = False) -> C.CDLL:
     lib.srn_bn_train_forward_noalloc.argtypes = [i32, vp, vp, i64, i32, vp, vp, vp, vp, vp]
     lib.srn_levenshtein.argtypes = [C.c_char_p, i32, C.c_char_p, i32]
     lib.srn_levenshtein.restype = i32
-    lib.srn_set_tensor_cores.argtypes = [i32]
+    lib.srn_debug_set_tensor_cores.argtypes = [i32]
+    lib.srn_alloc_count.restype = u64
+    lib.srn_build_seeded.argtypes = [vp, C.POINTER(LayerDesc), vp, vp, i32, vp]
     lib.srn_profile.argtypes = [vp, i32]
     lib.srn_profile_read.argtypes = [vp, vp, vp]
     lib.srn_debug_step.argtypes = [vp, vp, i32, i32]
@@ -105,12 +107,17 @@ def _ptr(a: Optional[np.ndarray]):
 
 
 def set_tensor_cores(on: bool):
-    """Process-wide: route aligned GEMMs through tcgen05 (default) or everything through the SIMT kernels."""
-    _check(load_library().srn_set_tensor_cores(int(on)))
+    """Test hook (srn_host.h, not part of the product ABI), process-wide: aligned GEMMs on tcgen05 (default) or everything on the SIMT kernels."""
+    _check(load_library().srn_debug_set_tensor_cores(int(on)))
 
 
 def launch_count() -> int:
     return int(load_library().srn_launch_count())
+
+
+def alloc_count() -> int:
+    """cudaMalloc calls made by the library so far (zero per steady-state generation)."""
+    return int(load_library().srn_alloc_count())
 
 
 def _hwc(shape: Sequence[int], spatial: int):
@@ -204,7 +211,8 @@ class Engine:
         self.h2d_bytes = sum(v.nbytes for v in (*a[:3], *b[:3]) if v is not None)
 
     # ---- population
-    def build(self, irs: Sequence[SerannIR], seed: int = 0):
+    def build(self, irs: Sequence[SerannIR], seed: int = 0, individual_seeds: Optional[Sequence[int]] = None):
+        """``individual_seeds``: one initialisation seed per individual (independent of shard and position)."""
         descs, offs = [], [0]
         for ir in irs:
             descs += layer_descs(ir)
@@ -212,7 +220,13 @@ class Engine:
         arr = (LayerDesc * len(descs))(*descs)
         offs = np.asarray(offs, dtype=np.int32)
         lb = np.asarray([ir.loss_balance for ir in irs], dtype=np.float32)
-        _check(self._lib.srn_build(self._h, arr, _ptr(offs), _ptr(lb), len(irs), C.c_uint64(seed & (2 ** 64 - 1))))
+        if individual_seeds is not None:
+            sd = np.asarray([int(v) & (2 ** 64 - 1) for v in individual_seeds], dtype=np.uint64)
+            if len(sd) != len(irs):
+                raise EngineError('one seed per individual expected')
+            _check(self._lib.srn_build_seeded(self._h, arr, _ptr(offs), _ptr(lb), len(irs), _ptr(sd)))
+        else:
+            _check(self._lib.srn_build(self._h, arr, _ptr(offs), _ptr(lb), len(irs), C.c_uint64(seed & (2 ** 64 - 1))))
         self.n, self.irs = len(irs), list(irs)
 
     def parameters_count(self, i: int) -> int:

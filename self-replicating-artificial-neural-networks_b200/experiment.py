@@ -12,14 +12,20 @@ from __future__ import annotations
 
 from datetime import datetime
 from typing import Dict, Optional
-from uuid import uuid4
+import random
+from uuid import UUID
 
 import numpy as np
 import pandas as pd
 
-from .engine import levenshtein
-from .frontend import extract_layer_counts
-from .parallel import reference_batches
+from .engine import levenshtein, unpack_bits
+from .frontend import InvalidSerann, compile_cached, extract_layer_counts
+from .parallel import (ShardContext, individual_cost, lpt_shards, pack_shard_results, reference_batches, stable_seed,
+                       unpack_shard_results)
+
+MODELS_INFO_COLUMNS = ['parameters_count', 'loss_balance', 'is_valid', 'is_overweight',
+                       'classification_validation_accuracy', 'classification_training_accuracy',
+                       'classification_test_accuracy', 'replication_mse']
 
 MAX_SERANN_PER_GPU = 112        # reference evolutionary_experiment/config.py:8
 
@@ -53,7 +59,8 @@ def pairwise_genotype_distances(genotypes: np.ndarray):
 
 class Experiment:
     def __init__(self, experiment_id, serann_dataset, workers_pool, experiment_db, parameters, genetic_encoder,
-                 start_generation: int = 0, population_source=None):
+                 start_generation: int = 0, population_source=None, shard_context: Optional[ShardContext] = None,
+                 seed_base: int = 0):
         """``genetic_encoder``: a ``RibosomalAutoencoder`` (reference builds it itself from config paths,
         ``experiment.py:36``).  ``population_source``: optional callable ``(n) -> list of source strings``; when
         given, the next generation's *source codes* come from it instead of from the decoder - needed with a
@@ -69,6 +76,17 @@ class Experiment:
         self._experiment_db.save_execution_info(datetime.now(), self._parameters)
         self._workers_pool = workers_pool
         self.generation_seconds = []
+        # one process per GPU (torchrun): this rank trains its shard of every generation, one all-gather per generation
+        self._ctx = shard_context or ShardContext()
+        self._seed_base = seed_base
+        self._generation_index = start_generation
+        # individual ids: version-4 UUIDs from a generator every rank seeds alike (uuid4() would differ per process);
+        # the legacy np.random stream is left to the draws the reference makes from it
+        self._id_rng = random.Random(stable_seed(seed_base, 'ids', start_generation))
+        self.phase_seconds = []          # per generation: evaluate / allgather / statistics / select+decode
+
+    def _new_id(self) -> str:
+        return str(UUID(int=self._id_rng.getrandbits(128), version=4))
 
     # ------------------------------------------------------------------ main loop (experiment.py:43-108)
     def execute(self):
@@ -85,7 +103,12 @@ class Experiment:
             current['generation'] = generation
             current['num_offspring'] = 0
             print('Starting training and replication')
+            self._generation_index = generation
+            ph = {}
+            tp = datetime.now()
             models_info, offspring_by_id, times = self._learn_and_replicate(current, offspring_pool_size)
+            ph['evaluate'] = (datetime.now() - tp).total_seconds()
+            ph['allgather_ms'] = self._ctx.last_allgather_ms
             current = current.join(models_info)
             print('Calculating fecundity scores')
             current['absolute_fertility'], current['relative_fertility'] = \
@@ -99,14 +122,19 @@ class Experiment:
             counts = pd.DataFrame([extract_layer_counts(s) for s in valid['source_code']], index=valid.index)
             current = current.join(counts, how='left')
             print('Saving generation information to the experiment DB')
+            tp = datetime.now()
             self._report_generation_statistics(current, generation, times, t0)
             print('Saving SeRANN records to the experiment DB')
             self._experiment_db.save_seranns_info(current)
+            ph['statistics_db'] = (datetime.now() - tp).total_seconds()
             if len(valid) == 0:
                 print('No valid SeRANNs left! stopping...')
                 break
             print('Applying offspring selection')
+            tp = datetime.now()
             nxt = self._select_offspring(current, offspring_by_id)
+            ph['select_decode'] = (datetime.now() - tp).total_seconds()
+            self.phase_seconds.append(ph)
             print(f'Generation {generation} execution is done')
             offspring_pool_size = int(current['num_offspring'].max() * p['offspring_pool_size_factor'])
             print('Offspring pool size was updated to:', offspring_pool_size)
@@ -144,10 +172,10 @@ class Experiment:
         ancestor = p.get('ancestor_genotype')
         if ancestor is None:
             sample = np.random.randint(0, len(self._serann_dataset), p['num_seranns'])
-            by_id = {str(uuid4()): self._serann_dataset[s] for s in sample}
+            by_id = {self._new_id(): self._serann_dataset[s] for s in sample}
         else:
             ancestor = np.array(ancestor)
-            by_id = {str(uuid4()): ancestor for _ in range(p['num_seranns'])}
+            by_id = {self._new_id(): ancestor for _ in range(p['num_seranns'])}
         gen = pd.Series(by_id).rename('genotype').rename_axis('id').to_frame()
         genotypes = np.array(gen['genotype'].values.tolist())
         gen['source_code'] = self._sources_for(genotypes)
@@ -164,21 +192,94 @@ class Experiment:
         return list(self._population_source(len(genotypes)))
 
     # ------------------------------------------------------------------ evaluation (experiment.py:162-190)
+    def _seeds_for(self, generation: pd.DataFrame):
+        """Row order of this generation's epochs and initial weights per individual, independent of the sharding."""
+        fit_seed = stable_seed(self._seed_base, 'fit', self._generation_index) >> 1
+        return fit_seed, {i: stable_seed(self._seed_base, 'init', i) for i in generation.index}
+
+    @staticmethod
+    def _offspring_from_kernel(result: dict) -> dict:
+        """{id: (R, G) float16 of 0.0 / 1.0} from the readout kernel's bits (what ``np.round(np.clip(p, 0, 1))`` gives,
+        experiment.py:210); a row that held a NaN probability stays NaN, as it does in the reference."""
+        out = {}
+        for sid, bits in result.get('offspring_bits_by_id', {}).items():
+            g = bits.astype(np.float16)
+            nan = np.asarray(result['offspring_nan_by_id'][sid], dtype=bool)
+            if nan.any():
+                p = result['offspring_by_id'][sid]
+                g = np.where(np.isnan(p.astype(np.float32)), np.float16(np.nan), g)
+            out[sid] = g
+        return out
+
     def _learn_and_replicate(self, generation: pd.DataFrame, num_offspring):
+        if self._ctx.world > 1:
+            return self._learn_and_replicate_sharded(generation, num_offspring)
         times: Dict[str, list] = {}
         infos, offspring_by_id = [], {}
         workers = self._workers_pool.get_workers_count()
         batch_index = reference_batches(len(generation), workers, MAX_SERANN_PER_GPU)
         batch_by_id = pd.Series(batch_index, index=generation.index).astype(int)
         total = batch_by_id.nunique()
-        jobs = [{'args': [data, num_offspring]} for _, data in generation.groupby(batch_by_id)]
+        seeded = getattr(self._workers_pool, 'accepts_seeds', False)
+        kwargs = {}
+        if seeded:
+            fit_seed, ind_seeds = self._seeds_for(generation)
+            kwargs = {'kwargs': {'fit_seed': fit_seed, 'individual_seeds': ind_seeds}}
+        jobs = [{'args': [data, num_offspring], **kwargs} for _, data in generation.groupby(batch_by_id)]
         for i, result in enumerate(self._workers_pool.imap_unordered(jobs), 1):
             print(f'{i} of {total} batches completed')
             infos.append(result['models_info'])
-            offspring_by_id.update(result.get('offspring_by_id', {}))
+            if 'offspring_bits_by_id' in result:
+                offspring_by_id.update(self._offspring_from_kernel(result))     # the readout kernel's thresholded bits
+            else:
+                offspring_by_id.update(result.get('offspring_by_id', {}))
             times.setdefault('learning_times', []).append(result['learning_time'])
-            times.setdefault('replication_times', []).append(result['replication_time'])
+            times.setdefault('replication_times', []).append(result.get('replication_time', 0))
         return pd.concat(infos), offspring_by_id, times
+
+    def _learn_and_replicate_sharded(self, generation: pd.DataFrame, num_offspring):
+        """One process per GPU: longest-processing-time-first shards of equal size, this rank evaluates its shard, one
+        all-gather carries every shard's ``models_info`` columns, bit-packed offspring and mutation counts to every
+        rank (reference: pickled shards through a Redis task farm, experiment.py:162-190)."""
+        p = self._parameters
+        ctx = self._ctx
+        dims = dict(image_dims=tuple(p['classification_image_dimensions']), genotype_size=int(p['genotype_size']),
+                    n_classes=int(p['num_classification_classes']))
+        costs = []
+        for src in generation['source_code']:
+            try:
+                costs.append(individual_cost(compile_cached(src, **dims), int(p['training_batch_size'])))
+            except InvalidSerann:
+                costs.append(0.0)
+        shards = lpt_shards(costs, ctx.world)
+        self.last_shards = shards
+        ids_by_rank = [[generation.index[k] for k in sh] for sh in shards]
+        mine = generation.loc[ids_by_rank[ctx.rank]]
+        fit_seed, ind_seeds = self._seeds_for(generation)
+        job = {'args': [mine, num_offspring], 'kwargs': {'fit_seed': fit_seed, 'individual_seeds': ind_seeds}}
+        result = next(iter(self._workers_pool.imap_unordered([job])))
+        R, G = int(num_offspring), int(p['genotype_size'])
+        blobs = ctx.allgather_bytes(pack_shard_results(ids_by_rank[ctx.rank], result, MODELS_INFO_COLUMNS, R, G))
+        infos, offspring_by_id, times = [], {}, {'learning_times': [], 'replication_times': []}
+        for rank, blob in enumerate(blobs):
+            t, info, has, packed, mut, nan = unpack_shard_results(blob, len(MODELS_INFO_COLUMNS), G)
+            ids = ids_by_rank[rank]
+            df = pd.DataFrame(info, index=pd.Index(ids, name=generation.index.name), columns=MODELS_INFO_COLUMNS)
+            df['is_valid'] = df['is_valid'].fillna(0).astype(bool)
+            df['is_overweight'] = df['is_overweight'].fillna(0).astype(bool)
+            infos.append(df)
+            bits = unpack_bits(packed, G)
+            for k, sid in enumerate(ids):
+                if has[k]:
+                    g = bits[k].astype(np.float16)
+                    if nan[k].any():         # F6 individuals: every probability of a row is NaN, and so is the stored genotype
+                        g[nan[k].astype(bool)] = np.float16(np.nan)
+                    offspring_by_id[sid] = g
+            times['learning_times'].append(float(t[0]))
+            times['replication_times'].append(float(t[1]))
+        print(f'{ctx.world} of {ctx.world} shards gathered ({ctx.last_allgather_ms:.2f} ms)')
+        # rows back in the generation's own order
+        return pd.concat(infos).loc[generation.index], {i: offspring_by_id[i] for i in generation.index if i in offspring_by_id}, times
 
     # ------------------------------------------------------------------ selection (experiment.py:192-238, 305-321)
     def _select_offspring(self, generation: pd.DataFrame, offspring_by_id: dict):
@@ -194,7 +295,7 @@ class Experiment:
             bits = np.round(np.clip(probs, 0, 1))                     # experiment.py:210
             chosen = strategy(parent_genotype, n, bits)
             chosen = self._probabilistic_proofreading(parent_genotype, chosen)
-            ids += [str(uuid4()) for _ in range(n)]
+            ids += [self._new_id() for _ in range(n)]
             parents += [parent_id] * n
             genotypes += list(chosen)
         offspring = np.array(genotypes)

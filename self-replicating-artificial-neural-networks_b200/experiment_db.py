@@ -20,8 +20,10 @@ FLOAT_COLUMNS = ['error_correction_probability', 'selection_pressure']
 
 
 class ExperimentDB:
-    def __init__(self, db_path):
+    def __init__(self, db_path, read_only: bool = False):
+        """``read_only``: the ranks other than 0 of a multi-GPU run compute the same tables and must not write them."""
         self._db_path = str(db_path)
+        self._read_only = read_only
 
     @property
     def db_path(self):
@@ -42,6 +44,8 @@ class ExperimentDB:
         return conn.execute("select count(*) from sqlite_master where type='table' and name=?", (name,)).fetchone()[0] > 0
 
     def save_execution_info(self, start_time, parameters):
+        if self._read_only:
+            return
         with self.db_connection() as conn:
             row = {'start_time': str(start_time)}
             row.update(parameters)
@@ -54,6 +58,8 @@ class ExperimentDB:
             existing.to_sql('execution_info', conn, index=False, if_exists='replace')
 
     def save_seranns_info(self, seranns_info: pd.DataFrame):
+        if self._read_only:
+            return
         with self.db_connection() as conn:
             genotype_str = seranns_info['genotype'].map(lambda x: str(np.asarray(x).tolist()))
             df = seranns_info.assign(genotype=genotype_str)
@@ -63,6 +69,8 @@ class ExperimentDB:
             df.to_sql('serann', conn, if_exists='append', index=True, index_label='id')
 
     def save_generation_info(self, generation_info: dict):
+        if self._read_only:
+            return
         with self.db_connection() as conn:
             row = {k: (str(v) if k == 'start_time' else v) for k, v in generation_info.items()}
             pd.DataFrame([row]).to_sql('generations', conn, index=False, if_exists='append')

@@ -7,6 +7,11 @@ with ``encodings``, ``x_train``, ``y_train``, ``x_test``, ``y_test`` and the dec
 (the figshare assets and the MNIST download are not available offline).
 
     python -m serann_b200.run_experiment -p evolutionary_experiment/parameters/example.json --synthetic --results-dir out
+    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 -m serann_b200.run_experiment \
+        -p evolutionary_experiment/parameters/full_experiment.json --synthetic --results-dir out
+
+Under torchrun every rank (one per GPU) builds the same generation table from the same seeded ``np.random`` stream, trains
+its cost-balanced shard, and one NCCL all-gather per generation brings every rank all results; rank 0 writes the SQLite file.
 """
 from __future__ import annotations
 
@@ -32,9 +37,12 @@ def get_args(argv=None):
     ap.add_argument('-a', '--workers-pool-address', required=False, help='ignored (no worker farm)')
     ap.add_argument('--assets', help='.npz with encodings, MNIST arrays and decoder weights')
     ap.add_argument('--synthetic', action='store_true', help='synthetic data, random-init autoencoder, generator sources')
+    ap.add_argument('--synthetic-rows', default='60000,10000', help='train,test rows of the synthetic data set')
     ap.add_argument('--results-dir', default='data/experiment_results')
     ap.add_argument('--num-generations', type=int, help='override num_generations of the parameters file')
     ap.add_argument('--num-seranns', type=int, help='override num_seranns of the parameters file')
+    ap.add_argument('--devices', help='comma-separated CUDA devices for a single-process run (default: LOCAL_RANK or 0); '
+                                      'under torchrun every rank takes its LOCAL_RANK device and the population is sharded over the ranks')
     return ap.parse_args(argv)
 
 
@@ -52,7 +60,8 @@ def load_assets(args, params):
     if not args.synthetic:
         raise SystemExit('pass --assets FILE.npz or --synthetic (the reference assets are not available offline)')
     from .generator import sample_population
-    data = synthetic_dataset(image_dims=tuple(params['classification_image_dimensions']),
+    n_train, n_test = (int(v) for v in args.synthetic_rows.split(','))
+    data = synthetic_dataset(n_train=n_train, n_test=n_test, image_dims=tuple(params['classification_image_dimensions']),
                              genotype_size=params['genotype_size'], n_classes=params['num_classification_classes'])
     weights = synthetic_decoder_weights(params['genotype_size'], params['max_tokens'])
     state = {'seed': 0}
@@ -72,18 +81,23 @@ def main(argv=None):
     from .experiment_db import ExperimentDB
     from .worker import B200PopulationWorker, InProcessPool
 
+    from .parallel import ShardContext
     seed = int(args.random_seed or RANDOM_SEED)
-    np.random.seed(seed)
+    np.random.seed(seed)                      # every rank seeds the driver's stream alike: selection runs redundantly
+    ctx = ShardContext.from_env()             # torchrun: one process per GPU; plain python: a single rank
     results = Path(args.results_dir)
     results.mkdir(exist_ok=True, parents=True)
+    # rank 0 owns the results file; the other ranks compute the same tables and drop them
+    make_db = (lambda path: ExperimentDB(path)) if ctx.rank == 0 else (lambda path: ExperimentDB(path, read_only=True))
     info = {}
     if args.resume_experiment_id is None:
-        experiment_id = str(uuid4())
+        experiment_id = ctx.allgather_bytes(str(uuid4()).encode())[0].decode()      # rank 0's draw, on every rank
         with open(args.parameters) as f:
-            info = {'parameters': json.load(f), 'experiment_db': ExperimentDB(results / f'{experiment_id}.sqlite')}
+            info = {'parameters': json.load(f), 'experiment_db': make_db(results / f'{experiment_id}.sqlite')}
     else:
         experiment_id = args.resume_experiment_id
-        db = ExperimentDB(results / f'{experiment_id}.sqlite')
+        ctx.barrier()
+        db = make_db(results / f'{experiment_id}.sqlite')
         start = db.get_generations_count()
         if args.parameters is not None:
             with open(args.parameters) as f:
@@ -109,10 +123,16 @@ def main(argv=None):
     device = int(os.environ.get('LOCAL_RANK', 0))
     encoder = RibosomalAutoencoder(params['max_tokens'], decoder_weights, genotype_size=params['genotype_size'], device=device)
     pool_args = (B200PopulationWorker, {'args': [params], 'kwargs': {'dataset': data}})
-    with InProcessPool(*pool_args, devices=[device]) as pool:
-        exp = Experiment(experiment_id, data['encodings'], pool, genetic_encoder=encoder, population_source=source, **info)
+    devices = [device]
+    if ctx.world == 1 and args.devices:        # one process driving several GPUs: one worker and one host thread per device
+        devices = [int(d) for d in args.devices.split(',')]
+    with InProcessPool(*pool_args, devices=devices) as pool:
+        exp = Experiment(experiment_id, data['encodings'], pool, genetic_encoder=encoder, population_source=source,
+                         shard_context=ctx, seed_base=seed, **info)
         exp.execute()
-    print('results:', info['experiment_db'].db_path)
+    ctx.barrier()
+    if ctx.rank == 0:
+        print('results:', info['experiment_db'].db_path)
     return exp
 
 

@@ -137,11 +137,21 @@ class B200PopulationWorker:
             waves.append(cur)
         return waves
 
-    def run(self, seranns_info: pd.DataFrame, num_replications: int) -> dict:
-        """Reference ``EvolutionaryExperimentWorker.run`` (experiment_worker.py:45-99)."""
+    def run(self, seranns_info: pd.DataFrame, num_replications: int, fit_seed: Optional[int] = None,
+            individual_seeds: Optional[Dict[str, int]] = None) -> dict:
+        """Reference ``EvolutionaryExperimentWorker.run`` (experiment_worker.py:45-99).
+
+        ``fit_seed`` fixes the row order of the epochs and ``individual_seeds`` (id -> seed) the initial weights of
+        each individual, whatever shard it is in: with both given, a generation evaluated on 1, 2, 4 or 8 GPUs
+        trains every individual from the same weights on the same mini-batches (Keras draws both from unseeded
+        generators, experiment_worker.py:63-70,113-118).  Besides the reference's dict entries the result carries the
+        readout kernel's outputs: ``offspring_bits_by_id`` {id: (R, G) uint8}, ``mutations_by_id`` {id: (R,) int32} and
+        ``offspring_nan_by_id`` {id: (R,) bool} (rows holding a NaN probability)."""
         print('Processing ', len(seranns_info), 'SeRANNs')
         p = self._parameters
+        t_c = time.perf_counter()
         irs, models_info = self._compile(seranns_info)
+        self._compile_s = time.perf_counter() - t_c
         models_info['is_valid'] = ~models_info['loss_balance'].isna()
         models_info['is_overweight'] = False
         for col in ('classification_validation_accuracy', 'classification_training_accuracy',
@@ -155,24 +165,30 @@ class B200PopulationWorker:
         epochs = int(p['training_epochs'])
         n_fit = int(self._n_train * (1.0 - VALIDATION_SPLIT))          # Keras: split_at = int(len * (1 - split))
         n_val = self._n_train - n_fit
-        learning_time = replication_time = 0.0
+        learning_time = replication_time = build_time = test_time = 0.0
         device_ms = 0.0
-        offspring_by_id = {}
+        offspring_by_id, bits_by_id, mut_by_id, nan_by_id = {}, {}, {}, {}
         eng = self._engine
         num_replications = int(num_replications)
         # position of each trainable individual in the reference's joined replicate batch (experiment_worker.py:139-150)
         order = {sid: k for k, sid in enumerate(trainable)}
         repeat = int(np.ceil(len(trainable) * max(num_replications, 1) / self._n_test))
         for wave in self._waves(trainable, irs):
-            eng.build([irs[i] for i in wave], seed=int(self._rng.integers(0, 2 ** 63)))
+            t_b = time.perf_counter()
+            seeds = None if individual_seeds is None else [individual_seeds[i] for i in wave]
+            eng.build([irs[i] for i in wave], seed=int(self._rng.integers(0, 2 ** 63)), individual_seeds=seeds)
+            build_time += time.perf_counter() - t_b
             t0 = time.perf_counter()
             print('Learning started')
-            res = eng.fit(epochs, self._batch, n_val, shuffle_seed=int(self._rng.integers(0, 2 ** 63)))
+            shuffle = int(self._rng.integers(0, 2 ** 63)) if fit_seed is None else int(fit_seed)
+            res = eng.fit(epochs, self._batch, n_val, shuffle_seed=shuffle)
             learning_time += time.perf_counter() - t0
             device_ms += res['device_ms']
             print('Learning done')
             print('Test set evaluation started')
+            t_e = time.perf_counter()
             test_correct, _ = eng.evaluate(1, 0, self._n_test, EVALUATE_BATCH)
+            test_time += time.perf_counter() - t_e
             step_sizes = _chunks(n_fit, self._batch)
             val_sizes = _chunks(n_val, self._batch)
             test_sizes = _chunks(self._n_test, EVALUATE_BATCH)
@@ -190,14 +206,20 @@ class B200PopulationWorker:
                 parents = np.stack([genotype_bits(seranns_info.at[sid, 'genotype']) for sid in wave])
                 rows = np.concatenate([np.arange(order[sid] * num_replications, (order[sid] + 1) * num_replications) for sid in wave])
                 probs, packed, mut = eng.replicate(parents, num_replications, image_index=rows // repeat)
+                bits = _engine.unpack_bits(packed, eng.G)
+                nan_rows = np.isnan(probs.astype(np.float32)).any(axis=-1)
                 for k, sid in enumerate(wave):
                     offspring_by_id[sid] = probs[k]
+                    bits_by_id[sid], mut_by_id[sid], nan_by_id[sid] = bits[k], mut[k], nan_rows[k]
                 replication_time += time.perf_counter() - t0
                 print('Replication done')
-        self.last_stats = {'device_ms_fit': device_ms, 'trained': len(trainable), 'steps': epochs * len(_chunks(n_fit, self._batch))}
+        self.last_stats = {'device_ms_fit': device_ms, 'trained': len(trainable), 'steps': epochs * len(_chunks(n_fit, self._batch)),
+                           'compile_s': self._compile_s, 'build_s': build_time, 'fit_s': learning_time, 'test_s': test_time,
+                           'replicate_s': replication_time}
         out = {'learning_time': learning_time, 'models_info': models_info}
         if num_replications > 0:
-            out.update({'replication_time': replication_time, 'offspring_by_id': offspring_by_id})
+            out.update({'replication_time': replication_time, 'offspring_by_id': offspring_by_id,
+                        'offspring_bits_by_id': bits_by_id, 'mutations_by_id': mut_by_id, 'offspring_nan_by_id': nan_by_id})
         return out
 
 
@@ -207,6 +229,8 @@ class InProcessPool:
     object per visible GPU, jobs run in this process.  Extra positional arguments of the reference's
     constructor (password, address, port, timeouts; ``run_experiment.py:102-104``) are accepted and ignored.
     """
+
+    accepts_seeds = True         # jobs may carry kwargs (fit_seed, individual_seeds): the reference's farm passes args only
 
     def __init__(self, worker_cls, init_args: Optional[dict] = None, *_pool_args, devices: Optional[Sequence[int]] = None,
                  **_pool_kwargs):
@@ -235,9 +259,34 @@ class InProcessPool:
         return len(self._devices)
 
     def imap_unordered(self, jobs: Iterable[dict]):
-        for k, job in enumerate(jobs):
-            w = self._workers[k % len(self._workers)]
-            yield w.run(*job.get('args', []), **job.get('kwargs', {}))
+        """Jobs are dealt round-robin to the workers; each worker (one GPU) runs its jobs in its own host thread - the
+        C ABI calls release the GIL, so the devices work at the same time - and results come back in completion order."""
+        jobs = list(jobs)
+        if len(self._workers) == 1 or len(jobs) <= 1:
+            for k, job in enumerate(jobs):
+                w = self._workers[k % len(self._workers)]
+                yield w.run(*job.get('args', []), **job.get('kwargs', {}))
+            return
+        import queue
+        import threading
+        done: 'queue.Queue' = queue.Queue()
+
+        def serve(widx):
+            for k in range(widx, len(jobs), len(self._workers)):
+                try:
+                    done.put((None, self._workers[widx].run(*jobs[k].get('args', []), **jobs[k].get('kwargs', {}))))
+                except BaseException as e:           # shipped to the caller like the farm ships worker exceptions
+                    done.put((e, None))
+        threads = [threading.Thread(target=serve, args=(i,), daemon=True) for i in range(len(self._workers))]
+        for t in threads:
+            t.start()
+        for _ in jobs:
+            err, res = done.get()
+            if err is not None:
+                raise err
+            yield res
+        for t in threads:
+            t.join()
 
     def update_workers(self, data: dict):
         for w in self._workers:
