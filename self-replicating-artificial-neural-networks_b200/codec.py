@@ -39,6 +39,8 @@ class RibosomalAutoencoder:
                                                     _engine._ptr(dk), _engine._ptr(db), _engine._ptr(bn2),
                                                     C.byref(self._d)))
         self.last_device_ms = 0.0
+        self.h2d_bytes = sum(a.nbytes for a in (ck, cb, bn1, dk, db, bn2))
+        self.d2h_bytes = 0
 
     def close(self):
         if getattr(self, '_d', None):
@@ -75,6 +77,8 @@ class RibosomalAutoencoder:
         ms = C.c_float()
         _engine._check(self._lib.srn_decoder_decode(self._d, _engine._ptr(bits), len(bits), _engine._ptr(tokens), C.byref(ms)))
         self.last_device_ms = ms.value
+        self.h2d_bytes += bits.nbytes
+        self.d2h_bytes += tokens.nbytes
         return tokens.astype(np.int64)
 
     def sequence_to_string(self, serann_sequences) -> List[str]:

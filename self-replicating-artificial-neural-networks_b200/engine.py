@@ -174,6 +174,9 @@ class Engine:
         self.n = 0
         self.irs: List[SerannIR] = []
         self.n_train = self.n_test = 0
+        # bytes this handle has moved between host and device through the ABI (counted from the arrays passed)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
 
     def close(self):
         if getattr(self, '_h', None) is not None and self._h:
@@ -208,7 +211,7 @@ class Engine:
         _check(self._lib.srn_set_dataset(self._h, _ptr(a[0]), _ptr(a[1]), _ptr(a[2]), a[3],
                                          _ptr(b[0]), _ptr(b[1]), _ptr(b[2]), b[3]))
         self.n_train, self.n_test = a[3], b[3]
-        self.h2d_bytes = sum(v.nbytes for v in (*a[:3], *b[:3]) if v is not None)
+        self.h2d_bytes += sum(v.nbytes for v in (*a[:3], *b[:3]) if v is not None)
 
     # ---- population
     def build(self, irs: Sequence[SerannIR], seed: int = 0, individual_seeds: Optional[Sequence[int]] = None):
@@ -228,6 +231,7 @@ class Engine:
         else:
             _check(self._lib.srn_build(self._h, arr, _ptr(offs), _ptr(lb), len(irs), C.c_uint64(seed & (2 ** 64 - 1))))
         self.n, self.irs = len(irs), list(irs)
+        self.h2d_bytes += C.sizeof(arr) + offs.nbytes + lb.nbytes
 
     def parameters_count(self, i: int) -> int:
         return int(self._lib.srn_parameters_count(self._h, i))
@@ -273,6 +277,8 @@ class Engine:
             p = np.ascontiguousarray(np.asarray(perms, dtype=np.int32).reshape(epochs, n_fit))
         _check(self._lib.srn_fit(self._h, epochs, batch, n_val, _ptr(p), C.c_uint64(shuffle_seed), max_steps,
                                  _ptr(tc), _ptr(tl), _ptr(vc), _ptr(vm), C.byref(ms)))
+        self.h2d_bytes += 4 * epochs * n_fit                      # the epochs' row orders (drawn on the host when perms is None)
+        self.d2h_bytes += tc.nbytes + tl.nbytes + vc.nbytes + vm.nbytes
         return {'train_correct': tc, 'train_loss': tl, 'val_correct': vc, 'val_mse_sum': vm, 'device_ms': ms.value,
                 'steps_per_epoch': S, 'val_chunks': V}
 
@@ -281,6 +287,7 @@ class Engine:
         c = np.zeros((slots, self.n), dtype=np.int32)
         m = np.zeros((slots, self.n), dtype=np.float32)
         _check(self._lib.srn_evaluate(self._h, split, start, rows, chunk, _ptr(c), _ptr(m)))
+        self.d2h_bytes += c.nbytes + m.nbytes
         return c, m
 
     def replicate(self, parent_bits: np.ndarray, R: int, image_index: Optional[np.ndarray] = None,
@@ -292,6 +299,8 @@ class Engine:
         mut = np.empty((self.n, R), dtype=np.int32)
         idx = None if image_index is None else np.ascontiguousarray(np.asarray(image_index, dtype=np.int32))
         _check(self._lib.srn_replicate(self._h, _ptr(pb), R, _ptr(idx), _ptr(probs), _ptr(packed), _ptr(mut)))
+        self.h2d_bytes += pb.nbytes + 4 * self.n * R
+        self.d2h_bytes += (probs.nbytes if probs is not None else 0) + packed.nbytes + mut.nbytes
         return probs, packed, mut
 
     def forward_logits(self, split: int, start: int, rows: int, training: bool = False) -> np.ndarray:

@@ -60,7 +60,7 @@ def pairwise_genotype_distances(genotypes: np.ndarray):
 class Experiment:
     def __init__(self, experiment_id, serann_dataset, workers_pool, experiment_db, parameters, genetic_encoder,
                  start_generation: int = 0, population_source=None, shard_context: Optional[ShardContext] = None,
-                 seed_base: int = 0):
+                 seed_base: int = 0, nan_offspring: str = 'keep'):
         """``genetic_encoder``: a ``RibosomalAutoencoder`` (reference builds it itself from config paths,
         ``experiment.py:36``).  ``population_source``: optional callable ``(n) -> list of source strings``; when
         given, the next generation's *source codes* come from it instead of from the decoder - needed with a
@@ -75,6 +75,13 @@ class Experiment:
         self._population_source = population_source
         self._experiment_db.save_execution_info(datetime.now(), self._parameters)
         self._workers_pool = workers_pool
+        # 'keep' = the reference: an individual whose BatchNorm statistics overflowed (fp16 sample size) emits NaN
+        # probabilities, its offspring genotypes are NaN and decoding them raises IndexError (ribosomal_autoencoder.py:123).
+        # 'zero' keeps the run alive: NaN loci become 0, as the readout kernel packs them (such offspring differ from
+        # their parent in every counted locus); used by the synthetic benchmark, whose generator mix holds ~36 % such nets.
+        if nan_offspring not in ('keep', 'zero'):
+            raise ValueError("nan_offspring must be 'keep' or 'zero'")
+        self._nan_offspring = nan_offspring
         self.generation_seconds = []
         # one process per GPU (torchrun): this rank trains its shard of every generation, one all-gather per generation
         self._ctx = shard_context or ShardContext()
@@ -197,17 +204,15 @@ class Experiment:
         fit_seed = stable_seed(self._seed_base, 'fit', self._generation_index) >> 1
         return fit_seed, {i: stable_seed(self._seed_base, 'init', i) for i in generation.index}
 
-    @staticmethod
-    def _offspring_from_kernel(result: dict) -> dict:
+    def _offspring_from_kernel(self, result: dict) -> dict:
         """{id: (R, G) float16 of 0.0 / 1.0} from the readout kernel's bits (what ``np.round(np.clip(p, 0, 1))`` gives,
         experiment.py:210); a row that held a NaN probability stays NaN, as it does in the reference."""
         out = {}
         for sid, bits in result.get('offspring_bits_by_id', {}).items():
             g = bits.astype(np.float16)
             nan = np.asarray(result['offspring_nan_by_id'][sid], dtype=bool)
-            if nan.any():
-                p = result['offspring_by_id'][sid]
-                g = np.where(np.isnan(p.astype(np.float32)), np.float16(np.nan), g)
+            if nan.any() and self._nan_offspring == 'keep':
+                g[nan] = np.float16(np.nan)          # row granularity, as the all-gather carries it (an F6 row is all NaN)
             out[sid] = g
         return out
 
@@ -272,7 +277,7 @@ class Experiment:
             for k, sid in enumerate(ids):
                 if has[k]:
                     g = bits[k].astype(np.float16)
-                    if nan[k].any():         # F6 individuals: every probability of a row is NaN, and so is the stored genotype
+                    if nan[k].any() and self._nan_offspring == 'keep':     # F6 individuals: a NaN row stays NaN in the stored genotype
                         g[nan[k].astype(bool)] = np.float16(np.nan)
                     offspring_by_id[sid] = g
             times['learning_times'].append(float(t[0]))
