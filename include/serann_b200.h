@@ -169,7 +169,11 @@ int srn_forward_logits(srn_engine* h, int32_t split, int32_t start, int32_t rows
 /* Ribosomal autoencoder decode: replaces RiboAeProcess.decode (ribosomal_autoencoder.py:119-126) over the
  * decoder of ribosomal_autoencoder/model.py:35-48.  Weights fp32 in Keras layouts: conv kernel (5, 2, 32),
  * conv bias 32, BN1 gamma/beta/mean/var 32 each, dense kernel (96*32, max_tokens*vocab), dense bias,
- * BN2 gamma/beta/mean/var `vocab` each. */
+ * BN2 gamma/beta/mean/var `vocab` each.  Creation folds the binary-input convolution and the first BN into the
+ * Dense kernel (a table over the five-bit windows, accumulated in double) and splits it into two fp16 halves; decode
+ * is then one tcgen05 GEMM with the second BN and the per-token argmax in its epilogue, plus an exact (double)
+ * recomputation of the tokens whose top-two margin is too small for the split to be trusted.  Shapes the tensor-core
+ * kernel does not serve (vocab not a multiple of 8, genotype_size > 104) run the exact kernel for every token. */
 int srn_decoder_create(int32_t device, int32_t genotype_size, int32_t max_tokens, int32_t vocab,
                        const float* conv_kernel, const float* conv_bias, const float* bn1,
                        const float* dense_kernel, const float* dense_bias, const float* bn2,
@@ -178,6 +182,9 @@ void srn_decoder_destroy(srn_decoder* d);
 /* bits [n][genotype_size] 0/1 -> tokens [n][max_tokens] (argmax over the vocabulary, first maximum wins).
  * device_ms (may be NULL) receives the device time of the decode kernels. */
 int srn_decoder_decode(srn_decoder* d, const uint8_t* bits, int32_t n, int32_t* tokens, float* device_ms);
+/* Of the last srn_decoder_decode call: tokens that went through the exact recomputation, and whether the tensor-core
+ * kernel served the call (no reference counterpart: bench.py and the tests report them). */
+int srn_decoder_stats(srn_decoder* d, int64_t* rechecked, int32_t* tensor_path);
 
 /* Stand-alone readout (experiment.py:210,229; serann_evaluation/logic.py:199-203,223):
  * probs [rows][G] fp16 -> packed bits [rows][ceil(G/32)], mutations [rows] vs parent_bits [rows/rows_per_parent][G]. */

@@ -17,7 +17,7 @@ PKG = pathlib.Path(__file__).resolve().parent
 ROOT = PKG.parent
 CSRC = PKG / 'csrc'
 LIB = PKG / 'libserann_b200.so'
-SOURCES = ['srn_engine.cu', 'srn_ops.cu']
+SOURCES = ['srn_engine.cu', 'srn_ops.cu', 'srn_decode.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=default', '--expt-relaxed-constexpr']
 

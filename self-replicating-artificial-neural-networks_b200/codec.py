@@ -77,6 +77,9 @@ class RibosomalAutoencoder:
         ms = C.c_float()
         _engine._check(self._lib.srn_decoder_decode(self._d, _engine._ptr(bits), len(bits), _engine._ptr(tokens), C.byref(ms)))
         self.last_device_ms = ms.value
+        re, tp = C.c_int64(), C.c_int32()
+        _engine._check(self._lib.srn_decoder_stats(self._d, C.byref(re), C.byref(tp)))
+        self.last_stats = {'rechecked_tokens': int(re.value), 'tokens': int(tokens.size), 'tensor_core_kernel': bool(tp.value)}
         self.h2d_bytes += bits.nbytes
         self.d2h_bytes += tokens.nbytes
         return tokens.astype(np.int64)

@@ -25,6 +25,7 @@
 #include "srn_gemm_tc.cuh"
 #include "srn_kernels.cuh"
 #include "srn_host.h"
+#include "srn_tma.h"
 
 namespace srn {
 
@@ -981,33 +982,6 @@ extern "C" int srn_debug_set_tensor_cores(int32_t on) {
 
 // ------------------------------------------------------------------ launch plan per batch size
 // ------------------------------------------------------------------ TMA tensor maps of Dense problems
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn encode_tiled_fn() {
-    static EncodeTiledFn fn = nullptr;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
-        void* f = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (getenv("SRN_NO_TMA") == nullptr &&
-            cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(f);
-    }
-    return fn;
-}
-// row-major fp16 matrix [rows][cols] with a row pitch (elements), box = 64 columns x box_rows rows, swizzle-128B
-static bool encode_matrix(CUtensorMap* m, const void* base, long long rows, long long cols, long long pitch, int box_rows) {
-    EncodeTiledFn fn = encode_tiled_fn();
-    if (!fn || !base || rows <= 0 || cols <= 0 || (pitch * 2) % 16 != 0 || ((uintptr_t)base & 15) != 0) return false;
-    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    const cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
-    const cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
-    const cuuint32_t estr[2] = {1u, 1u};
-    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-}
 // The two maps (A operand, B operand) of one pass of a Dense problem whose operands are plain matrices; false = gather path
 static bool dense_tensor_maps(const Prob& p, int nb, int mode, int BN, CUtensorMap* m) {
     static const int mask = getenv("SRN_TMA_MASK") ? atoi(getenv("SRN_TMA_MASK")) : 7;     // bit per pass (fwd, dgrad, wgrad): experiments

@@ -1,4 +1,4 @@
-// Stand-alone entry points: ribosomal-autoencoder decode, genotype readout, BatchNormalizationF16 forward.
+// Stand-alone entry points: edit distance, genotype readout, BatchNormalizationF16 forward (the autoencoder decode is srn_decode.cu).
 #include <algorithm>
 #include <atomic>
 #include <cmath>
@@ -6,7 +6,6 @@
 #include <vector>
 
 #include "../../include/serann_b200.h"
-#include "srn_gemm_simt.cuh"
 #include "srn_kernels.cuh"
 #include "srn_host.h"
 
@@ -24,165 +23,6 @@ static int check_device(int device) {
     if (e != cudaSuccess || count == 0) return fail(SRN_ERR_CUDA, "no CUDA device (%s); this library has no CPU path", cudaGetErrorString(e));
     if (device < 0 || device >= count) return fail(SRN_ERR_ARG, "device %d of %d", device, count);
     CK(cudaSetDevice(device));
-    return SRN_OK;
-}
-
-// ------------------------------------------------------------------ ribosomal autoencoder decode (fp32)
-// generative_net in inference mode (reference ribosomal_autoencoder/model.py:35-48):
-//   one_hot(bits) (n,G,2) -> Conv1D(32, 5) -> BN -> Flatten -> Dense(T*V) -> Reshape(T,V) -> BN -> argmax
-// The input is binary, so the convolution is a table lookup: out[l][f] = bias[f] + sum_t K[t][bit(l+t)][f].
-struct srn_decoder {
-    int device, G, T, V, L, Kd, Nd;          // L = G - 4 conv positions, Kd = L*32, Nd = T*V
-    float *conv_k, *conv_b, *bn1, *dense_k, *dense_b, *bn2;   // device
-    float* hbuf = nullptr; float* zbuf = nullptr; uint8_t* bits = nullptr; int* tokens = nullptr;
-    int cap = 0;                              // rows the scratch buffers hold
-};
-
-constexpr int DEC_F = 32, DEC_KW = 5;
-constexpr float KERAS_BN_EPS = 1e-3f;
-
-// h[n][l][f] = BN1(conv(one_hot(bits)))   (tf.nn.batch_normalization: x * inv + (beta - mean * inv))
-__global__ void k_dec_conv_bn(const uint8_t* __restrict__ bits, int n, int G, int L, const float* __restrict__ ck,
-                              const float* __restrict__ cb, const float* __restrict__ bn1, float* __restrict__ h) {
-    long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long total = (long long)n * L * DEC_F;
-    if (e >= total) return;
-    const int f = (int)(e % DEC_F);
-    const int l = (int)((e / DEC_F) % L);
-    const long long s = e / ((long long)DEC_F * L);
-    float acc = 0.f;
-#pragma unroll
-    for (int t = 0; t < DEC_KW; ++t) {
-        const int bit = bits[s * G + l + t] ? 1 : 0;
-        acc += ck[(t * 2 + bit) * DEC_F + f];          // Keras Conv1D kernel layout (5, 2, 32)
-    }
-    acc += cb[f];
-    const float inv = (1.0f / sqrtf(bn1[3 * DEC_F + f] + KERAS_BN_EPS)) * bn1[f];
-    h[e] = acc * inv + (bn1[DEC_F + f] - bn1[2 * DEC_F + f] * inv);
-}
-
-// z[n][Nd] = BN2(h @ W + b), BN2 per vocabulary index (column % V); fp32 SIMT 64x64 tiles
-__global__ void __launch_bounds__(SIMT_THREADS)
-k_dec_dense_bn(const float* __restrict__ h, const float* __restrict__ W, const float* __restrict__ b,
-               const float* __restrict__ bn2, int n, int K, int N, int V, float* __restrict__ z) {
-    constexpr int BM = 64, BN = 64;
-    __shared__ __align__(16) float As[SIMT_BK][BM + 4];
-    __shared__ __align__(16) float Bs[SIMT_BK][BN + 4];
-    const int tilesN = (N + BN - 1) / BN;
-    const int m0 = (blockIdx.x / tilesN) * BM, n0 = (blockIdx.x % tilesN) * BN;
-    const int tid = threadIdx.x, ty = tid / 16, tx = tid % 16;
-    float acc[4][4] = {};
-    for (int k0 = 0; k0 < K; k0 += SIMT_BK) {
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            int m = m0 + tid / 16 + 16 * r, k = k0 + tid % 16;
-            As[tid % 16][tid / 16 + 16 * r] = (m < n && k < K) ? h[(long long)m * K + k] : 0.f;
-            int kk = k0 + tid / 64 + 4 * r, c = n0 + tid % 64;
-            Bs[tid / 64 + 4 * r][tid % 64] = (kk < K && c < N) ? W[(long long)kk * N + c] : 0.f;
-        }
-        __syncthreads();
-        simt_mma<BM, BN>(As, Bs, acc, ty, tx);
-        __syncthreads();
-    }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        int m = m0 + ty * 4 + i;
-        if (m >= n) continue;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            int c = n0 + tx * 4 + j;
-            if (c >= N) continue;
-            const int v = c % V;
-            const float inv = (1.0f / sqrtf(bn2[3 * V + v] + KERAS_BN_EPS)) * bn2[v];
-            z[(long long)m * N + c] = (acc[i][j] + b[c]) * inv + (bn2[V + v] - bn2[2 * V + v] * inv);
-        }
-    }
-}
-
-// tokens[n][T] = argmax over V (first maximum wins; log-softmax is argmax-neutral)
-__global__ void k_dec_argmax(const float* __restrict__ z, long long rows, int V, int* __restrict__ tokens) {
-    long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= rows) return;
-    const float* p = z + r * V;
-    float best = p[0]; int arg = 0;
-    for (int v = 1; v < V; ++v) { float x = p[v]; if (x > best) { best = x; arg = v; } }
-    tokens[r] = arg;
-}
-
-static int upload(float** dst, const float* src, size_t n) {
-    CK(cudaMalloc(dst, n * sizeof(float)));
-    CK(cudaMemcpy(*dst, src, n * sizeof(float), cudaMemcpyHostToDevice));
-    return SRN_OK;
-}
-
-extern "C" int srn_decoder_create(int32_t device, int32_t genotype_size, int32_t max_tokens, int32_t vocab,
-                                  const float* conv_kernel, const float* conv_bias, const float* bn1,
-                                  const float* dense_kernel, const float* dense_bias, const float* bn2,
-                                  srn_decoder** out) {
-    if (!out || !conv_kernel || !conv_bias || !bn1 || !dense_kernel || !dense_bias || !bn2) return fail(SRN_ERR_ARG, "srn_decoder_create: null argument");
-    if (genotype_size < DEC_KW || max_tokens <= 0 || vocab <= 0) return fail(SRN_ERR_ARG, "srn_decoder_create: bad dimensions");
-    int rc = check_device(device);
-    if (rc) return rc;
-    srn_decoder* d = new srn_decoder();
-    d->device = device; d->G = genotype_size; d->T = max_tokens; d->V = vocab;
-    d->L = genotype_size - DEC_KW + 1; d->Kd = d->L * DEC_F; d->Nd = max_tokens * vocab;
-    if ((rc = upload(&d->conv_k, conv_kernel, DEC_KW * 2 * DEC_F))) return rc;
-    if ((rc = upload(&d->conv_b, conv_bias, DEC_F))) return rc;
-    if ((rc = upload(&d->bn1, bn1, 4 * DEC_F))) return rc;
-    if ((rc = upload(&d->dense_k, dense_kernel, (size_t)d->Kd * d->Nd))) return rc;
-    if ((rc = upload(&d->dense_b, dense_bias, d->Nd))) return rc;
-    if ((rc = upload(&d->bn2, bn2, 4 * (size_t)vocab))) return rc;
-    *out = d;
-    return SRN_OK;
-}
-
-extern "C" void srn_decoder_destroy(srn_decoder* d) {
-    if (!d) return;
-    cudaSetDevice(d->device);
-    cudaFree(d->conv_k); cudaFree(d->conv_b); cudaFree(d->bn1); cudaFree(d->dense_k); cudaFree(d->dense_b); cudaFree(d->bn2);
-    cudaFree(d->hbuf); cudaFree(d->zbuf); cudaFree(d->bits); cudaFree(d->tokens);
-    delete d;
-}
-
-extern "C" int srn_decoder_decode(srn_decoder* d, const uint8_t* bits, int32_t n, int32_t* tokens, float* device_ms) {
-    if (!d || !bits || !tokens || n < 0) return fail(SRN_ERR_ARG, "srn_decoder_decode: bad argument");
-    if (device_ms) *device_ms = 0.f;
-    if (n == 0) return SRN_OK;
-    CK(cudaSetDevice(d->device));
-    const int CH = 8192;                       // rows per pass: bounds the logits scratch to CH * T * V floats
-    const int cap = std::min(n, CH);
-    if (cap > d->cap) {
-        cudaFree(d->hbuf); cudaFree(d->zbuf); cudaFree(d->bits); cudaFree(d->tokens);
-        CK(cudaMalloc(&d->hbuf, (size_t)cap * d->Kd * sizeof(float)));
-        CK(cudaMalloc(&d->zbuf, (size_t)cap * d->Nd * sizeof(float)));
-        CK(cudaMalloc(&d->bits, (size_t)cap * d->G));
-        CK(cudaMalloc(&d->tokens, (size_t)cap * d->T * sizeof(int)));
-        d->cap = cap;
-    }
-    cudaEvent_t e0, e1;
-    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-    float total = 0.f;
-    for (int s = 0; s < n; s += CH) {
-        const int m = std::min(CH, n - s);
-        CK(cudaMemcpy(d->bits, bits + (size_t)s * d->G, (size_t)m * d->G, cudaMemcpyHostToDevice));
-        CK(cudaEventRecord(e0, 0));
-        const long long he = (long long)m * d->Kd;
-        k_dec_conv_bn<<<(unsigned)((he + 255) / 256), 256>>>(d->bits, m, d->G, d->L, d->conv_k, d->conv_b, d->bn1, d->hbuf);
-        const int tiles = ((m + 63) / 64) * ((d->Nd + 63) / 64);
-        k_dec_dense_bn<<<tiles, SIMT_THREADS>>>(d->hbuf, d->dense_k, d->dense_b, d->bn2, m, d->Kd, d->Nd, d->V, d->zbuf);
-        const long long rows = (long long)m * d->T;
-        k_dec_argmax<<<(unsigned)((rows + 255) / 256), 256>>>(d->zbuf, rows, d->V, d->tokens);
-        g_launches.fetch_add(3);
-        CK(cudaEventRecord(e1, 0));
-        CK(cudaEventSynchronize(e1));
-        CK(cudaGetLastError());
-        float ms = 0.f;
-        CK(cudaEventElapsedTime(&ms, e0, e1));
-        total += ms;
-        CK(cudaMemcpy(tokens + (size_t)s * d->T, d->tokens, (size_t)m * d->T * sizeof(int), cudaMemcpyDeviceToHost));
-    }
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
-    if (device_ms) *device_ms = total;
     return SRN_OK;
 }
 

@@ -77,6 +77,7 @@ def load_library(rebuild: bool = False) -> C.CDLL:
     lib.srn_decoder_destroy.argtypes = [vp]
     lib.srn_decoder_destroy.restype = None
     lib.srn_decoder_decode.argtypes = [vp, vp, i32, vp, C.POINTER(C.c_float)]
+    lib.srn_decoder_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(i32)]
     lib.srn_readout.argtypes = [i32, vp, vp, i32, i32, i32, vp, vp]
     lib.srn_bn_train_forward.argtypes = [i32, vp, i64, i32, vp, vp, vp, vp, vp]
     lib.srn_bn_train_forward_noalloc.argtypes = [i32, vp, vp, i64, i32, vp, vp, vp, vp, vp]
