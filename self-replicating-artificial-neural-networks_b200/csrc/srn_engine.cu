@@ -992,6 +992,7 @@ static bool dense_tensor_maps(const Prob& p, int nb, int mode, int BN, CUtensorM
     const bool a_ok = HW == 1 || p.in_bs == HW * p.Cs, g_ok = HoWo == 1 || p.out_bs == HoWo * p.Fs;
     const long long M = (long long)nb * HW;
     const long long a_pitch = HW == 1 ? p.in_bs : p.Cs, g_pitch = HoWo == 1 ? p.out_bs : p.Fs;
+    if (mode == TC_FWD && tc_fwd_pack(p, nb, false) > 1) return false;      // packed short reductions: gathered rows, several sub-tiles per stage
     if (mode == TC_FWD)
         return a_ok && encode_matrix(&m[0], p.in, M, p.Cs, a_pitch, 128) && encode_matrix(&m[1], p.w, p.C, p.ldw, p.ldw, 64);
     if (mode == TC_DGRAD)

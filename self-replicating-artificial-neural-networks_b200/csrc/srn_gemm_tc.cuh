@@ -27,6 +27,7 @@
 // use the SCALAR_A variant: the im2col operand is gathered element by element and stored to shared memory
 // with ordinary 16-byte stores; everything else is identical.
 #pragma once
+#include <cstdlib>
 #include <type_traits>
 #include "srn_common.cuh"
 
@@ -71,7 +72,23 @@ __host__ __device__ inline int tc_k_dgrad(const Prob& p) { return p.kh * p.kw * 
 constexpr int TC_SUB = 8;
 __host__ __device__ inline int tc_fwd_sub(const Prob& p, int nb) {
     const int mt = (nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM;
-    return (tc_k_fwd(p) <= TC_BK && mt >= 8 * TC_SUB) ? TC_SUB : 1;
+    // (any reduction length: what a descriptor costs the loaders - fetching it, the geometry set-up, the k table - is
+    // about as much as five k-blocks of copies, so a problem with many row tiles shares it among TC_SUB of them)
+#ifndef __CUDA_ARCH__
+    static const bool only_short = getenv("SRN_SUB_K64") != nullptr;       // A/B: sub-tiles only for one-k-block problems
+    if (only_short && tc_k_fwd(p) > TC_BK) return 1;
+#endif
+    return mt >= 8 * TC_SUB ? TC_SUB : 1;
+}
+// Sub-tiles of such a problem whose reduction is at most 16 (32) elements are packed four (two) to a ring stage: row r of
+// the stage's 128-byte rows holds the k chunks of row r of every packed sub-tile side by side, the MMA of sub-tile q
+// reads them through the matrix descriptor advanced by q * Kpad elements (exactly like a K = 16 step), and the weight
+// tile is loaded once per stage.  One barrier round trip then carries four sub-tiles: with one k-block per tile the
+// pipeline is bound by how many bytes a CTA keeps in flight, not by bandwidth.
+__host__ __device__ inline int tc_fwd_pack(const Prob& p, int nb, bool scalar_a) {
+    if (scalar_a || tc_fwd_sub(p, nb) == 1) return 1;
+    const int K = tc_k_fwd(p);
+    return K <= 16 ? 4 : (K <= 32 ? 2 : 1);
 }
 // Forward problems with few output tiles and a long reduction (Dense on a flattened feature map: 750 rows, K up to
 // 25 000) are split along k so that the reduction runs on many SMs; the partial sums meet in an fp32 scratch tile.
@@ -149,6 +166,9 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, int c0, int c1, uint32_t bar) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n"
                  ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1) : "memory");
@@ -157,6 +177,7 @@ __device__ __forceinline__ void loaders_sync() { asm volatile("bar.sync 1, 256;\
 // try_wait suspends the thread until the phase completes or the time hint (ns) runs out, so a long hint means few
 // polls: every poll is a shared-memory access that competes with the copies and the operand reads
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    const uint32_t hint = 20000u;
     asm volatile(
         "{\n"
         ".reg .pred P1;\n"
@@ -165,7 +186,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         "@P1 bra WAIT_DONE;\n"
         "bra WAIT_LOOP;\n"
         "WAIT_DONE:\n"
-        "}\n" ::"r"(bar), "r"(parity), "r"(20000u) : "memory");
+        "}\n" ::"r"(bar), "r"(parity), "r"(hint) : "memory");
 }
 // same, for waits that last a whole tile (epilogue, accumulator hand-back): back off so that the spinning warps
 // do not take issue slots from the loaders
@@ -181,6 +202,12 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity)
         if (done) break;
         __nanosleep(200);
     }
+}
+// one lane of the (converged) warp
+__device__ __forceinline__ bool elect_one_sync() {
+    uint32_t pred = 0;
+    asm volatile("{\n.reg .pred P1;\nelect.sync _|P1, 0xffffffff;\nselp.u32 %0, 1, 0, P1;\n}\n" : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
@@ -288,7 +315,8 @@ struct __align__(16) TcTile {
     int nsub;          // 128-row sub-tiles m0, m0 + 128, .. covered by this descriptor (forward only, else 1)
     // split-K (forward, few output tiles and a long reduction): this tile covers k-blocks kb0 .. kb0 + nk - 1 of nsplit
     // splits; partial sums meet in the fp32 scratch sk_acc [Mrows][Fs], sk_cnt[4 * sk_tile + warp] counts arrivals
-    int kb0, nsplit, sk_tile, sk_pad;
+    int kb0, nsplit, sk_tile;
+    int pack;          // forward sub-tiles per ring stage (tc_fwd_pack), else 1
     float* sk_acc;
     int* sk_cnt;
     int ph, pw, Hc, Wc, khp, kwp;     // dgrad: residue class of this tile (tc_dgrad_class)
@@ -308,7 +336,8 @@ inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool
     const int KK = p.kh * p.kw;
     const int Kf = SCALAR_A ? KK : KK * p.Cs;
     t.tm = nullptr;
-    t.r0 = 0; t.r1 = 0; t.nsub = 1; t.kb0 = 0; t.nsplit = 1; t.sk_tile = 0; t.sk_pad = 0; t.sk_acc = nullptr; t.sk_cnt = nullptr;
+    t.pack = 1;
+    t.r0 = 0; t.r1 = 0; t.nsub = 1; t.kb0 = 0; t.nsplit = 1; t.sk_tile = 0; t.sk_acc = nullptr; t.sk_cnt = nullptr;
     int Kend = 0;                                           // end of this tile's part of the reduction (elements)
     if (MODE == TC_FWD) {
         t.Mrows = nb * HoWo; t.Ncols = p.F;
@@ -317,6 +346,7 @@ inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool
         tile -= split * per_split;
         t.m0 = (tile / tn) * sub * TC_BM; t.n0 = (tile % tn) * BN;
         t.nsub = min(sub, mt - (tile / tn) * sub);
+        t.pack = tc_fwd_pack(p, nb, SCALAR_A);
         t.nk = (Kf + TC_BK - 1) / TC_BK;
         t.nsplit = SCALAR_A ? 1 : tc_fwd_split(p, nb, BN, smax);
         if (t.nsplit > 1) {
@@ -417,7 +447,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
 
     if (tid == 0) {
         for (int i = 0; i < STAGES; ++i) { mbar_init(sFull + i * 8, TC_LOADERS); mbar_init(sEmpty + i * 8, 1); }
-        for (int i = 0; i < NACC; ++i) { mbar_init(sTFull + i * 8, 1); mbar_init(sTEmpty + i * 8, 128); }
+        for (int i = 0; i < NACC; ++i) { mbar_init(sTFull + i * 8, 1); mbar_init(sTEmpty + i * 8, 4); }
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
     }
     if (warp == TC_LW) tmem_alloc(sSlot, (uint32_t)tmem_cols);
@@ -451,12 +481,12 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
         int a_h[4] = {0, 0, 0, 0}, a_w[4] = {0, 0, 0, 0}, a_base[4] = {0, 0, 0, 0};       // DGRAD: input position of its rows, biased offset
         int w_koff[2] = {0, 0}; bool w_kok[2] = {false, false};    // WGRAD (vector): offsets of this thread's two kk chunks inside the window
         int t_ldw = 0, t_Cs = 1, t_Fs = 1, t_kw = 1, t_W = 1, t_Wo = 1, t_Ho = 1, t_sh = 1, t_sw = 1;
-        int t_Kf = 0, t_n0 = 0, t_out_bs = 0, t_HoWo = 1, t_r0 = 0, t_r1 = 0, t_m0 = 0, t_Cldw = 0, t_C8 = 0;
+        int t_Kf = 0, t_n0 = 0, t_out_bs = 0, t_HoWo = 1, t_r0 = 0, t_r1 = 0, t_m0 = 0, t_Cldw = 0, t_C8 = 0, t_C = 0;
         bool t_lut = false, t_s1 = true, t_flat = false, t_fast = false;
         int t_tap0 = 0, t_tapi = 0, t_tapj = 0, t_dW = 1;        // DGRAD: weight-row offsets of the class's taps, class width
         KGeo geo{};
         FastDiv t_fdrows{}, t_fdw{};
-        int lj = 0, lnk = 0, lsub = 1, t_Mrows = 0, lkb0 = 0;
+        int lj = 0, lnk = 0, lsub = 1, t_Mrows = 0, lkb0 = 0, lpack = 1;
         const char* t_tm = nullptr;
         auto geo_of = [&](const TcTile& T) {
             const Prob& p = T.p;
@@ -488,11 +518,12 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
             const Prob& p = T.p;
             { const __half* in = resolve_in(p, I, l_in_bs); l_in = reinterpret_cast<const char*>(in); }
             lnk = T.nk; lsub = T.nsub; t_Mrows = T.Mrows; lkb0 = T.kb0; t_tm = reinterpret_cast<const char*>(T.tm);
+            lpack = MODE == TC_FWD ? T.pack : 1;
             t_w = reinterpret_cast<const char*>(p.w); t_gout = reinterpret_cast<const char*>(p.gout);
             t_ldw = p.ldw; t_Cs = p.Cs; t_Fs = p.Fs; t_kw = p.kw; t_W = p.W;
             t_Wo = p.Wo; t_Ho = p.Ho; t_sh = p.sh; t_sw = p.sw; t_n0 = T.n0; t_out_bs = p.out_bs; t_HoWo = p.Ho * p.Wo;
             t_r0 = T.r0; t_r1 = T.r1; t_m0 = T.m0;
-            t_Cldw = p.C * p.ldw; t_C8 = p.C - T.n0;
+            t_Cldw = p.C * p.ldw; t_C8 = p.C - T.n0; t_C = p.C;
             const int KK = p.kh * p.kw;
             t_Kf = SCALAR_A ? KK : KK * p.Cs;
             t_lut = (T.kb0 + T.nk) * 8 <= TC_LUT && (MODE == TC_DGRAD ? T.khp * T.kwp : KK) != 1;
@@ -504,7 +535,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
             const int HW = MODE == TC_DGRAD ? T.Hc * T.Wc : p.H * p.W;
             t_dW = T.Wc;
             if (MODE == TC_FWD) {
-                t_cs = (T.nk == 1 && t_Kf <= 32) ? (t_Kf <= 16 ? 1 : 2) : 3;
+                t_cs = (T.nk == 1 && t_Kf <= 32 && T.pack == 1) ? (t_Kf <= 16 ? 1 : 2) : 3;      // packed stages use whole 128-byte rows
                 t_items = 1 << (t_cs - 1);
                 t_ch = lane & ((1 << t_cs) - 1);
                 const int rpw = 32 >> t_cs, subr = lane >> t_cs;
@@ -736,14 +767,41 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
 
         fill_lut(0);
         int sb = 0; uint32_t ph = 1;     // ring stage and the parity a fresh "empty" barrier passes immediately
+        auto stage_issued = [&]() {
+            cp_async_arrive_noinc(sFull + sb * 8);       // fires when this thread's copies for the stage have landed
+            if (++sb == STAGES) { sb = 0; ph ^= 1u; }
+        };
         for (lj = 0; lj < my_tiles; ++lj) {
             loader_enter_tile();
+            if (MODE == TC_FWD && lpack > 1) {
+                // packed short reductions: chunk column ch belongs to sub-tile s + ch / cps, k chunk ch % cps
+                const int cps = 8 / lpack, q = ch / cps, kc = ch - q * cps;
+                const bool kvalid = kc * 8 < t_Kf;
+                for (int s = 0; s < lsub; s += lpack) {
+                    fwd_rows(t_m0 + (s + q) * TC_BM);
+                    const bool sub_ok = s + q < lsub && kvalid;
+                    mbar_wait(sEmpty + sb * 8, ph);
+                    const uint32_t aS = sA + sb * TC_A_BYTES, bS = sB + sb * B_BYTES;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const bool ok = sub_ok && a_ok[i];
+                        cp_async16_ca(aS + k_dst + i * 4096, l_in + (ok ? a_off[i] + (uint32_t)(kc * 16) : 0u), ok);
+                    }
+                    load_b_mn(bS, (t_Kf + 15) & ~15, [&](int kl, int& left) -> const char* {
+                        const bool kok = kl < t_C;
+                        left = kok ? 2 * (t_ldw - t_n0) : 0;
+                        return t_w + (kok ? 2u * (uint32_t)(kl * t_ldw + t_n0) : 0u);
+                    });
+                    stage_issued();
+                }
+                continue;
+            }
             for (int s = 0; s < lsub; ++s) {
                 if (MODE == TC_FWD) fwd_rows(t_m0 + s * TC_BM);
                 for (int kb = lkb0; kb < lkb0 + lnk; ++kb) {
                     mbar_wait(sEmpty + sb * 8, ph);
                     if (t_tm) {
-                        // row-major operands: one thread issues the tile copies, everybody else just arrives
+                        // row-major operands: one thread issues the tile copies
                         const uint32_t bar = sFull + sb * 8;
                         if (tid == 0) {
                             const uint32_t aS = sA + sb * TC_A_BYTES, bS = sB + sb * B_BYTES;
@@ -769,50 +827,86 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                         } else {
                             mbar_arrive(bar);
                         }
+                        if (++sb == STAGES) { sb = 0; ph ^= 1u; }
                     } else {
                         if (t_fast) load_stage(sb, kb, std::true_type{});
                         else load_stage(sb, kb, std::false_type{});
                         if (SCALAR_A) fence_proxy_async();       // the element-wise gather used ordinary shared-memory stores
-                        cp_async_arrive_noinc(sFull + sb * 8);   // fires when this thread's copies for the stage have landed
+                        stage_issued();
                     }
-                    if (++sb == STAGES) { sb = 0; ph ^= 1u; }
                 }
             }
         }
         cp_async_wait_all();
     } else if (warp == TC_LW) {
         // =================================================================== MMA issuer
-        if (lane == 0) {
+        // The whole warp walks the loop in lock step and one elected lane issues: every operand of the tensor-core
+        // instructions is then a warp-uniform value that the compiler keeps in uniform registers.  Run under
+        // `if (lane == 0)` the same loop cost ~145 instructions per k-block (a uniformity "waterfall" around every
+        // UTCHMMA / UTCBAR), and with tiles of one to five k-blocks of a 128 x 32 tile (32 tensor-pipe cycles each)
+        // that single thread's instruction stream bounded the whole kernel (ncu: the issuer warp never stalled).
+        {
+            const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
+            auto bcast = [](int v) { return __shfl_sync(0xffffffffu, v, 0); };
             int st = 0; uint32_t fph = 0;     // ring stage and the parity of its "full" barrier
             // K-major operands advance 32 bytes per K = 16 step inside the 128-byte rows, MN-major ones two 8-k atoms
             const uint64_t dA0 = MODE == TC_WGRAD ? umma_desc_sw128(sA, 8192, 1024) : umma_desc_sw128(sA, 16, 1024);
             const uint64_t dB0 = MODE == TC_DGRAD ? umma_desc_sw128(sB, 16, 1024) : umma_desc_sw128(sB, 8192, 1024);
-            const uint64_t a_step = MODE == TC_WGRAD ? (2048 >> 4) : (32 >> 4), b_step = MODE == TC_DGRAD ? (32 >> 4) : (2048 >> 4);
+            constexpr uint64_t a_step = MODE == TC_WGRAD ? (2048 >> 4) : (32 >> 4), b_step = MODE == TC_DGRAD ? (32 >> 4) : (2048 >> 4);
             int jj = 0;                       // accumulator hand-overs so far (one per sub-tile)
             for (int j = 0; j < my_tiles; ++j) {
-                int nk = 1, klast = 4, nsub = 1; uint32_t idesc = 0;
+                // descriptor j was stored by the loaders before they published the tile's first stage
+                mbar_wait(sFull + st * 8, fph);
+                const TcTile& T = ring[j % TC_RING];
+                const int nk = bcast(T.nk), klast = bcast(T.klast), nsub = bcast(T.nsub);
+                const int pack = MODE == TC_FWD ? bcast(T.pack) : 1;
+                const uint32_t idesc = umma_idesc(MODE == TC_WGRAD ? 1 : 0, MODE == TC_DGRAD ? 0 : 1, bcast(T.n_umma));
+                if (MODE == TC_FWD && pack > 1) {
+                    // packed short reductions (tc_fwd_pack): one stage feeds `pack` sub-tiles, each into its own accumulator
+                    const int kper = 4 / pack;             // K = 16 steps per sub-tile inside the stage
+                    for (int s = 0; s < nsub; s += pack) {
+                        if (s) mbar_wait(sFull + st * 8, fph);
+                        fence_proxy_async();
+                        tc_fence_after();
+                        const uint64_t dA = dA0 + (uint64_t)((uint32_t)(st * TC_A_BYTES) >> 4), dB = dB0 + (uint64_t)(((uint32_t)st * B_BYTES) >> 4);
+                        for (int q = 0; q < pack && s + q < nsub; ++q, ++jj) {
+                            const int acc = jj % NACC;
+                            if (jj >= NACC) { mbar_wait(sTEmpty + acc * 8, (uint32_t)((jj / NACC - 1) & 1)); tc_fence_after(); }
+                            const uint32_t tacc = tmem_u + (uint32_t)(acc * acc_cols);
+                            if (elect_one_sync()) {
+                                umma_f16(tacc, dA + a_step * (uint64_t)(q * kper), dB, idesc, 0u);
+                                if (klast > 1) umma_f16(tacc, dA + a_step * (uint64_t)(q * kper + 1), dB + b_step, idesc, 1u);
+                                umma_commit(sTFull + acc * 8);
+                            }
+                            __syncwarp();
+                        }
+                        if (elect_one_sync()) umma_commit(sEmpty + st * 8);
+                        __syncwarp();
+                        if (++st == STAGES) { st = 0; fph ^= 1u; }
+                    }
+                    continue;
+                }
                 for (int s = 0; s < nsub; ++s, ++jj) {
                     const int acc = jj % NACC;
                     if (jj >= NACC) mbar_wait(sTEmpty + acc * 8, (uint32_t)((jj / NACC - 1) & 1));   // epilogue drained this accumulator
-                    const uint32_t tacc = tmem + (uint32_t)(acc * acc_cols);
+                    const uint32_t tacc = tmem_u + (uint32_t)(acc * acc_cols);
                     for (int kb = 0; kb < nk; ++kb) {
-                        mbar_wait(sFull + st * 8, fph);
+                        if (s | kb) mbar_wait(sFull + st * 8, fph);
                         fence_proxy_async();     // the stage was written through the generic proxy (cp.async), UMMA reads it through the async proxy
                         tc_fence_after();
-                        if ((s | kb) == 0) {     // the descriptor was fetched by the loaders long before this stage was published
-                            const TcTile& T = ring[j % TC_RING];
-                            nk = T.nk; klast = T.klast; nsub = T.nsub;
-                            idesc = umma_idesc(MODE == TC_WGRAD ? 1 : 0, MODE == TC_DGRAD ? 0 : 1, T.n_umma);
-                        }
                         const uint64_t dA = dA0 + (uint64_t)((uint32_t)(st * TC_A_BYTES) >> 4), dB = dB0 + (uint64_t)(((uint32_t)st * B_BYTES) >> 4);
                         const int nks = kb == nk - 1 ? klast : TC_BK / 16;
-#pragma unroll
-                        for (int ks = 0; ks < TC_BK / 16; ++ks)
-                            if (ks < nks) umma_f16(tacc, dA + a_step * ks, dB + b_step * ks, idesc, (kb | ks) ? 1u : 0u);
-                        umma_commit(sEmpty + st * 8);
+                        if (elect_one_sync()) {
+                            umma_f16(tacc, dA, dB, idesc, kb ? 1u : 0u);
+                            if (nks > 1) umma_f16(tacc, dA + a_step, dB + b_step, idesc, 1u);
+                            if (nks > 2) umma_f16(tacc, dA + a_step * 2, dB + b_step * 2, idesc, 1u);
+                            if (nks > 3) umma_f16(tacc, dA + a_step * 3, dB + b_step * 3, idesc, 1u);
+                            umma_commit(sEmpty + st * 8);
+                            if (kb == nk - 1) umma_commit(sTFull + acc * 8);
+                        }
+                        __syncwarp();
                         if (++st == STAGES) { st = 0; fph ^= 1u; }
                     }
-                    umma_commit(sTFull + acc * 8);
                 }
             }
         }
@@ -996,7 +1090,8 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                 tc_fence_after();
                 epilogue(T, s, tmem + (uint32_t)(acc * acc_cols), ewarp);
                 tc_fence_before();
-                mbar_arrive(sTEmpty + acc * 8);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(sTEmpty + acc * 8);
             }
         }
     }
