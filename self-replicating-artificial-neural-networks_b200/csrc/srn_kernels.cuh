@@ -8,6 +8,33 @@
 
 namespace srn {
 
+// Packed-half arithmetic for the op-by-op fp16 parts: the product or sum of two fp16 values is exact in fp32, so
+// rh(float(a) * float(b)) == __hmul(a, b) bit for bit, and likewise for add / sub.  Eight elements cost four packed
+// instructions instead of eight convert-operate-convert chains; these passes were bound by instruction issue, not HBM.
+struct __align__(16) Half2x4 { __half2 v[4]; };
+__device__ __forceinline__ Half2x4 as_h2(const Half8& h) { return *reinterpret_cast<const Half2x4*>(&h); }
+__device__ __forceinline__ Half8 as_h8(const Half2x4& h) { return *reinterpret_cast<const Half8*>(&h); }
+// gradient of an activation, eight elements: ReLU keeps g where y > 0 (anything else, NaN included, gives +0),
+// sigmoid is TF's SigmoidGrad dy * y * (1 - y) with one rounding per op
+__device__ __forceinline__ Half8 act_grad8(const Half8& g, const Half8& y, int act) {
+    Half2x4 g2 = as_h2(g);
+    const Half2x4 y2 = as_h2(y);
+    if (act == 1) {
+        const __half2 zero = __float2half2_rn(0.f);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const unsigned m = __hgt2_mask(y2.v[k], zero);
+            unsigned bits = *reinterpret_cast<const unsigned*>(&g2.v[k]) & m;
+            g2.v[k] = *reinterpret_cast<__half2*>(&bits);
+        }
+    } else if (act == 2) {
+        const __half2 one = __float2half2_rn(1.f);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) g2.v[k] = __hmul2_rn(__hmul2_rn(g2.v[k], y2.v[k]), __hsub2_rn(one, y2.v[k]));      // _rn: never contracted into an fma
+    }
+    return as_h8(g2);
+}
+
 constexpr int COL_THREADS = 256;
 constexpr int COL_ITERS = 16;         // rows per row lane and CTA in the column-reduction kernels
 
@@ -78,23 +105,43 @@ k_act_bwd_bias(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
         int in_bs = 0;
         const __half* xin = K1 ? resolve_in(p, I, in_bs) : nullptr;
         if (active) {
-            for (long long r = r0 + rl; r < r1; r += g.RL) {
+            long long r = r0 + rl;
+            if (g.cw == 8) {
+                // four rows per trip: all loads of a trip are issued before the first dependent instruction, so a thread
+                // keeps 64 - 128 bytes in flight instead of 16 - 32 (the pass is latency-bound otherwise: 1.6 TB/s)
+                for (; r + 3LL * g.RL < r1; r += 4LL * g.RL) {
+                    long long o[4]; Half8 gv[4], y[4]; float xr[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const long long rr = r + (long long)u * g.RL;
+                        o[u] = out_row_off(rr, p.Ho * p.Wo, p.out_bs, Fs) + (long long)cq * 8;
+                        gv[u] = ld8(p.gout + o[u]);
+                        if (p.act) y[u] = ld8(p.out + o[u]);
+                        xr[u] = K1 ? __half2float(xin[in_row_off(rr, p.H * p.W, in_bs, 1)]) : 0.f;
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        if (p.act) {
+                            gv[u] = act_grad8(gv[u], y[u], p.act);
+                            st8(p.gout + o[u], gv[u]);
+                        }
+                        const Half2x4 g2 = as_h2(gv[u]);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const float2 f = __half22float2(g2.v[k]);
+                            s[2 * k] += f.x; s[2 * k + 1] += f.y;
+                            if (K1) { sx[2 * k] += f.x * xr[u]; sx[2 * k + 1] += f.y * xr[u]; }
+                        }
+                    }
+                }
+            }
+            for (; r < r1; r += g.RL) {
                 const long long o = out_row_off(r, p.Ho * p.Wo, p.out_bs, Fs) + (long long)cq * g.cw;
                 const float xr = K1 ? __half2float(xin[in_row_off(r, p.H * p.W, in_bs, 1)]) : 0.f;
                 if (g.cw == 8) {
                     Half8 gv = ld8(p.gout + o);
-                    if (p.act == 1) {
-                        const Half8 y = ld8(p.out + o);
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) if (!(__half2float(y.v[j]) > 0.f)) gv.v[j] = __float2half_rn(0.f);
-                        st8(p.gout + o, gv);
-                    } else if (p.act == 2) {
-                        const Half8 y = ld8(p.out + o);
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float yy = __half2float(y.v[j]);
-                            gv.v[j] = __float2half_rn(rh(__half2float(gv.v[j]) * yy) * rh(1.f - yy));
-                        }
+                    if (p.act) {
+                        gv = act_grad8(gv, ld8(p.out + o), p.act);
                         st8(p.gout + o, gv);
                     }
 #pragma unroll
@@ -364,11 +411,17 @@ k_bn_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, int n
         const unsigned ru = (unsigned)q / (unsigned)nq; const long long r = ru; const int c0 = (int)((unsigned)q - ru * (unsigned)nq) * cw;
         const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = out_row_off(r, rps, p.out_bs, p.Fs) + c0;
         if (cw == 8) {
-            const Half8 x = ld8(in + io);
-            Half8 y;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) y.v[j] = __float2half_rn(rh(__half2float(x.v[j]) * inv[c0 + j]) + shift[c0 + j]);
-            st8(p.out + oo, y);
+            // inv and shift hold fp16 values: y = fp16(fp16(x * inv) + shift) is two packed instructions per pair (the _rn forms
+            // are never contracted into one fma, which would round once instead of twice)
+            const Half2x4 x2 = as_h2(ld8(in + io));
+            const float4 i0 = *reinterpret_cast<const float4*>(inv + c0), i1 = *reinterpret_cast<const float4*>(inv + c0 + 4);
+            const float4 s0 = *reinterpret_cast<const float4*>(shift + c0), s1 = *reinterpret_cast<const float4*>(shift + c0 + 4);
+            Half2x4 y2;
+            y2.v[0] = __hadd2_rn(__hmul2_rn(x2.v[0], __floats2half2_rn(i0.x, i0.y)), __floats2half2_rn(s0.x, s0.y));
+            y2.v[1] = __hadd2_rn(__hmul2_rn(x2.v[1], __floats2half2_rn(i0.z, i0.w)), __floats2half2_rn(s0.z, s0.w));
+            y2.v[2] = __hadd2_rn(__hmul2_rn(x2.v[2], __floats2half2_rn(i1.x, i1.y)), __floats2half2_rn(s1.x, s1.y));
+            y2.v[3] = __hadd2_rn(__hmul2_rn(x2.v[3], __floats2half2_rn(i1.z, i1.w)), __floats2half2_rn(s1.z, s1.w));
+            st8(p.out + oo, as_h8(y2));
         } else {
             p.out[oo] = __float2half_rn(rh(__half2float(in[io]) * inv[c0]) + shift[c0]);
         }
@@ -425,18 +478,27 @@ k_bn_bwd_apply(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
         const unsigned ru = (unsigned)q / (unsigned)nq; const long long r = ru; const int c0 = (int)((unsigned)q - ru * (unsigned)nq) * cw;
         const long long io = in_row_off(r, rps, in_bs, Cs) + c0, oo = out_row_off(r, rps, p.out_bs, p.Fs) + c0;
         if (cw == 8) {
-            const Half8 x = ld8(in + io), dy = ld8(p.gout + oo);
-            Half8 d;
-            if (p.din_acc) d = ld8(p.din + io);
+            const Half2x4 x2 = as_h2(ld8(in + io)), dy2 = as_h2(ld8(p.gout + oo));
+            Half2x4 d2;
+            if (p.din_acc) d2 = as_h2(ld8(p.din + io));
+            float dx[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int c = c0 + j;
-                float dx = inv[c] * (__half2float(dy.v[j]) - coef[c * 2]) - (__half2float(x.v[j]) - mean32[c]) * coef[c * 2 + 1];
-                if (c >= p.C) dx = 0.f;
-                if (p.din_acc) dx = rh(dx) + __half2float(d.v[j]);
-                d.v[j] = __float2half_rn(dx);
+            for (int k = 0; k < 4; ++k) {
+                const float2 xf = __half22float2(x2.v[k]), df = __half22float2(dy2.v[k]);
+                const int c = c0 + 2 * k;
+                const float4 cf = *reinterpret_cast<const float4*>(coef + c * 2);       // {mean dy, coefficient} of channels c, c + 1
+                dx[2 * k] = inv[c] * (df.x - cf.x) - (xf.x - mean32[c]) * cf.y;
+                dx[2 * k + 1] = inv[c + 1] * (df.y - cf.z) - (xf.y - mean32[c + 1]) * cf.w;
             }
-            st8(p.din + io, d);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (c0 + j >= p.C) dx[j] = 0.f;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                __half2 h = __floats2half2_rn(dx[2 * k], dx[2 * k + 1]);
+                if (p.din_acc) h = __hadd2_rn(h, d2.v[k]);                                 // fp16(dx) + fp16 accumulator, one rounding
+                d2.v[k] = h;
+            }
+            st8(p.din + io, as_h8(d2));
         } else {
             float dx = inv[c0] * (__half2float(p.gout[oo]) - coef[c0 * 2]) - (__half2float(in[io]) - mean32[c0]) * coef[c0 * 2 + 1];
             if (p.din_acc) dx = rh(dx) + __half2float(p.din[io]);
@@ -459,36 +521,32 @@ k_maxpool_fwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
     int in_bs;
     const __half* in = resolve_in(p, I, in_bs);
     long long q = (long long)blk * EW_PER_CTA + threadIdx.x;
-#pragma unroll 1
+#pragma unroll 2
     for (int it = 0; it < EW_PER_THREAD; ++it, q += EW_THREADS) {
         if (q >= total) break;
         const unsigned pix = (unsigned)q / (unsigned)nq; const int c0 = (int)((unsigned)q - pix * (unsigned)nq) * cw;
         const unsigned bu = pix / (unsigned)HoWo; const long long b = bu; const int rem = (int)(pix - bu * (unsigned)HoWo);
         const int ho = rem / p.Wo, wo = rem - ho * p.Wo;
         const __half* base = in + b * in_bs + ((long long)(ho * p.sh) * p.W + wo * p.sw) * Cs + c0;
-        float best[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) best[j] = -INFINITY;
-        for (int i = 0; i < p.kh; ++i)
-            for (int jj = 0; jj < p.kw; ++jj) {
-                const __half* s = base + ((long long)i * p.W + jj) * Cs;
-                if (cw == 8) {
-                    const Half8 x = ld8(s);
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) { const float v = __half2float(x.v[j]); if (better_max(v, best[j])) best[j] = v; }
-                } else {
-                    const float v = __half2float(*s);
-                    if (better_max(v, best[0])) best[0] = v;
-                }
-            }
         __half* o = p.out + out_row_off(pix, HoWo, p.out_bs, p.Fs) + c0;
         if (cw == 8) {
-            Half8 y;
+            // the maximum of fp16 values is one of them: packed max, NaN wins once seen (as better_max does)
+            Half2x4 best = as_h2(ld8(base));
+            for (int i = 0; i < p.kh; ++i)
+                for (int jj = (i == 0 ? 1 : 0); jj < p.kw; ++jj) {
+                    const Half2x4 x = as_h2(ld8(base + ((long long)i * p.W + jj) * Cs));
 #pragma unroll
-            for (int j = 0; j < 8; ++j) y.v[j] = __float2half_rn(best[j]);
-            st8(o, y);
+                    for (int k = 0; k < 4; ++k) best.v[k] = __hmax2_nan(best.v[k], x.v[k]);
+                }
+            st8(o, as_h8(best));
         } else {
-            *o = __float2half_rn(best[0]);
+            float best = -INFINITY;
+            for (int i = 0; i < p.kh; ++i)
+                for (int jj = 0; jj < p.kw; ++jj) {
+                    const float v = __half2float(base[((long long)i * p.W + jj) * Cs]);
+                    if (better_max(v, best)) best = v;
+                }
+            *o = __float2half_rn(best);
         }
     }
 }
@@ -641,11 +699,25 @@ k_dense_k1_fwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, i
         const float x = __half2float(in[in_row_off(r, p.H * p.W, in_bs, 1)]);
         const Half8 w = ld8(p.w + c0), b = ld8(p.bias + c0);
         Half8 o;
+        if (p.act != 2 && c0 + 8 <= p.F) {
+            // linear / ReLU: fp16(fp16(x * w) + b) and the clamp as packed halves (pad columns of w and b are zero)
+            const Half2x4 w2 = as_h2(w), b2 = as_h2(b);
+            const __half2 x2 = __float2half2_rn(x), zero = __float2half2_rn(0.f);
+            Half2x4 o2;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            float z = 0.f;
-            if (c0 + j < p.F) z = act_forward(rh(rh(x * __half2float(w.v[j])) + __half2float(b.v[j])), p.act);
-            o.v[j] = __float2half_rn(z);
+            for (int k = 0; k < 4; ++k) {
+                __half2 z = __hadd2_rn(__hmul2_rn(x2, w2.v[k]), b2.v[k]);
+                if (p.act == 1) z = __hmax2_nan(z, zero);
+                o2.v[k] = z;
+            }
+            o = as_h8(o2);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float z = 0.f;
+                if (c0 + j < p.F) z = act_forward(rh(rh(x * __half2float(w.v[j])) + __half2float(b.v[j])), p.act);
+                o.v[j] = __float2half_rn(z);
+            }
         }
         st8(p.out + out_row_off(r, rps, p.out_bs, Fs) + c0, o);
     }
