@@ -91,6 +91,8 @@ struct Indiv {
     std::vector<Tensor> tensors;
     float lb = 0.f;
     long long pcount = 0;
+    int lane = 0;
+    long long act_cost = 0;        // activation elements per sample: what the lanes are balanced on
 };
 
 // Device memory owned by an engine handle is grow-only: a buffer is reallocated (with some headroom) only when a call
@@ -159,6 +161,7 @@ struct Cached {
 
 struct Group {
     int depth, kind, cfgF, cfgC, ordinal, tc;
+    int lane = 0;                  // half of the shard this bucket's individuals belong to (srn_engine::LaneCtx)
     int mode = 3;                  // bit 0: runs when the inputs are a shared batch, bit 1: when they are per individual
     std::vector<Prob> h;
     Prob* d = nullptr;
@@ -180,16 +183,30 @@ struct srn_engine {
     cudaStream_t stream = 0;
     cudaStream_t cur = 0;                 // stream the LAUNCH macros use (main stream or one of the side streams)
     static constexpr int NSIDE = 7;
-    cudaStream_t side[NSIDE] = {};        // independent launch buckets of one depth level overlap their tails on these
-    cudaEvent_t ev_fork = nullptr, ev_join[NSIDE] = {};
+    static constexpr int NWG = 3;
+    static constexpr int NLANES = 2;
+    // A lane = one half of the shard's individuals with its own set of streams.  Individuals are independent, so the two
+    // halves walk their depth levels out of step: while one half is in its deep, latency-bound levels (a few small
+    // launches in a dependency chain) the other half's wide first levels keep the SMs busy.  Lane 0 runs on the
+    // engine's main stream; inference passes (one forward over all individuals) use lane 0 for everything.
+    struct LaneCtx {
+        cudaStream_t main = nullptr;
+        cudaStream_t side[NSIDE] = {};        // independent launch buckets of one depth level overlap their tails on these
+        cudaEvent_t ev_fork = nullptr, ev_join[NSIDE] = {};
+        cudaStream_t wg_stream[NWG] = {};
+        cudaEvent_t ev_wg = nullptr, ev_wg_done[NWG] = {};
+        int wg_next = 0; bool wg_used[NWG] = {};
+        cudaEvent_t ev_done = nullptr;
+        Prob* d_loss = nullptr; int n_loss = 0;      // this lane's slice of the loss problems
+    } lane[NLANES];
+    LaneCtx* L = nullptr;                 // lane whose streams the launch helpers use
+    int n_lanes = 1;                      // lanes the current population is split into
+    int stagger_depth = 0;                // lane 1 starts once lane 0 has issued this forward depth level (0: together)
+    cudaEvent_t ev_inputs = nullptr;
     // the optimiser pass runs on its own stream so that the next step's batch gather and im2col overlap it
     // weight-gradient launches float: they only need their layer's activation backward, nothing in the backward pass
     // needs them, so they run on their own streams, fill the idle SMs of the latency-bound deep levels and are joined
     // before the optimiser
-    static constexpr int NWG = 3;
-    cudaStream_t wg_stream[NWG] = {};
-    cudaEvent_t ev_wg = nullptr, ev_wg_done[NWG] = {};
-    int wg_next = 0; bool wg_used[NWG] = {};
     cudaStream_t adam_stream = nullptr;
     cudaEvent_t ev_adam_go = nullptr, ev_adam_done = nullptr;
     bool adam_pending = false;
@@ -291,6 +308,8 @@ static void free_population(srn_engine* h, bool release = false) {
     h->groups.clear();
     h->inds.clear();
     h->d_loss = nullptr; h->d_lb = nullptr;
+    for (auto& L : h->lane) { L.d_loss = nullptr; L.n_loss = 0; }
+    h->n_lanes = 1;
     h->im2col = nullptr; h->geos.clear();
     h->P = h->M = h->V = h->S = h->act = nullptr; h->Gr = h->save = nullptr;
     h->met_correct = nullptr; h->met_ce = h->met_mse = nullptr; h->met_slots = 0;
@@ -335,17 +354,25 @@ extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
 static int create_resources(srn_engine* h) {
     const srn_config* cfg = &h->cfg;
     CK(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
-    for (int i = 0; i < srn_engine::NSIDE; ++i) {
-        CK(cudaStreamCreateWithFlags(&h->side[i], cudaStreamNonBlocking));
-        CK(cudaEventCreateWithFlags(&h->ev_join[i], cudaEventDisableTiming));
+    for (int l = 0; l < srn_engine::NLANES; ++l) {
+        srn_engine::LaneCtx& L = h->lane[l];
+        if (l == 0) L.main = h->stream;
+        else CK(cudaStreamCreateWithFlags(&L.main, cudaStreamNonBlocking));
+        for (int i = 0; i < srn_engine::NSIDE; ++i) {
+            CK(cudaStreamCreateWithFlags(&L.side[i], cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&L.ev_join[i], cudaEventDisableTiming));
+        }
+        CK(cudaEventCreateWithFlags(&L.ev_fork, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&L.ev_wg, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&L.ev_done, cudaEventDisableTiming));
+        for (int i = 0; i < srn_engine::NWG; ++i) {
+            CK(cudaStreamCreateWithFlags(&L.wg_stream[i], cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&L.ev_wg_done[i], cudaEventDisableTiming));
+        }
     }
-    CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+    h->L = &h->lane[0];
+    CK(cudaEventCreateWithFlags(&h->ev_inputs, cudaEventDisableTiming));
     CK(cudaStreamCreateWithFlags(&h->adam_stream, cudaStreamNonBlocking));
-    CK(cudaEventCreateWithFlags(&h->ev_wg, cudaEventDisableTiming));
-    for (int i = 0; i < srn_engine::NWG; ++i) {
-        CK(cudaStreamCreateWithFlags(&h->wg_stream[i], cudaStreamNonBlocking));
-        CK(cudaEventCreateWithFlags(&h->ev_wg_done[i], cudaEventDisableTiming));
-    }
     CK(cudaEventCreateWithFlags(&h->ev_adam_go, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->ev_adam_done, cudaEventDisableTiming));
     h->multi_stream = getenv("SRN_SINGLE_STREAM") == nullptr;
@@ -368,16 +395,22 @@ extern "C" void srn_destroy(srn_engine* h) {
     free_population(h, true);
     if (h->ev_t0) cudaEventDestroy(h->ev_t0);
     if (h->ev_t1) cudaEventDestroy(h->ev_t1);
-    for (int i = 0; i < srn_engine::NSIDE; ++i) { if (h->side[i]) cudaStreamDestroy(h->side[i]); if (h->ev_join[i]) cudaEventDestroy(h->ev_join[i]); }
-    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    for (int l = 0; l < srn_engine::NLANES; ++l) {
+        srn_engine::LaneCtx& L = h->lane[l];
+        for (int i = 0; i < srn_engine::NSIDE; ++i) { if (L.side[i]) cudaStreamDestroy(L.side[i]); if (L.ev_join[i]) cudaEventDestroy(L.ev_join[i]); }
+        if (L.ev_fork) cudaEventDestroy(L.ev_fork);
+        if (L.ev_wg) cudaEventDestroy(L.ev_wg);
+        if (L.ev_done) cudaEventDestroy(L.ev_done);
+        for (int i = 0; i < srn_engine::NWG; ++i) {
+            if (L.ev_wg_done[i]) cudaEventDestroy(L.ev_wg_done[i]);
+            if (L.wg_stream[i]) cudaStreamDestroy(L.wg_stream[i]);
+        }
+        if (l > 0 && L.main) cudaStreamDestroy(L.main);
+    }
+    if (h->ev_inputs) cudaEventDestroy(h->ev_inputs);
     if (h->ev_adam_go) cudaEventDestroy(h->ev_adam_go);
     if (h->ev_adam_done) cudaEventDestroy(h->ev_adam_done);
     if (h->adam_stream) cudaStreamDestroy(h->adam_stream);
-    if (h->ev_wg) cudaEventDestroy(h->ev_wg);
-    for (int i = 0; i < srn_engine::NWG; ++i) {
-        if (h->ev_wg_done[i]) cudaEventDestroy(h->ev_wg_done[i]);
-        if (h->wg_stream[i]) cudaStreamDestroy(h->wg_stream[i]);
-    }
     for (int s = 0; s < 2; ++s) { cudaFree(h->x[s]); cudaFree(h->y[s]); cudaFree(h->gb[s]); }
     cudaFree(h->xin); cudaFree(h->gin); cudaFree(h->lab);
     delete h;
@@ -669,8 +702,32 @@ extern "C" int srn_build_seeded(srn_engine* h, const srn_layer_desc* layers, con
     CK(cudaMemsetAsync(h->S, 0, (size_t)h->s_elems * sizeof(__half), h->stream));
     CK(cudaMemsetAsync(h->save, 0, (size_t)h->save_elems * sizeof(float), h->stream));
     CK(cudaMemsetAsync(h->act, 0, (size_t)h->act_elems * sizeof(__half), h->stream));
+    // ---- lanes: two halves of about equal activation volume (greedy on the sorted sizes); a small shard stays whole
+    // (measured on the benchmark population: 9.7 ms per step with two lanes against 8.95 with one - the extra launches
+    // and the halved buckets cost more than the overlap of the deep levels gains - so one lane is the default)
+    h->n_lanes = (n >= 8 && getenv("SRN_TWO_LANES") != nullptr) ? srn_engine::NLANES : 1;
+    {
+        std::vector<int> order((size_t)n);
+        for (int i = 0; i < n; ++i) {
+            order[(size_t)i] = i;
+            long long c = 0;
+            for (const Tensor& T : h->inds[i].tensors) if (T.act_off >= 0) c += T.bs;
+            h->inds[i].act_cost = c;
+            h->inds[i].lane = 0;
+        }
+        if (h->n_lanes > 1) {
+            std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return h->inds[a].act_cost > h->inds[b].act_cost; });
+            long long load[srn_engine::NLANES] = {};
+            for (int i : order) {
+                int best = 0;
+                for (int l = 1; l < h->n_lanes; ++l) if (load[l] < load[best]) best = l;
+                h->inds[i].lane = best;
+                load[best] += h->inds[i].act_cost;
+            }
+        }
+    }
     // ---- pass 2: pointers, consumer ordinals, problem groups
-    std::map<std::tuple<int, int, int, int, int>, Group> gmap;
+    std::map<std::tuple<int, int, int, int, int, int>, Group> gmap;
     long long geo_elems = 0;
     h->h_loss.clear();
     for (int i = 0; i < n; ++i) {
@@ -778,14 +835,16 @@ extern "C" int srn_build_seeded(srn_engine* h, const srn_layer_desc* layers, con
                     s2.coff = gi;                            // geometry index, used for the fix-up
                     s2.Cj = e.KK < e.Kp ? 1 : 0;             // the matrix has a ones column: bias gradient from the weight-gradient GEMM
                     const int cF = tc_cfg_for(s2.F), cC = tc_cfg_for(s2.C);
-                    auto key2 = std::make_tuple(to.depth, kind, cF + 16 * 1 + 64 * 1, cC, ordinal);
+                    auto key2 = std::make_tuple(to.depth, kind, cF + 16 * 1 + 64 * 1, cC, ordinal, ind.lane);
                     Group& g2 = gmap[key2];
+                    g2.lane = ind.lane;
                     g2.depth = to.depth; g2.kind = kind; g2.cfgF = cF; g2.cfgC = cC; g2.ordinal = ordinal; g2.tc = 1; g2.mode = 1;
                     g2.h.push_back(s2);
                     mode = 2;
                 }
-                auto key = std::make_tuple(to.depth, kind, cfgF + 16 * tc + 64 * mode, cfgC, ordinal);
+                auto key = std::make_tuple(to.depth, kind, cfgF + 16 * tc + 64 * mode, cfgC, ordinal, ind.lane);
                 Group& g = gmap[key];
+                g.lane = ind.lane;
                 g.depth = to.depth; g.kind = kind; g.cfgF = cfgF; g.cfgC = cfgC; g.ordinal = ordinal; g.tc = tc; g.mode = mode;
                 g.h.push_back(p);
             }
@@ -843,6 +902,19 @@ extern "C" int srn_build_seeded(srn_engine* h, const srn_layer_desc* layers, con
     }
     POOL_ALLOC(h->d_loss, Prob, n * sizeof(Prob));
     CK(cudaMemcpyAsync(h->d_loss, h->h_loss.data(), n * sizeof(Prob), cudaMemcpyHostToDevice, h->stream));
+    {
+        // the same problems once more, lane by lane (the loss kernel of a lane covers only its own individuals)
+        std::vector<Prob> by_lane;
+        Prob* d_by_lane = nullptr;
+        POOL_ALLOC(d_by_lane, Prob, n * sizeof(Prob));
+        for (int l = 0; l < srn_engine::NLANES; ++l) {
+            h->lane[l].d_loss = d_by_lane + by_lane.size();
+            for (int i = 0; i < n; ++i) if (h->inds[i].lane == l) by_lane.push_back(h->h_loss[(size_t)i]);
+            h->lane[l].n_loss = (int)(d_by_lane + by_lane.size() - h->lane[l].d_loss);
+        }
+        CK(cudaMemcpyAsync(d_by_lane, by_lane.data(), n * sizeof(Prob), cudaMemcpyHostToDevice, h->stream));
+        CK(cudaStreamSynchronize(h->stream));      // by_lane goes out of scope
+    }
     POOL_ALLOC(h->d_lb, float, n * sizeof(float));
     CK(cudaMemcpyAsync(h->d_lb, loss_balance, n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
     // ---- Keras default initialisation on the device
@@ -1162,20 +1234,20 @@ static int run_level(srn_engine* h, std::vector<Group*>& level, F&& body) {
     if (level.empty()) return SRN_OK;
     const bool fan = h->multi_stream && level.size() > 1;
     if (fan) {
-        cudaEventRecord(h->ev_fork, h->stream);
-        for (int i = 0; i < srn_engine::NSIDE; ++i) cudaStreamWaitEvent(h->side[i], h->ev_fork, 0);
+        cudaEventRecord(h->L->ev_fork, h->L->main);
+        for (int i = 0; i < srn_engine::NSIDE; ++i) cudaStreamWaitEvent(h->L->side[i], h->L->ev_fork, 0);
     }
     bool used[srn_engine::NSIDE] = {};
     int rc = SRN_OK;
     for (size_t k = 0; k < level.size() && !rc; ++k) {
         const int lane = fan ? (int)(k % (srn_engine::NSIDE + 1)) : 0;
-        h->cur = lane == 0 ? h->stream : h->side[lane - 1];
+        h->cur = lane == 0 ? h->L->main : h->L->side[lane - 1];
         if (lane) used[lane - 1] = true;
         rc = body(*level[k]);
     }
-    h->cur = h->stream;
+    h->cur = h->L->main;
     for (int i = 0; i < srn_engine::NSIDE; ++i)
-        if (used[i]) { cudaEventRecord(h->ev_join[i], h->side[i]); cudaStreamWaitEvent(h->stream, h->ev_join[i], 0); }
+        if (used[i]) { cudaEventRecord(h->L->ev_join[i], h->L->side[i]); cudaStreamWaitEvent(h->L->main, h->L->ev_join[i], 0); }
     return rc;
 }
 
@@ -1184,20 +1256,20 @@ static int run_tasks(srn_engine* h, std::vector<std::function<int()>>& tasks) {
     if (tasks.empty()) return SRN_OK;
     const bool fan = h->multi_stream && tasks.size() > 1;
     if (fan) {
-        cudaEventRecord(h->ev_fork, h->stream);
-        for (int i = 0; i < srn_engine::NSIDE; ++i) cudaStreamWaitEvent(h->side[i], h->ev_fork, 0);
+        cudaEventRecord(h->L->ev_fork, h->L->main);
+        for (int i = 0; i < srn_engine::NSIDE; ++i) cudaStreamWaitEvent(h->L->side[i], h->L->ev_fork, 0);
     }
     bool used[srn_engine::NSIDE] = {};
     int rc = SRN_OK;
     for (size_t k = 0; k < tasks.size() && !rc; ++k) {
         const int lane = fan ? (int)(k % (srn_engine::NSIDE + 1)) : 0;
-        h->cur = lane == 0 ? h->stream : h->side[lane - 1];
+        h->cur = lane == 0 ? h->L->main : h->L->side[lane - 1];
         if (lane) used[lane - 1] = true;
         rc = tasks[k]();
     }
-    h->cur = h->stream;
+    h->cur = h->L->main;
     for (int i = 0; i < srn_engine::NSIDE; ++i)
-        if (used[i]) { cudaEventRecord(h->ev_join[i], h->side[i]); cudaStreamWaitEvent(h->stream, h->ev_join[i], 0); }
+        if (used[i]) { cudaEventRecord(h->L->ev_join[i], h->L->side[i]); cudaStreamWaitEvent(h->L->main, h->L->ev_join[i], 0); }
     return rc;
 }
 
@@ -1247,14 +1319,15 @@ static void wait_adam(srn_engine* h) {
     if (h->adam_pending) { cudaStreamWaitEvent(h->stream, h->ev_adam_done, 0); h->adam_pending = false; }
 }
 
-static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
+// shared im2col matrices of the first layers (one per window geometry), written once per batch on lane 0's streams
+static void shared_im2col(srn_engine* h, int nb, const Inputs& I) {
     const int mode = (I.x_istride == 0 && I.g_istride == 0) ? 1 : 2;
     if (mode == 1 && !h->geos.empty()) {
         // one small launch per window geometry: independent, so they go out on all streams at once
         const bool fan = h->multi_stream && h->geos.size() > 1;
         if (fan) {
-            cudaEventRecord(h->ev_fork, h->stream);
-            for (int i = 0; i < srn_engine::NSIDE; ++i) cudaStreamWaitEvent(h->side[i], h->ev_fork, 0);
+            cudaEventRecord(h->L->ev_fork, h->L->main);
+            for (int i = 0; i < srn_engine::NSIDE; ++i) cudaStreamWaitEvent(h->L->side[i], h->L->ev_fork, 0);
         }
         bool used[srn_engine::NSIDE] = {};
         for (size_t k = 0; k < h->geos.size(); ++k) {
@@ -1263,15 +1336,20 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
             e.in = img ? I.x : I.g; e.in_bs = img ? I.x_bs : I.g_bs;
             const long long total = (long long)nb * e.Ho * e.Wo * (e.Kp >> 3);
             const int lane = fan ? (int)(k % (srn_engine::NSIDE + 1)) : 0;
-            h->cur = lane == 0 ? h->stream : h->side[lane - 1];
+            h->cur = lane == 0 ? h->L->main : h->L->side[lane - 1];
             if (lane) used[lane - 1] = true;
             LAUNCH(SRN_CAT_GATHER, k_im2col, (unsigned)((total + 255) / 256), 256, e, nb);
         }
-        h->cur = h->stream;
+        h->cur = h->L->main;
         for (int i = 0; i < srn_engine::NSIDE; ++i)
-            if (used[i]) { cudaEventRecord(h->ev_join[i], h->side[i]); cudaStreamWaitEvent(h->stream, h->ev_join[i], 0); }
+            if (used[i]) { cudaEventRecord(h->L->ev_join[i], h->L->side[i]); cudaStreamWaitEvent(h->L->main, h->L->ev_join[i], 0); }
     }
-    wait_adam(h);
+}
+
+// lane < 0: every bucket (inference passes); else the buckets of that lane's individuals, on the current lane context
+static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training, int lane = -1) {
+    const int mode = (I.x_istride == 0 && I.g_istride == 0) ? 1 : 2;
+    if (lane < 0) { shared_im2col(h, nb, I); wait_adam(h); }
     // buckets of one depth level are independent: spread them over the side streams so that the tail of one
     // persistent launch overlaps the ramp-up of the next; levels are separated by events
     size_t gi = 0;
@@ -1279,7 +1357,7 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
         size_t ge = gi;
         std::vector<Group*> level;
         while (ge < h->groups.size() && h->groups[ge].depth == h->groups[gi].depth) {
-            if (h->groups[ge].mode & mode) level.push_back(&h->groups[ge]);
+            if ((h->groups[ge].mode & mode) && (lane < 0 || h->groups[ge].lane == lane)) level.push_back(&h->groups[ge]);
             ++ge;
         }
         static const bool merge = getenv("SRN_NO_MERGE_FWD") == nullptr;
@@ -1297,7 +1375,7 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
             for (int b = 0; b < 4; ++b) {
                 if (by_bn[b].empty()) continue;
                 if (by_bn[b].size() == 1) { Group* g = by_bn[b][0]; tasks.push_back([=, &I]() { return fwd_group(h, *g, nb, I, training); }); continue; }
-                auto key = std::make_tuple(nb, by_bn[b][0]->depth, b, mode);
+                auto key = std::make_tuple(nb, by_bn[b][0]->depth, b, mode + 16 * (lane + 1));
                 auto it = h->merged_fwd.find(key);
                 if (it == h->merged_fwd.end()) {
                     std::vector<TcTile> all;
@@ -1332,6 +1410,7 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training) {
             rc = run_tasks(h, tasks);
         }
         if (rc) return rc;
+        if (lane == 0 && training && h->stagger_depth > 0 && h->groups[gi].depth == h->stagger_depth) cudaEventRecord(h->ev_inputs, h->L->main);
         gi = ge;
     }
     return SRN_OK;
@@ -1355,10 +1434,10 @@ static int bwd_group(srn_engine* h, Group& g, int nb, const Inputs& I) {
                 // the weight gradient goes to a floating stream behind this bucket's activation backward
                 cudaStream_t lane = h->cur;
                 if (h->multi_stream) {
-                    const int w = h->wg_next; h->wg_next = (w + 1) % srn_engine::NWG; h->wg_used[w] = true;
-                    cudaEventRecord(h->ev_wg, lane);
-                    cudaStreamWaitEvent(h->wg_stream[w], h->ev_wg, 0);
-                    h->cur = h->wg_stream[w];
+                    const int w = h->L->wg_next; h->L->wg_next = (w + 1) % srn_engine::NWG; h->L->wg_used[w] = true;
+                    cudaEventRecord(h->L->ev_wg, lane);
+                    cudaStreamWaitEvent(h->L->wg_stream[w], h->L->ev_wg, 0);
+                    h->cur = h->L->wg_stream[w];
                 }
                 if (g.tc) {
                     const int BNf = TC_BN[g.cfgF];
@@ -1391,7 +1470,7 @@ static int bwd_group(srn_engine* h, Group& g, int nb, const Inputs& I) {
     return SRN_OK;
 }
 
-static int backward_pass(srn_engine* h, int nb, const Inputs& I) {
+static int backward_pass(srn_engine* h, int nb, const Inputs& I, int lane = -1) {
     const int mode = (I.x_istride == 0 && I.g_istride == 0) ? 1 : 2;
     int gi = (int)h->groups.size() - 1;
     while (gi >= 0) {
@@ -1399,7 +1478,7 @@ static int backward_pass(srn_engine* h, int nb, const Inputs& I) {
         std::vector<Group*> first, later;      // consumers that overwrite an input gradient / that add to it afterwards
         while (ge >= 0 && h->groups[ge].depth == h->groups[gi].depth) {
             Group& g = h->groups[ge];
-            if (g.mode & mode) (g.ordinal == 0 ? first : later).push_back(&g);
+            if ((g.mode & mode) && (lane < 0 || g.lane == lane)) (g.ordinal == 0 ? first : later).push_back(&g);
             --ge;
         }
         int rc = run_level(h, first, [&](Group& g) { return bwd_group(h, g, nb, I); });
@@ -1408,10 +1487,10 @@ static int backward_pass(srn_engine* h, int nb, const Inputs& I) {
         gi = ge;
     }
     for (int w = 0; w < srn_engine::NWG; ++w)      // every weight gradient is in before the optimiser (and the next batch) starts
-        if (h->wg_used[w]) {
-            cudaEventRecord(h->ev_wg_done[w], h->wg_stream[w]);
-            cudaStreamWaitEvent(h->stream, h->ev_wg_done[w], 0);
-            h->wg_used[w] = false;
+        if (h->L->wg_used[w]) {
+            cudaEventRecord(h->L->ev_wg_done[w], h->L->wg_stream[w]);
+            cudaStreamWaitEvent(h->L->main, h->L->ev_wg_done[w], 0);
+            h->L->wg_used[w] = false;
         }
     return SRN_OK;
 }
@@ -1437,7 +1516,7 @@ static Inputs shared_inputs(srn_engine* h) {
     return I;
 }
 
-static void launch_loss(srn_engine* h, int nb, const Inputs& I, int slot_base, int chunk, int row0, int training) {
+static void launch_loss(srn_engine* h, int nb, const Inputs& I, int slot_base, int chunk, int row0, int training, int lane = -1) {
     LossArgs a;
     a.labels = h->lab;
     a.bits = I.g; a.bits_istride = I.g_istride; a.bits_bs = I.g_bs;
@@ -1445,8 +1524,10 @@ static void launch_loss(srn_engine* h, int nb, const Inputs& I, int slot_base, i
     a.met_correct = h->met_correct; a.met_ce = h->met_ce; a.met_mse = h->met_mse;
     a.n = h->n; a.ncls = h->ncls; a.G = h->G;
     a.slot_base = slot_base; a.chunk = chunk; a.row0 = row0; a.training = training;
-    const int ctas = h->n * ((nb + 7) / 8);
-    LAUNCH(SRN_CAT_LOSS, k_loss, ctas, 256, h->d_loss, h->n, nb, a);
+    const Prob* probs = lane < 0 ? h->d_loss : h->lane[lane].d_loss;
+    const int np = lane < 0 ? h->n : h->lane[lane].n_loss;
+    const int ctas = np * ((nb + 7) / 8);
+    LAUNCH(SRN_CAT_LOSS, k_loss, ctas, 256, probs, np, nb, a);
 }
 
 static AdamScalars adam_scalars(int t) {
@@ -1466,10 +1547,30 @@ static AdamScalars adam_scalars(int t) {
 static int train_step(srn_engine* h, const int* d_idx, int start, int nb, int slot, bool apply_adam) {
     LAUNCH(SRN_CAT_GATHER, k_gather_batch, nb, 256, h->x[0], h->gb[0], h->y[0], d_idx, start, nb, h->xe, h->G, h->xin, h->gin, h->lab);
     Inputs I = shared_inputs(h);
-    int rc = forward_pass(h, nb, I, true);
-    if (rc) return rc;
-    launch_loss(h, nb, I, slot, 1 << 30, 0, 1);
-    rc = backward_pass(h, nb, I);
+    int rc = SRN_OK;
+    h->L = &h->lane[0];
+    shared_im2col(h, nb, I);
+    wait_adam(h);
+    const int lanes = h->multi_stream ? h->n_lanes : 1;
+    h->stagger_depth = getenv("SRN_STAGGER") ? atoi(getenv("SRN_STAGGER")) : 2;
+    if (lanes > 1) cudaEventRecord(h->ev_inputs, h->stream);
+    for (int l = 0; l < h->n_lanes && !rc; ++l) {
+        // with one stream (profiling) the lanes simply follow each other on lane 0's streams
+        srn_engine::LaneCtx* L = &h->lane[lanes > 1 ? l : 0];
+        h->L = L;
+        h->cur = L->main;
+        if (lanes > 1 && l > 0) cudaStreamWaitEvent(L->main, h->ev_inputs, 0);
+        rc = forward_pass(h, nb, I, true, l);
+        if (!rc) {
+            launch_loss(h, nb, I, slot, 1 << 30, 0, 1, l);
+            rc = backward_pass(h, nb, I, l);
+        }
+        if (lanes > 1 && l > 0) cudaEventRecord(L->ev_done, L->main);
+    }
+    h->L = &h->lane[0];
+    h->cur = h->stream;
+    if (lanes > 1)
+        for (int l = 1; l < h->n_lanes; ++l) cudaStreamWaitEvent(h->stream, h->lane[l].ev_done, 0);
     if (rc) return rc;
     if (apply_adam) {
         h->adam_t += 1;
