@@ -7,6 +7,7 @@
 // problems.  A training step is then ~3 launches per bucket regardless of the population size.
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -1644,6 +1645,7 @@ extern "C" int srn_fit(srn_engine* h, int32_t epochs, int32_t batch, int32_t n_v
     if (rc) return rc;
     cudaEvent_t ev0 = h->ev_t0, ev1 = h->ev_t1;
     float ms_total = 0.f;
+    double host_enqueue_s = 0.0;          // host time spent issuing the steps' launches (SRN_HOST_TIMING prints it)
     int steps_done = 0;
     bool stop = false;
     // gradient accumulators start at zero (a debug step without the optimiser leaves its sums behind)
@@ -1655,7 +1657,9 @@ extern "C" int srn_fit(srn_engine* h, int32_t epochs, int32_t batch, int32_t n_v
         CK(cudaEventRecord(ev0, h->stream));
         for (int s = 0; s < S; ++s) {
             const int nb = std::min(batch, n_fit - s * batch);
+            const auto th0 = std::chrono::steady_clock::now();
             rc = train_step(h, d_perm + (size_t)e * n_fit + (size_t)s * batch, 0, nb, e * S + s, true);
+            host_enqueue_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - th0).count();
             if (rc) return rc;
             if (max_steps > 0 && ++steps_done >= max_steps) { stop = true; break; }
         }
@@ -1691,6 +1695,8 @@ extern "C" int srn_fit(srn_engine* h, int32_t epochs, int32_t batch, int32_t n_v
     if (val_correct && vn) CK(cudaMemcpy(val_correct, h->met_correct + tn, vn * sizeof(int), cudaMemcpyDeviceToHost));
     if (val_mse_sum && vn) CK(cudaMemcpy(val_mse_sum, h->met_mse + tn, vn * sizeof(float), cudaMemcpyDeviceToHost));
     if (device_ms) *device_ms = ms_total;
+    if (getenv("SRN_HOST_TIMING"))
+        fprintf(stderr, "srn_fit: %d steps, device %.3f ms, host enqueue %.3f ms\n", max_steps > 0 ? steps_done : epochs * S, ms_total, 1e3 * host_enqueue_s);
     return SRN_OK;
 }
 
