@@ -99,12 +99,32 @@ struct Indiv {
 // Device memory owned by an engine handle is grow-only: a buffer is reallocated (with some headroom) only when a call
 // needs more than it holds, so that a steady-state generation - same population size, similar architectures - makes
 // no cudaMalloc / cudaFree at all (both synchronise the whole device).
+// SRN_GUARD=1 (tests; compute-sanitizer is closed on the GPU pool): every buffer gets a 4 KiB band of 0xA5 right behind
+// the bytes the current use asked for, and srn_debug_check_guards reports any band that a kernel has written into.
+constexpr size_t GUARD_BYTES = 4096;
+static bool guards_on() { static const bool on = getenv("SRN_GUARD") != nullptr; return on; }
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
+    size_t used = 0;         // bytes of the current use (where the guard band starts)
     template <class T> T* as() const { return static_cast<T*>(p); }
 };
+static cudaError_t buf_reserve_raw(DevBuf& b, size_t bytes, double headroom);
 static cudaError_t buf_reserve(DevBuf& b, size_t bytes, double headroom = 1.0) {
+    if (!guards_on()) return buf_reserve_raw(b, bytes, headroom);
+    cudaError_t e = buf_reserve_raw(b, bytes + GUARD_BYTES, headroom);
+    if (e != cudaSuccess) return e;
+    b.used = bytes;
+    return cudaMemset(static_cast<char*>(b.p) + bytes, 0xA5, GUARD_BYTES);
+}
+static bool buf_guard_ok(const DevBuf& b) {
+    if (!guards_on() || !b.p) return true;
+    unsigned char host[GUARD_BYTES];
+    if (cudaMemcpy(host, static_cast<const char*>(b.p) + b.used, GUARD_BYTES, cudaMemcpyDeviceToHost) != cudaSuccess) return false;
+    for (size_t i = 0; i < GUARD_BYTES; ++i) if (host[i] != 0xA5) return false;
+    return true;
+}
+static cudaError_t buf_reserve_raw(DevBuf& b, size_t bytes, double headroom) {
     if (bytes <= b.cap && b.p) return cudaSuccess;
     if (b.p) { cudaFree(b.p); b.p = nullptr; b.cap = 0; }
     size_t want = (size_t)((double)bytes * headroom);
@@ -1875,6 +1895,18 @@ extern "C" int srn_debug_get_grad(srn_engine* h, int32_t ind, int32_t layer, int
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
     return copy_rows(buf, reinterpret_cast<char*>(h->Gr + (p - h->P)), rows, cols, ld, sizeof(float), rm, true);
+}
+
+// SRN_GUARD=1: number of the first handle buffer whose guard band was overwritten (1-based), 0 = all intact, -1 = guards off
+extern "C" int srn_debug_check_guards(srn_engine* h) {
+    if (!h) return -1;
+    if (!guards_on()) return -1;
+    if (cudaSetDevice(h->cfg.device) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) return -2;
+    const DevBuf* bufs[] = {&h->bP, &h->bM, &h->bV, &h->bGr, &h->bS, &h->bSave, &h->bAct, &h->bIm2col, &h->bMetC, &h->bMetCe, &h->bMetMse,
+                            &h->bPerm, &h->bLogits, &h->bIdx, &h->bRepX, &h->bRepG, &h->bRepPar, &h->bRepProbs, &h->bRepPacked, &h->bRepMut};
+    int k = 0;
+    for (const DevBuf* b : bufs) { ++k; if (!buf_guard_ok(*b)) return k; }
+    return 0;
 }
 
 extern "C" int srn_debug_launch_groups(srn_engine* h) { return h && h->built ? (int)h->groups.size() : -1; }

@@ -27,6 +27,9 @@ int srn_debug_get_tensor(srn_engine* h, int32_t individual, int32_t tensor, int3
 // fp32 gradient accumulator of a weight (which = 0 kernel/gamma, 1 bias/beta)
 int srn_debug_get_grad(srn_engine* h, int32_t individual, int32_t layer, int32_t which, float* buf, int64_t count);
 int srn_debug_launch_groups(srn_engine* h);
+// with SRN_GUARD=1 in the environment every handle buffer carries a guard band behind its live bytes: 0 = all intact,
+// k > 0 = buffer k was overrun, -1 = guards are off (the pool's compute-sanitizer is closed; this is the stand-in)
+int srn_debug_check_guards(srn_engine* h);
 // per-launch records of the last profiled region; returns the number written (see srn_engine.cu)
 int srn_debug_group_probs(srn_engine* h, int32_t group, int32_t cap, int32_t* out);
 int srn_debug_profile_detail(srn_engine* h, int32_t nb, int32_t cap, float* ms, float* start, int32_t* info, double* work);

@@ -257,3 +257,39 @@ def test_evaluator_k32_matches_the_oracle_in_distribution(which):
     finally:
         ev.close()
         ae.close()
+
+
+def test_no_kernel_writes_past_its_buffers_at_batch_750():
+    """compute-sanitizer is closed on the GPU pool, so the arenas carry guard bands instead (SRN_GUARD=1, a fresh process
+    because the switch is read once): build, three training steps at B = 750, validation, test evaluation and
+    replication of a slice of the bench population, then every band must still hold its pattern."""
+    import subprocess
+    import sys
+    code = '''
+import sys, numpy as np
+sys.path.insert(0, "tests")
+import parity_util as U
+from serann_b200 import generator
+from serann_b200.engine import Engine
+pop = generator.sample_population(100, seed=0, distinct=True)[::9]
+data = U.small_dataset(n_train=3 * 750 + 300, n_test=96, seed=3)
+eng = Engine(max_batch=750)
+eng.set_dataset(data["x_train"], data["y_train"], data["g_train"], data["x_test"], data["y_test"], data["g_test"])
+eng.build([ir for _, ir in pop], seed=2)
+assert eng._lib.srn_debug_check_guards(eng._h) == 0
+eng.fit(1, 750, 300, shuffle_seed=1)
+eng.evaluate(1, 0, 96, 32)
+eng.replicate(data["g_test"][:len(pop)], 7)
+rc = eng._lib.srn_debug_check_guards(eng._h)
+eng.build([ir for _, ir in pop[:5]], seed=3)          # a smaller population in the same (grow-only) buffers
+eng.fit(1, 750, 300, shuffle_seed=2, max_steps=2)
+rc2 = eng._lib.srn_debug_check_guards(eng._h)
+print("GUARDS", rc, rc2)
+'''
+    import os
+    import pathlib
+    root = pathlib.Path(__file__).resolve().parent.parent
+    r = subprocess.run([sys.executable, '-c', code], cwd=root, env=dict(os.environ, SRN_GUARD='1', PYTHONPATH=str(root)),
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert 'GUARDS 0 0' in r.stdout, r.stdout[-500:]
