@@ -259,7 +259,7 @@ def run_reference(args):
                                    f'itself needs TensorFlow 2.6, which is not installable here)'},
         'e2e': {'value': rate, 'unit': 'steps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------------------------------------
@@ -356,8 +356,23 @@ def pop1000_leg(D, data, decoder_weights, tmpdir, generations=1):
     return out
 
 
+def _claim_stdout():
+    """Libraries (NCCL's version banner, torchrun children) write to fd 1: keep the real stdout for the one JSON line and
+    point fd 1 at stderr for everything else."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), 'w')
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    _REAL_STDOUT.write(json.dumps(line) + '\n')
+    _REAL_STDOUT.flush()
+
+
 def main():
     args = parse()
+    _claim_stdout()
     if args.impl == 'reference':
         run_reference(args)
         return
@@ -376,11 +391,11 @@ def main():
         res = pop1000_leg(D, data, decoder_weights, tmpdir, generations=max(1, args.generations - 1))
         if D.rank == 0:
             steps = PARAMS['training_epochs'] * 76
-            print(json.dumps({'metric': METRIC, 'value': res['steps_per_s'], 'unit': 'steps/s', 'n_gpus': D.world, 'steps': steps,
+            emit({'metric': METRIC, 'value': res['steps_per_s'], 'unit': 'steps/s', 'n_gpus': D.world, 'steps': steps,
                               'warmup': 0, 'ms_per_step': 1000.0 * res['seconds_per_generation'] / steps, 'higher_is_better': True,
                               'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f16', 'data': 'synthetic',
                               'config': {'workload': 'configs[2]: one population of 1000 SeRANNs sharded over the GPUs, whole generations end to end'},
-                              'pop1000': res}))
+                              'pop1000': res})
         return
 
     # weak scaling: every GPU evaluates its own args.pop individuals drawn from the same architecture mix (independent
@@ -427,8 +442,10 @@ def main():
     e2e = None
     if not args.no_e2e:
         G = max(1, args.generations)
-        pools = [[s for s, _ in pop]] + [[s for s, _ in population(args.pop, args.mix, seed=g)] for g in range(1, G)]
-        r = run_generations(D, dict(PARAMS, num_seranns=args.pop), pools, data, decoder_weights, tmpdir)
+        # weak scaling: the job's population is args.pop per GPU, sharded longest-processing-time-first over the ranks
+        n_job = args.pop * D.world
+        pools = [[s for s, _ in population(n_job, args.mix, seed=g)] for g in range(G)]
+        r = run_generations(D, dict(PARAMS, num_seranns=n_job), pools, data, decoder_weights, tmpdir)
         trained = D.reduce(sum(r['trained']), 'sum')
         steps_gen = r['steps'][0]
         total_steps = steps_gen * len(r['steps'])
@@ -441,7 +458,7 @@ def main():
                'what': 'Experiment.execute() over InProcessPool(B200PopulationWorker): H2D of the data set (once), then per generation '
                        'source compilation, build, 5 x 76 steps, validation, test, replication + readout (R = 10), D2H of metrics and '
                        'offspring, all-gather (N > 1), fertility, multinomial, statistics, SQLite, selection, decode of the offspring; '
-                       'a new generator-sampled population every generation (a random-init autoencoder decodes no valid programs)'}
+                       'a new generator-sampled population of pop x N individuals every generation, sharded over the N ranks (a random-init autoencoder decodes no valid programs)'}
 
     # ---- BASELINE's second figure: one population of 1000 over the N GPUs ---------------------------
     p1000 = None
@@ -464,7 +481,7 @@ def main():
                 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f16', 'data': 'synthetic',
                 'config': workload_config(args, len(irs), D.world), 'roofline': roofline, 'cpu_baseline': cpu, 'e2e': e2e,
                 'pop1000': p1000, 'gpu_launches': int(launches), 'clocks': clocks.summary(), 'wall_s_timed_region': wall}
-        print(json.dumps(line))
+        emit(line)
     if D.world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
@@ -509,7 +526,7 @@ def decode_leg(D, args):
                'sample': f'{m} of the 100000 genotypes through the fp32 torch CPU oracle ({cs:.1f} s)',
                'argmax_mismatches_outside_1e-4_margin': mism, 'tokens_compared': int(clear.sum())}
     if D.rank == 0:
-        print(json.dumps({'metric': 'autoencoder-decode genotypes/s', 'value': n_total / dev_s, 'unit': 'genotypes/s', 'n_gpus': D.world,
+        emit({'metric': 'autoencoder-decode genotypes/s', 'value': n_total / dev_s, 'unit': 'genotypes/s', 'n_gpus': D.world,
                           'steps': 1, 'warmup': 1, 'ms_per_step': 1000.0 * dev_s, 'higher_is_better': True, 'scaling': 'strong',
                           'vs_baseline': None, 'dtype': 'fp16 hi/lo split table x exact one-hot operand, fp32 accumulate', 'data': 'synthetic',
                           'config': {'workload': 'configs[3]: decode 100000 synthetic genotypes (seed 1) with a random-init ribosomal autoencoder (seed 4), max_tokens 350, vocabulary 40'},
@@ -518,7 +535,7 @@ def decode_leg(D, args):
                                        'note': 'algorithmic fp32 FLOPs (86.1 MFLOP / genotype) over the device time of the decode kernels; the '
                                                'kernel issues 2 fp16 products per fp32 product (one-hot left operand exact in fp16, table split hi + lo)', 'kernel_stats': stats},
                           'e2e': {'value': n_total / wall, 'unit': 'genotypes/s', 'h2d_bytes_per_step': int(bits.nbytes), 'd2h_bytes_per_step': int(tok.nbytes)},
-                          'cpu_baseline': cpu, 'clocks': clocks.summary()}))
+                          'cpu_baseline': cpu, 'clocks': clocks.summary()})
     ae.close()
 
 
@@ -553,13 +570,13 @@ def eval_leg(D, args):
     n = len(pool)
     if D.rank == 0:
         steps = K * n * params['training_epochs'] * 76
-        print(json.dumps({'metric': 'serann_evaluation genotypes/s', 'value': n / secs, 'unit': 'genotypes/s', 'n_gpus': D.world, 'steps': n,
+        emit({'metric': 'serann_evaluation genotypes/s', 'value': n / secs, 'unit': 'genotypes/s', 'n_gpus': D.world, 'steps': n,
                           'warmup': 0, 'ms_per_step': 1000.0 * secs / n, 'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None,
                           'dtype': 'f16', 'data': 'synthetic',
                           'config': {'workload': f'configs[4]: {n} genotypes x {K} re-initialisations x 380 steps at batch {BATCH}, R = {R} offspring each, decode + validity'},
                           'train_steps_per_s': steps / secs,
                           'rank0': {'validation_accuracy_mean': float(np.nanmean(accs)), 'validation_accuracy_std': float(np.nanstd(accs)),
-                                    'mutation_rate_mean': float(np.mean(rates))}}))
+                                    'mutation_rate_mean': float(np.mean(rates))}})
     ev.close()
     ae.close()
 
