@@ -576,42 +576,59 @@ k_maxpool_bwd(const Prob* __restrict__ probs, const int* __restrict__ prefix, in
             const unsigned bu = pix / (unsigned)HoWo; const long long b = bu; const int rem = (int)(pix - bu * (unsigned)HoWo);
             const int ho = rem / p.Wo, wo = rem - ho * p.Wo;
             const long long oo = out_row_off(pix, HoWo, p.out_bs, p.Fs) + c0;
-            float mx[8], go[8]; int arg[8];
-            if (cw == 8) { const Half8 m8 = ld8(p.out + oo), g8 = ld8(p.gout + oo);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) { mx[j] = __half2float(m8.v[j]); go[j] = __half2float(g8.v[j]); arg[j] = -1; }
-            } else { mx[0] = __half2float(p.out[oo]); go[0] = __half2float(p.gout[oo]); arg[0] = -1; }
-            const __half* ib = in + b * in_bs + ((long long)(ho * p.kh) * p.W + wo * p.kw) * Cs + c0;
-            for (int i = 0; i < p.kh; ++i)
-                for (int jj = 0; jj < p.kw; ++jj) {
-                    const __half* s = ib + ((long long)i * p.W + jj) * Cs;
-                    if (cw == 8) { const Half8 e = ld8(s);
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) { const float v = __half2float(e.v[j]); if (arg[j] < 0 && (v == mx[j] || (v != v && mx[j] != mx[j]))) arg[j] = i * p.kw + jj; }
-                    } else { const float v = __half2float(*s); if (arg[0] < 0 && (v == mx[0] || (v != v && mx[0] != mx[0]))) arg[0] = i * p.kw + jj; }
-                }
             const int h_end = (ho == p.Ho - 1) ? p.H - ho * p.kh : p.kh;      // also the uncovered rows / columns
             const int w_end = (wo == p.Wo - 1) ? p.W - wo * p.kw : p.kw;
+            const __half* ib = in + b * in_bs + ((long long)(ho * p.kh) * p.W + wo * p.kw) * Cs + c0;
             __half* db = p.din + b * p.in_bs + ((long long)(ho * p.kh) * p.W + wo * p.kw) * Cs + c0;
+            if (cw == 8) {
+                // packed: an element takes the window's gradient iff it equals the maximum (or both are NaN) and no earlier
+                // element of the window did; everything is bit masks on half pairs, no conversions (pad channels carry a
+                // zero gradient, so they need no mask of their own)
+                const Half2x4 m8 = as_h2(ld8(p.out + oo)), g8 = as_h2(ld8(p.gout + oo));
+                unsigned found[4] = {0u, 0u, 0u, 0u}, nan_m[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) nan_m[k] = __hneu2_mask(m8.v[k], m8.v[k]);
+                for (int i = 0; i < h_end; ++i)
+                    for (int jj = 0; jj < w_end; ++jj) {
+                        __half* d = db + ((long long)i * p.W + jj) * Cs;
+                        Half2x4 o;
+                        if (i < p.kh && jj < p.kw) {
+                            const Half2x4 e = as_h2(ld8(ib + ((long long)i * p.W + jj) * Cs));
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const unsigned eq = __heq2_mask(e.v[k], m8.v[k]) | (__hneu2_mask(e.v[k], e.v[k]) & nan_m[k]);
+                                const unsigned take = eq & ~found[k];
+                                found[k] |= eq;
+                                unsigned bits = *reinterpret_cast<const unsigned*>(&g8.v[k]) & take;
+                                o.v[k] = *reinterpret_cast<__half2*>(&bits);
+                            }
+                        } else {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) o.v[k] = __float2half2_rn(0.f);
+                        }
+                        if (p.din_acc) {
+                            const Half2x4 prev = as_h2(ld8(d));
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) o.v[k] = __hadd2_rn(o.v[k], prev.v[k]);
+                        }
+                        st8(d, as_h8(o));
+                    }
+                continue;
+            }
+            float mx = __half2float(p.out[oo]), go = __half2float(p.gout[oo]);
+            int arg = -1;
+            for (int i = 0; i < p.kh; ++i)
+                for (int jj = 0; jj < p.kw; ++jj) {
+                    const float v = __half2float(ib[((long long)i * p.W + jj) * Cs]);
+                    if (arg < 0 && (v == mx || (v != v && mx != mx))) arg = i * p.kw + jj;
+                }
             for (int i = 0; i < h_end; ++i)
                 for (int jj = 0; jj < w_end; ++jj) {
                     __half* d = db + ((long long)i * p.W + jj) * Cs;
                     const int id = (i < p.kh && jj < p.kw) ? i * p.kw + jj : -2;
-                    if (cw == 8) {
-                        Half8 o;
-                        if (p.din_acc) o = ld8(d);
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            float v = (arg[j] == id && c0 + j < p.C) ? go[j] : 0.f;
-                            if (p.din_acc) v = rh(v) + __half2float(o.v[j]);
-                            o.v[j] = __float2half_rn(v);
-                        }
-                        st8(d, o);
-                    } else {
-                        float v = (arg[0] == id) ? go[0] : 0.f;
-                        if (p.din_acc) v = rh(v) + __half2float(*d);
-                        *d = __float2half_rn(v);
-                    }
+                    float v = (arg == id) ? go : 0.f;
+                    if (p.din_acc) v = rh(v) + __half2float(*d);
+                    *d = __float2half_rn(v);
                 }
         }
         return;
