@@ -796,11 +796,27 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                 }
                 continue;
             }
+            if (!t_tm) {
+                // gathered tiles: the k loop is instantiated once per path so that it carries no per-k-block path tests
+                auto k_loops = [&](auto FAST) {
+                    for (int s = 0; s < lsub; ++s) {
+                        if (MODE == TC_FWD) fwd_rows(t_m0 + s * TC_BM);
+                        for (int kb = lkb0; kb < lkb0 + lnk; ++kb) {
+                            mbar_wait(sEmpty + sb * 8, ph);
+                            load_stage(sb, kb, FAST);
+                            if (SCALAR_A) fence_proxy_async();       // the element-wise gather used ordinary shared-memory stores
+                            stage_issued();
+                        }
+                    }
+                };
+                if (t_fast) k_loops(std::true_type{});
+                else k_loops(std::false_type{});
+                continue;
+            }
             for (int s = 0; s < lsub; ++s) {
-                if (MODE == TC_FWD) fwd_rows(t_m0 + s * TC_BM);
                 for (int kb = lkb0; kb < lkb0 + lnk; ++kb) {
                     mbar_wait(sEmpty + sb * 8, ph);
-                    if (t_tm) {
+                    {
                         // row-major operands: one thread issues the tile copies
                         const uint32_t bar = sFull + sb * 8;
                         if (tid == 0) {
@@ -828,11 +844,6 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                             mbar_arrive(bar);
                         }
                         if (++sb == STAGES) { sb = 0; ph ^= 1u; }
-                    } else {
-                        if (t_fast) load_stage(sb, kb, std::true_type{});
-                        else load_stage(sb, kb, std::false_type{});
-                        if (SCALAR_A) fence_proxy_async();       // the element-wise gather used ordinary shared-memory stores
-                        stage_issued();
                     }
                 }
             }
