@@ -3,7 +3,8 @@
 Same class surface as the reference ``RibosomalAutoencoder``
 (``evolutionary_experiment/logic/ribosomal_autoencoder.py:12-83``) for the decode direction; the
 daemon child process and its queues are gone (the decode runs in-process on the GPU).  ``encode_*``
-is outside the per-generation path (never called by the evolution loop) and raises.
+is outside the per-generation path (never called by the evolution loop): it runs the PyTorch restatement of the
+inference net from ``tools/train_autoencoder.py`` when the weights carry an encoder.
 """
 from __future__ import annotations
 
@@ -33,6 +34,7 @@ class RibosomalAutoencoder:
         dk = f32(weights['dense_kernel'], (L * 32, self._max_serann_tokens * self._V))
         db = f32(weights['dense_bias'], (self._max_serann_tokens * self._V,))
         bn2 = np.ascontiguousarray(np.stack([f32(weights[f'bn2_{k}'], (self._V,)) for k in ('gamma', 'beta', 'mean', 'var')]))
+        self._weights = weights
         self._d = C.c_void_p()
         _engine._check(self._lib.srn_decoder_create(device, self._G, self._max_serann_tokens, self._V,
                                                     _engine._ptr(ck), _engine._ptr(cb), _engine._ptr(bn1),
@@ -92,7 +94,29 @@ class RibosomalAutoencoder:
     def decode_to_string(self, encoded_serann_codes) -> List[str]:
         return self.sequence_to_string(self.decode_to_sequence(encoded_serann_codes))
 
-    def encode_sequence(self, *_a, **_k):
-        raise NotImplementedError('encoding is outside the per-generation path (SURVEY.md section 8f, rank 4)')
+    def encode_sequence(self, serann_token_index_sequences) -> np.ndarray:
+        """Token-id sequences (n, max_tokens) -> genotypes (n, G): argmax of the inference net's logits (reference
+        ``ribosomal_autoencoder.py:40-46,119-120``; ``model.py:17-33,101-104``).  Encoding is dataset preparation, never
+        called by the evolution loop, and not a CUDA entry point of this library: it runs the PyTorch restatement of
+        the inference net in ``tools/train_autoencoder.py`` on the ``enc_*`` arrays that tool exports."""
+        enc = {k: v for k, v in self._weights.items() if k.startswith('enc_')}
+        if not enc:
+            raise NotImplementedError('these weights hold no encoder (enc_* arrays, written by tools/train_autoencoder.py)')
+        import importlib.util
+        import pathlib
+        import torch
+        spec = importlib.util.spec_from_file_location('train_autoencoder', pathlib.Path(__file__).resolve().parent.parent / 'tools' / 'train_autoencoder.py')
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        model = mod.GeneticAutoencoder(self._G, self._max_serann_tokens, self._V, embedding=int(enc['enc_emb'].shape[1]))
+        sd = model.state_dict()
+        for k in sd:
+            if k.startswith(('emb', 'e_')):
+                sd[k] = torch.as_tensor(enc['enc_' + k.replace('.', '_')])
+        model.load_state_dict(sd)
+        return model.encode(torch.as_tensor(np.asarray(serann_token_index_sequences)).long()).numpy()
 
-    encode_string = encode_sequence
+    def encode_string(self, serann_codes) -> np.ndarray:
+        """Reference ``ribosomal_autoencoder.py:48-57``: tokenise, truncate / pad with <PAD>, encode."""
+        from .vocabulary import encode_tokens
+        return self.encode_sequence(np.stack([encode_tokens(s, self._max_serann_tokens) for s in serann_codes]))
