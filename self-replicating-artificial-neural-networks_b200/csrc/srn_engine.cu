@@ -1221,7 +1221,7 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
 
 // persistent tensor-core launch: as many CTAs as fit the machine (shared memory bound), each walking the tile table
 static int tc_grid(srn_engine* h, int total, int BN) {
-    const int per_sm = std::max(1, std::min(4, (227 * 1024) / (tc_smem_bytes(BN) + 1024)));
+    const int per_sm = std::max(1, std::min(4, (228 * 1024) / (tc_smem_bytes(BN) + 1024)));      // 228 KB per SM, 1 KB reserved per CTA
     return std::min(total, h->num_sms * per_sm);
 }
 #define LAUNCH_TC1(cat, MODE, SCALAR, pass, BN_)                                                   \

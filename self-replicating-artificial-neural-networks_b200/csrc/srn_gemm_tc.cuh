@@ -54,7 +54,8 @@ constexpr int TC_LUT = 512;            // 16-byte k chunks per lookup table: red
 __host__ __device__ constexpr int tc_stages(int BN) { return BN <= 64 ? 4 : (BN <= 128 ? 3 : 4); }
 // B tiles are stored with 128-byte rows (swizzle-128B atoms), so a 32-wide MN-major tile takes the room of a 64-wide one
 __host__ __device__ constexpr int tc_b_bytes(int BN) { return (BN < 64 ? 64 : BN) * TC_BK * 2; }
-__host__ __device__ constexpr int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + tc_b_bytes(BN)) + 384 + TC_RING * TC_TILE_BYTES + 2 * TC_LUT * 8; }
+__host__ __device__ constexpr int tc_bias_bytes(int BN) { return 4 * BN * 2; }      // the tile's bias chunk, one copy per epilogue warp
+__host__ __device__ constexpr int tc_smem_bytes(int BN) { return tc_stages(BN) * (TC_A_BYTES + tc_b_bytes(BN)) + 384 + TC_RING * TC_TILE_BYTES + 2 * TC_LUT * 8 + tc_bias_bytes(BN); }
 __host__ __device__ constexpr int tc_acc_cols(int BN) { return BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256)); }
 // TMEM accumulators per CTA: 256 columns (two CTAs share the SM's 512) hold 8, 4 or 2 of them; a CTA that has the SM
 // alone (BN = 256) takes all 512 columns for two.  Short tiles (one or two k-blocks) are bound by the round trip
@@ -257,6 +258,16 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// same, raw bits into the first 16 of 32 registers (narrow tiles)
+__device__ __forceinline__ void tmem_ld16_raw(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+}
 // 32 consecutive fp32 columns of this thread's TMEM lane (one wait for the whole batch)
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
@@ -269,6 +280,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
         : "r"(taddr)
         : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+}
+// epilogue traffic goes straight to the global window (tile descriptors hold generic pointers, which would compile
+// to generic LD / ST): read-only 16-byte loads, 16- and 32-byte stores
+__device__ __forceinline__ uint4 ldg16(const __half* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ void stg16(__half* p, const uint4& v) {
+    asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void stg32(__half* p, const uint4& a, const uint4& b) {      // p is 32-byte aligned
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};\n" ::"l"(p), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w),
+                 "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w) : "memory");
 }
 // two fp32 accumulators -> packed fp16 (round to nearest even), low half = first
 __device__ __forceinline__ __half2 pack_h2(uint32_t lo, uint32_t hi) {
@@ -426,6 +447,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
     const uint32_t sTEmpty = sTFull + 8 * 8;
     const uint32_t sSlot = sTEmpty + 8 * 8;
     const uint32_t sLut = sFull + 384;                    // two k-chunk tables of TC_LUT entries (this tile, next tile)
+    const uint32_t sBias = sLut + 2 * TC_LUT * 8;         // forward: bias of the current tile's columns, per epilogue warp
     TcTile* ring = reinterpret_cast<TcTile*>(sgen + (sRing - sbase));
     volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(sgen + (sSlot - sbase));
     int2* lut = reinterpret_cast<int2*>(sgen + (sLut - sbase));
@@ -456,7 +478,8 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = *slot_ptr;
+    // (every role reads the TMEM base from the slot when it needs it: held in a register across the roles it was spilled
+    // to local memory and reloaded once per accumulator hand-over)
 
     if (warp < TC_LW) {
         // =================================================================== loaders (8 warps)
@@ -857,7 +880,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
         // UTCHMMA / UTCBAR), and with tiles of one to five k-blocks of a 128 x 32 tile (32 tensor-pipe cycles each)
         // that single thread's instruction stream bounded the whole kernel (ncu: the issuer warp never stalled).
         {
-            const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
+            const uint32_t tmem_u = __shfl_sync(0xffffffffu, *slot_ptr, 0);
             auto bcast = [](int v) { return __shfl_sync(0xffffffffu, v, 0); };
             int st = 0; uint32_t fph = 0;     // ring stage and the parity of its "full" barrier
             // K-major operands advance 32 bytes per K = 16 step inside the 128-byte rows, MN-major ones two 8-k atoms
@@ -924,6 +947,80 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
     } else {
         // =================================================================== epilogue (4 warps)
         const int ewarp = warp & 3;      // TMEM lanes 32 * ewarp .. + 31
+        const uint4* wbias = reinterpret_cast<const uint4*>(sgen + (sBias - sbase)) + ewarp * (BN / 8);
+        // Forward tiles without k-split.  (Per-tile values are read from the ring slot per sub-tile on purpose: hoisted, they
+        // are spilled to local memory under the 72-register cap, and local loads miss the L1 that the cp.async traffic churns.)
+        auto epilogue_fwd = [&](const TcTile& T, int sub, uint32_t tacc) {
+            const Prob& p = T.p;
+            const int e_m0 = T.m0, e_n0 = T.n0, e_Ncols = T.Ncols, e_numma = T.n_umma, e_Fs = p.Fs, e_act = p.act, e_Mrows = T.Mrows, e_HoWo = p.Ho * p.Wo;
+            const int e_out_bs = p.out_bs; __half* const e_out = p.out; const bool e_flat = e_out_bs == e_HoWo * e_Fs;
+            const int mrow = e_m0 + sub * TC_BM + ewarp * 32 + lane, n0 = e_n0, Ncols = e_Ncols, act = e_act;
+            const uint32_t trow = tacc + ((uint32_t)(ewarp * 32) << 16);
+            __half* orow = nullptr;
+            if (mrow < e_Mrows) {
+                if (e_flat) orow = e_out + (long long)mrow * e_Fs;      // samples back to back
+                else {
+                    const int b = fdiv(mrow, T.fd_rows), rem = mrow - b * e_HoWo;
+                    orow = e_out + (long long)b * e_out_bs + (long long)rem * e_Fs;
+                }
+            }
+            // 32 accumulator columns per TMEM read (16 when that is all the tile has).  Linear and ReLU layers round, add
+            // the bias and clamp as packed halves (one rounding per TensorFlow op, as the float path does); sigmoid goes
+            // through fp32.  Rows are stored 32 bytes at a time when aligned.
+            for (int cb = 0; cb < e_numma; cb += 32) {
+                const int left = Ncols - n0 - cb;                       // real columns from here on
+                const int nch = min(4, (left + 7) >> 3), nfull = min(4, left >> 3);
+                uint32_t r[32];
+                if (e_numma - cb > 16) tmem_ld32(trow + cb, r);
+                else tmem_ld16_raw(trow + cb, r);
+                if (!orow) continue;
+                __half* dst = orow + n0 + cb;
+                if (act != 2) {
+                    const __half2 zero = __float2half2_rn(0.f);
+                    const bool wide = nfull == 4 && (reinterpret_cast<uintptr_t>(dst) & 31) == 0;
+#pragma unroll
+                    for (int h16 = 0; h16 < 2; ++h16) {
+                        if (h16 * 2 >= nfull) break;
+                        uint4 o[2];
+#pragma unroll
+                        for (int q = 0; q < 2; ++q) {
+                            const int h8 = h16 * 2 + q;
+                            const uint4 bq = wbias[(cb >> 3) + h8];
+                            const __half2* b2 = reinterpret_cast<const __half2*>(&bq);
+                            __half2* o2 = reinterpret_cast<__half2*>(&o[q]);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                __half2 z = __hadd2(pack_h2(r[h8 * 8 + 2 * j], r[h8 * 8 + 2 * j + 1]), b2[j]);
+                                if (act == 1) z = __hmax2_nan(z, zero);
+                                o2[j] = z;
+                            }
+                        }
+                        if (wide || (nfull >= h16 * 2 + 2 && (reinterpret_cast<uintptr_t>(dst + h16 * 16) & 31) == 0)) stg32(dst + h16 * 16, o[0], o[1]);
+                        else {
+                            stg16(dst + h16 * 16, o[0]);
+                            if (h16 * 2 + 1 < nfull) stg16(dst + h16 * 16 + 8, o[1]);
+                        }
+                    }
+                    if (nch == nfull) continue;
+                }
+                // sigmoid layers, and the chunk that holds the last real columns when F is not a multiple of 8
+#pragma unroll
+                for (int h8 = 0; h8 < 4; ++h8) {
+                    if (h8 >= nch || (act != 2 && h8 < nfull)) continue;
+                    const int n = n0 + cb + h8 * 8;
+                    const uint4 bq = wbias[(cb >> 3) + h8];
+                    const Half8 bv = *reinterpret_cast<const Half8*>(&bq);
+                    Half8 o;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float z = 0.f;
+                        if (n + j < Ncols) z = act_forward(rh(rh(__uint_as_float(r[h8 * 8 + j])) + __half2float(bv.v[j])), act);
+                        o.v[j] = __float2half_rn(z);
+                    }
+                    stg16(dst + h8 * 8, *reinterpret_cast<const uint4*>(&o));
+                }
+            }
+        };
         auto epilogue = [&](const TcTile& T, int sub, uint32_t tacc, int ewarp) {
             const Prob& p = T.p;
             const int Cs = p.Cs, Fs = p.Fs;
@@ -934,8 +1031,11 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                 const __half* bias = p.bias; const int act = p.act;
                 __half* orow = nullptr;
                 if (mrow < T.Mrows) {
-                    const int b = fdiv(mrow, T.fd_rows), rem = mrow - b * HoWo;
-                    orow = p.out + (long long)b * p.out_bs + (long long)rem * Fs;
+                    if (p.out_bs == HoWo * Fs) orow = p.out + (long long)mrow * Fs;      // samples back to back
+                    else {
+                        const int b = fdiv(mrow, T.fd_rows), rem = mrow - b * HoWo;
+                        orow = p.out + (long long)b * p.out_bs + (long long)rem * Fs;
+                    }
                 }
                 if (T.nsplit > 1) {
                     // split-K: add this part of the reduction into the fp32 scratch row; the warp that arrives last for
@@ -980,39 +1080,6 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                     }
                     if (lane == 0) *cnt = 0;
                     return;
-                }
-                // 32 accumulator columns per TMEM read.  Linear and ReLU layers round, add the bias and clamp as packed
-                // halves (one rounding per TensorFlow op, as the float path does); sigmoid goes through fp32.
-                for (int cb = 0; cb < T.n_umma; cb += 32) {
-                    uint32_t r[32];
-                    tmem_ld32(trow + cb, r);
-                    if (!orow) continue;
-#pragma unroll
-                    for (int h8 = 0; h8 < 4; ++h8) {
-                        const int n = n0 + cb + h8 * 8;
-                        if (n >= Ncols) break;
-                        const Half8 bv = ld8(bias + n);      // bias arrays are padded to 8 elements in the arena
-                        Half8 o;
-                        if (act != 2 && n + 8 <= Ncols) {
-                            const __half2* b2 = reinterpret_cast<const __half2*>(&bv);
-                            __half2* o2 = reinterpret_cast<__half2*>(&o);
-                            const __half2 zero = __float2half2_rn(0.f);
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                __half2 z = __hadd2(pack_h2(r[h8 * 8 + 2 * j], r[h8 * 8 + 2 * j + 1]), b2[j]);
-                                if (act == 1) z = __hmax2_nan(z, zero);
-                                o2[j] = z;
-                            }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                float z = 0.f;
-                                if (n + j < Ncols) z = act_forward(rh(rh(__uint_as_float(r[h8 * 8 + j])) + __half2float(bv.v[j])), act);
-                                o.v[j] = __float2half_rn(z);
-                            }
-                        }
-                        st8(orow + n, o);
-                    }
                 }
             } else if (MODE == TC_DGRAD) {
                 __half* drow = nullptr;
@@ -1093,13 +1160,21 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
         for (int j = 0; j < my_tiles; ++j) {
             const TcTile& T = ring[j % TC_RING];
             const int nsub = T.nsub;
+            if (MODE == TC_FWD) {
+                // this warp's copy of the tile's bias columns (bias arrays are padded to 8 elements in the arena)
+                __syncwarp();
+                if (lane * 8 < T.n_umma && T.n0 + lane * 8 < T.Ncols)
+                    const_cast<uint4*>(wbias)[lane] = ldg16(T.p.bias + T.n0 + lane * 8);
+                __syncwarp();
+            }
             for (int s = 0; s < nsub; ++s, ++jj) {
                 const int acc = jj % NACC;
                 // long tiles: back off while waiting so that the spin does not take issue slots from the loaders
                 if (T.nk > 32) mbar_wait_relaxed(sTFull + acc * 8, (uint32_t)((jj / NACC) & 1));
                 else mbar_wait(sTFull + acc * 8, (uint32_t)((jj / NACC) & 1));
                 tc_fence_after();
-                epilogue(T, s, tmem + (uint32_t)(acc * acc_cols), ewarp);
+                if (MODE == TC_FWD && T.nsplit == 1) epilogue_fwd(T, s, *slot_ptr + (uint32_t)(acc * acc_cols));
+                else epilogue(T, s, *slot_ptr + (uint32_t)(acc * acc_cols), ewarp);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(sTEmpty + acc * 8);
@@ -1108,7 +1183,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == TC_LW) tmem_dealloc(tmem, (uint32_t)tmem_cols);
+    if (warp == TC_LW) tmem_dealloc(*slot_ptr, (uint32_t)tmem_cols);
 }
 
 }  // namespace srn
