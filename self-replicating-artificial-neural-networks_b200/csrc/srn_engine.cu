@@ -178,6 +178,9 @@ struct Cached {
     int total[P_COUNT] = {};
     TcTile* tiles[P_COUNT] = {};   // tensor-core passes: one descriptor per tile, heaviest first
     std::vector<TcTile> host_fwd;  // forward tiles kept on the host for the per-level merged tables
+    std::vector<SplitFin> host_fin;   // split-K forward problems of this bucket (k_splitk_finish), blk0 relative to the bucket
+    SplitFin* fin = nullptr;
+    int fin_blocks = 0;
 };
 
 struct Group {
@@ -263,7 +266,7 @@ struct srn_engine {
     DevPool pool;
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;      // srn_fit's timing events
     // forward launches of one depth level that run the same kernel (same N tile) share one tile table: key (nb, depth, BN, mode)
-    struct MergedFwd { TcTile* dev = nullptr; int total = 0; int first_group = -1; };
+    struct MergedFwd { TcTile* dev = nullptr; int total = 0; int first_group = -1; SplitFin* fin = nullptr; int nfin = 0, fin_blocks = 0; };
     std::map<std::tuple<int, int, int, int>, MergedFwd> merged_fwd;
 };
 
@@ -1093,13 +1096,16 @@ static bool dense_tensor_maps(const Prob& p, int nb, int mode, int BN, CUtensorM
     return a_ok && g_ok && encode_matrix(&m[0], p.in, M, p.Cs, a_pitch, 64) && encode_matrix(&m[1], p.gout, M, p.Fs, g_pitch, 64);
 }
 
-// most k-splits a forward bucket asks for: about two tiles per resident CTA over the whole bucket
+// most k-splits a forward bucket asks for: about one tile per SM over the whole bucket.  (Every split costs an fp32 atomic
+// pass over its output tile, and in the overlapped step the other launches of the level hide a long tile: asking for four
+// tiles per SM measured 0.13 ms per step slower, no splits at all the same step but 0.6 ms more serialised time.)
 static int group_smax(const Group& g, int nb) {
     if (g.tc != 1) return 1;
     long long base = 0;
     for (const Prob& p : g.h) base += tc_fwd_split_tiles(p, nb, TC_BN[g.cfgF]);
     if (base == 0) return 1;
-    const long long want = (4LL * 148 + base - 1) / base;
+    static const long long target = getenv("SRN_SPLIT_TARGET") ? atoll(getenv("SRN_SPLIT_TARGET")) : 1;      // A/B switch
+    const long long want = (target * 148 + base - 1) / base;
     return (int)std::max(1LL, std::min(32LL, want));
 }
 
@@ -1186,6 +1192,15 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
                         tt[t].sk_acc = reinterpret_cast<float*>(buf);
                         tt[t].sk_cnt = reinterpret_cast<int*>(buf + acc_bytes);
                     }
+                    SplitFin f;
+                    f.acc = reinterpret_cast<float*>(buf); f.out = p.out; f.bias = p.bias; f.rows = (int)rows; f.Fs = p.Fs; f.F = p.F; f.act = p.act;
+                    f.HoWo = p.Ho * p.Wo; f.out_bs = p.out_bs; f.blk0 = c.fin_blocks;
+                    c.fin_blocks += (int)((rows * (size_t)(p.Fs / 8) + 255) / 256);
+                    c.host_fin.push_back(f);
+                }
+                if (!c.host_fin.empty()) {
+                    POOL_ALLOC(c.fin, SplitFin, c.host_fin.size() * sizeof(SplitFin));
+                    CK(cudaMemcpy(c.fin, c.host_fin.data(), c.host_fin.size() * sizeof(SplitFin), cudaMemcpyHostToDevice));
                 }
             }
             if (g.tc == 1) {        // any problem with a 1 x 1 window over row-major operands (Dense, first layers over the shared im2col matrix)
@@ -1309,7 +1324,10 @@ static int fwd_group(srn_engine* h, Group& g, int nb, const Inputs& I, bool trai
             }
             if (g.tc) {
                 const int BN = TC_BN[g.cfgF];
-                if (g.tc == 1) LAUNCH_TC(SRN_CAT_GEMM_FWD, TC_FWD, false, P_FWD, BN);
+                if (g.tc == 1) {
+                    LAUNCH_TC(SRN_CAT_GEMM_FWD, TC_FWD, false, P_FWD, BN);
+                    if (c->fin_blocks) LAUNCH(SRN_CAT_GEMM_FWD, k_splitk_finish, c->fin_blocks, 256, c->fin, (int)c->host_fin.size());
+                }
                 else LAUNCH_TC(SRN_CAT_GEMM_FWD, TC_FWD, true, P_FWD, BN);
                 break;
             }
@@ -1400,9 +1418,13 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training, i
                 auto it = h->merged_fwd.find(key);
                 if (it == h->merged_fwd.end()) {
                     std::vector<TcTile> all;
+                    std::vector<SplitFin> fins;
+                    int fin_blocks = 0;
                     for (Group* g : by_bn[b]) {
                         Cached* c; rc = plan_for(h, *g, nb, &c); if (rc) return rc;
                         all.insert(all.end(), c->host_fwd.begin(), c->host_fwd.end());
+                        for (SplitFin f : c->host_fin) { f.blk0 += fin_blocks; fins.push_back(f); }
+                        fin_blocks += c->fin_blocks;
                     }
                     std::stable_sort(all.begin(), all.end(), [](const TcTile& x, const TcTile& y) { return x.nk * x.nsub > y.nk * y.nsub; });
                     srn_engine::MergedFwd m;
@@ -1411,6 +1433,11 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training, i
                     if (m.total) {
                         POOL_ALLOC(m.dev, TcTile, all.size() * sizeof(TcTile));
                         CK(cudaMemcpy(m.dev, all.data(), all.size() * sizeof(TcTile), cudaMemcpyHostToDevice));
+                    }
+                    if (!fins.empty()) {
+                        POOL_ALLOC(m.fin, SplitFin, fins.size() * sizeof(SplitFin));
+                        CK(cudaMemcpy(m.fin, fins.data(), fins.size() * sizeof(SplitFin), cudaMemcpyHostToDevice));
+                        m.nfin = (int)fins.size(); m.fin_blocks = fin_blocks;
                     }
                     it = h->merged_fwd.emplace(key, m).first;
                 }
@@ -1425,6 +1452,7 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training, i
                         case 128: LAUNCH_SMEM(SRN_CAT_GEMM_FWD, (k_gemm_tc<TC_FWD, false, 128>), tc_grid(h, m.total, 128), TC_THREADS, tc_smem_bytes(128), m.dev, m.total, nb, I); break;
                         default: LAUNCH_SMEM(SRN_CAT_GEMM_FWD, (k_gemm_tc<TC_FWD, false, 256>), tc_grid(h, m.total, 256), TC_THREADS, tc_smem_bytes(256), m.dev, m.total, nb, I); break;
                     }
+                    if (m.fin_blocks) LAUNCH(SRN_CAT_GEMM_FWD, k_splitk_finish, m.fin_blocks, 256, m.fin, m.nfin);
                     return (int)SRN_OK;
                 });
             }

@@ -335,7 +335,7 @@ struct __align__(16) TcTile {
     int klast;         // K = 16 steps of the last k-block (1..4): the tail of the reduction is neither loaded nor multiplied
     int nsub;          // 128-row sub-tiles m0, m0 + 128, .. covered by this descriptor (forward only, else 1)
     // split-K (forward, few output tiles and a long reduction): this tile covers k-blocks kb0 .. kb0 + nk - 1 of nsplit
-    // splits; partial sums meet in the fp32 scratch sk_acc [Mrows][Fs], sk_cnt[4 * sk_tile + warp] counts arrivals
+    // splits; partial sums meet in the fp32 scratch sk_acc [Mrows][Fs] (k_splitk_finish turns them into the output); sk_cnt is unused
     int kb0, nsplit, sk_tile;
     int pack;          // forward sub-tiles per ring stage (tc_fwd_pack), else 1
     float* sk_acc;
@@ -426,6 +426,37 @@ __device__ __forceinline__ int2 tc_k_entry(const KGeo& g, int chunk) {
                          (int)(0x80000000u | (uint32_t)ki | ((uint32_t)kj << 8) | ((uint32_t)(cp >> 3) << 16)));
     const int nvalid = min(8, max(0, g.C - cp));
     return make_int2(2 * ((ki * g.ww + kj) * g.cs + cp), (int)(0x80000000u | (uint32_t)(ij * g.C + cp) | ((uint32_t)nvalid << 20)));
+}
+
+// Split-K forward problems: the GEMM kernel adds the partial sums of every split into an fp32 scratch matrix [rows][Fs];
+// this kernel (launched behind it on the same stream) adds the bias, applies the activation, stores fp16 and leaves the
+// scratch zeroed for the next launch.  One thread per 8 columns, consecutive threads on consecutive chunks of a row.
+// (As the last-arriving epilogue warp's job, this pass was a chain of dependent L2 round trips per thread that outlasted
+// the tile's whole reduction, and its registers counted against the 72 of the main loops.)
+struct SplitFin { float* acc; __half* out; const __half* bias; int rows, Fs, F, act, HoWo, out_bs, blk0; };
+static __global__ void __launch_bounds__(256) k_splitk_finish(const SplitFin* __restrict__ fins, int nfin) {
+    int i = 0;
+    while (i + 1 < nfin && (int)blockIdx.x >= fins[i + 1].blk0) ++i;
+    const SplitFin f = fins[i];
+    const int cpr = f.Fs >> 3;                                     // 8-column chunks per row
+    const long long chunk = (long long)(blockIdx.x - f.blk0) * 256 + threadIdx.x;
+    if (chunk >= (long long)f.rows * cpr) return;
+    const int row = (int)(chunk / cpr), n = (int)(chunk - (long long)row * cpr) * 8;
+    float* a = f.acc + (long long)row * f.Fs + n;
+    const float4 x0 = __ldcg(reinterpret_cast<const float4*>(a)), x1 = __ldcg(reinterpret_cast<const float4*>(a + 4));
+    const float v[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+    const Half8 bv = ld8(f.bias + n);                              // bias arrays are padded to 8 elements in the arena
+    Half8 o;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        float z = 0.f;
+        if (n + j < f.F) z = act_forward(rh(rh(v[j]) + __half2float(bv.v[j])), f.act);
+        o.v[j] = __float2half_rn(z);
+    }
+    const int b = row / f.HoWo, rem = row - b * f.HoWo;
+    st8(f.out + (long long)b * f.out_bs + (long long)rem * f.Fs + n, o);
+    __stcg(reinterpret_cast<float4*>(a), make_float4(0.f, 0.f, 0.f, 0.f));
+    __stcg(reinterpret_cast<float4*>(a + 4), make_float4(0.f, 0.f, 0.f, 0.f));
 }
 
 template <int MODE, bool SCALAR_A, int BN>
@@ -1021,6 +1052,13 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                 }
             }
         };
+        uint32_t rel_bar = 0;      // "tmem_empty" barrier of the accumulator in hand; an epilogue that releases it early (all TMEM reads done) clears this
+        auto release_acc = [&]() {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(rel_bar);
+            rel_bar = 0;
+        };
         auto epilogue = [&](const TcTile& T, int sub, uint32_t tacc, int ewarp) {
             const Prob& p = T.p;
             const int Cs = p.Cs, Fs = p.Fs;
@@ -1038,8 +1076,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                     }
                 }
                 if (T.nsplit > 1) {
-                    // split-K: add this part of the reduction into the fp32 scratch row; the warp that arrives last for
-                    // its 32 rows reads the sums back, applies bias and activation, stores fp16 and leaves zeros behind
+                    // split-K: add this part of the reduction into the fp32 scratch row
                     float* arow = mrow < T.Mrows ? T.sk_acc + (long long)mrow * Fs : nullptr;
                     for (int cb = 0; cb < T.n_umma; cb += 32) {
                         uint32_t r[32];
@@ -1053,33 +1090,7 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                                                                                            __uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3])));
                         }
                     }
-                    __threadfence();
-                    __syncwarp();
-                    int* cnt = T.sk_cnt + T.sk_tile * 4 + ewarp;
-                    int old = 0;
-                    if (lane == 0) old = atomicAdd(cnt, 1);
-                    old = __shfl_sync(0xffffffffu, old, 0);
-                    if (old != T.nsplit - 1) return;
-                    __threadfence();
-                    if (orow) {
-                        for (int n = n0; n < Ncols && n < n0 + T.n_umma; n += 8) {
-                            const float4 a = __ldcg(reinterpret_cast<const float4*>(arow + n)), b = __ldcg(reinterpret_cast<const float4*>(arow + n + 4));
-                            const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-                            const Half8 bv = ld8(bias + n);
-                            Half8 o;
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                float z = 0.f;
-                                if (n + j < Ncols) z = act_forward(rh(rh(v[j]) + __half2float(bv.v[j])), act);
-                                o.v[j] = __float2half_rn(z);
-                            }
-                            st8(orow + n, o);
-                            __stcg(reinterpret_cast<float4*>(arow + n), make_float4(0.f, 0.f, 0.f, 0.f));
-                            __stcg(reinterpret_cast<float4*>(arow + n + 4), make_float4(0.f, 0.f, 0.f, 0.f));
-                        }
-                    }
-                    if (lane == 0) *cnt = 0;
-                    return;
+                    return;      // bias, activation and the fp16 store happen in k_splitk_finish, launched behind this kernel
                 }
             } else if (MODE == TC_DGRAD) {
                 __half* drow = nullptr;
@@ -1173,11 +1184,10 @@ k_gemm_tc(const TcTile* __restrict__ table, int ntiles, int nb, Inputs I) {
                 if (T.nk > 32) mbar_wait_relaxed(sTFull + acc * 8, (uint32_t)((jj / NACC) & 1));
                 else mbar_wait(sTFull + acc * 8, (uint32_t)((jj / NACC) & 1));
                 tc_fence_after();
+                rel_bar = sTEmpty + acc * 8;
                 if (MODE == TC_FWD && T.nsplit == 1) epilogue_fwd(T, s, *slot_ptr + (uint32_t)(acc * acc_cols));
                 else epilogue(T, s, *slot_ptr + (uint32_t)(acc * acc_cols), ewarp);
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(sTEmpty + acc * 8);
+                if (rel_bar) release_acc();
             }
         }
     }
