@@ -924,20 +924,36 @@ k_loss(const Prob* __restrict__ probs, int nprob, int nb, LossArgs a) {
     const int NL = a.ncls + a.G;
     const __half* z = p.out + (long long)b * p.out_bs;
     const int label = a.labels[b];
-    // ---- classification: log-sum-exp in fp32 from the fp16 logits (every lane computes it redundantly)
-    float zmax = -INFINITY; int arg = 0;
-    for (int j = 0; j < a.ncls; ++j) {
-        float v = __half2float(z[j]);
-        if (v > zmax) { zmax = v; arg = j; }
-    }
-    float se = 0.f;
-    for (int j = 0; j < a.ncls; ++j) se += expf(__half2float(z[j]) - zmax);
-    const float lse = zmax + logf(se);
-    // categorical_accuracy takes argmax over the model's fp16 softmax OUTPUT: probabilities that round to the same
-    // half tie and the first index wins (an all-NaN row keeps index 0, as tf.argmax does)
-    {
+    // ---- classification: log-sum-exp in fp32 from the fp16 logits
+    float lse; int arg = 0;
+    if (a.ncls <= 32) {
+        // lane j holds class j: one expf per lane, and the sums run over the classes in index order through shuffles, so
+        // every lane gets the bits the sequential loop below gives
+        const float zl = lane < a.ncls ? __half2float(z[lane]) : -INFINITY;
+        float zmax = -INFINITY;
+        for (int j = 0; j < a.ncls; ++j) {
+            const float v = __shfl_sync(0xffffffffu, zl, j);
+            if (v > zmax) zmax = v;
+        }
+        const float el = expf(zl - zmax);
+        float se = 0.f;
+        for (int j = 0; j < a.ncls; ++j) se += __shfl_sync(0xffffffffu, el, j);
+        lse = zmax + logf(se);
+        // categorical_accuracy takes argmax over the model's fp16 softmax OUTPUT: probabilities that round to the same
+        // half tie and the first index wins (an all-NaN row keeps index 0, as tf.argmax does)
+        const float pl = rh(el / se);
+        float pbest = __shfl_sync(0xffffffffu, pl, 0);
+        for (int j = 1; j < a.ncls; ++j) {
+            const float pj = __shfl_sync(0xffffffffu, pl, j);
+            if (pj > pbest) { pbest = pj; arg = j; }
+        }
+    } else {
+        float zmax = -INFINITY;
+        for (int j = 0; j < a.ncls; ++j) zmax = fmaxf(zmax, __half2float(z[j]));       // (NaN logits: se is NaN either way)
+        float se = 0.f;
+        for (int j = 0; j < a.ncls; ++j) se += expf(__half2float(z[j]) - zmax);
+        lse = zmax + logf(se);
         float pbest = rh(expf(__half2float(z[0]) - zmax) / se);
-        arg = 0;
         for (int j = 1; j < a.ncls; ++j) {
             const float pj = rh(expf(__half2float(z[j]) - zmax) / se);
             if (pj > pbest) { pbest = pj; arg = j; }
