@@ -43,6 +43,9 @@ def get_args(argv=None):
     ap.add_argument('--num-seranns', type=int, help='override num_seranns of the parameters file')
     ap.add_argument('--devices', help='comma-separated CUDA devices for a single-process run (default: LOCAL_RANK or 0); '
                                       'under torchrun every rank takes its LOCAL_RANK device and the population is sharded over the ranks')
+    ap.add_argument('--nan-offspring', choices=('keep', 'zero'), default='keep',
+                    help="offspring rows a NaN network produced (BatchNormalizationF16 overflow): 'keep' stores and decodes them as the "
+                         "reference does (its decode raises on them), 'zero' reads NaN loci as 0")
     return ap.parse_args(argv)
 
 
@@ -128,7 +131,7 @@ def main(argv=None):
         devices = [int(d) for d in args.devices.split(',')]
     with InProcessPool(*pool_args, devices=devices) as pool:
         exp = Experiment(experiment_id, data['encodings'], pool, genetic_encoder=encoder, population_source=source,
-                         shard_context=ctx, seed_base=seed, **info)
+                         shard_context=ctx, seed_base=seed, nan_offspring=args.nan_offspring, **info)
         exp.execute()
     ctx.barrier()
     if ctx.rank == 0:
