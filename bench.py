@@ -555,7 +555,7 @@ def eval_leg(D, args):
     params = dict(PARAMS)
     quiet = io.StringIO()
     with contextlib.redirect_stdout(quiet):
-        ev = B200SerannEvaluator(params, data, num_evaluations=K, replications_per_evaluation=R, ribosomal_ae=ae, device=D.local, shuffle_seed=1)
+        ev = B200SerannEvaluator(params, data, num_evaluations=K, replications_per_evaluation=R, ribosomal_ae=ae, device=D.local, shuffle_seed=1, nan_offspring='zero')
     np.random.seed(0)
     D.barrier()
     t0 = time.perf_counter()
@@ -573,7 +573,7 @@ def eval_leg(D, args):
         emit({'metric': 'serann_evaluation genotypes/s', 'value': n / secs, 'unit': 'genotypes/s', 'n_gpus': D.world, 'steps': n,
                           'warmup': 0, 'ms_per_step': 1000.0 * secs / n, 'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None,
                           'dtype': 'f16', 'data': 'synthetic',
-                          'config': {'workload': f'configs[4]: {n} genotypes x {K} re-initialisations x 380 steps at batch {BATCH}, R = {R} offspring each, decode + validity'},
+                          'config': {'workload': f'configs[4]: {n} genotypes x {K} re-initialisations x 380 steps at batch {BATCH}, R = {R} offspring each, decode + validity', 'nan_offspring': 'NaN loci of overflowing networks read as 0 (the reference decode raises on them)'},
                           'train_steps_per_s': steps / secs,
                           'rank0': {'validation_accuracy_mean': float(np.nanmean(accs)), 'validation_accuracy_std': float(np.nanstd(accs)),
                                     'mutation_rate_mean': float(np.mean(rates))}})

@@ -41,7 +41,12 @@ def empty_result():
 class B200SerannEvaluator:
     def __init__(self, experiment_params: dict, dataset: dict, num_evaluations: int = 50,
                  replications_per_evaluation: int = 100, ribosomal_ae=None, device: int = 0,
-                 shuffle_seed: Optional[int] = None):
+                 shuffle_seed: Optional[int] = None, nan_offspring: str = 'keep'):
+        if nan_offspring not in ('keep', 'zero'):
+            raise ValueError("nan_offspring must be 'keep' or 'zero'")
+        # 'keep': a network whose outputs are NaN (BatchNormalizationF16 overflow) yields NaN offspring, which the decode
+        # refuses exactly as the reference's does (logic.py:199-207 -> ribosomal_autoencoder.py:123); 'zero': NaN loci read as 0
+        self._nan_offspring = nan_offspring
         self._params = experiment_params
         self._k = int(num_evaluations)
         self._r = int(replications_per_evaluation)
@@ -111,6 +116,8 @@ class B200SerannEvaluator:
         probs, _, _ = eng.replicate(parents, r, image_index=np.tile(np.arange(r), k))
         self.last_probs = probs
         genotypes = np.round(np.clip(probs.reshape(k * r, -1).astype(np.float32), 0, 1))
+        if self._nan_offspring == 'zero':
+            genotypes = np.nan_to_num(genotypes, nan=0.0)
         fixed = probabilistic_proofreading(genotype, genotypes, self._params['error_correction_probability'])
         if self._ae is None:
             raise ValueError('a ribosomal autoencoder is needed to decode the offspring')

@@ -5,7 +5,7 @@ Training steps are counted by the k_adam launches (one per step); launches outsi
 the totals only if they repeat every step."""
 import csv, json, re, sys, collections
 
-CATEGORY = [('k_gemm_tc<0', 'gemm_fwd'), ('k_gemm_tc<1', 'gemm_dgrad'), ('k_gemm_tc<2', 'gemm_wgrad'), ('k_conv_fwd', 'gemm_fwd'), ('k_dense_k1', 'gemm_fwd'),
+CATEGORY = [('k_gemm_tc<0', 'gemm_fwd'), ('k_splitk', 'gemm_fwd'), ('k_gemm_tc<1', 'gemm_dgrad'), ('k_gemm_tc<2', 'gemm_wgrad'), ('k_conv_fwd', 'gemm_fwd'), ('k_dense_k1', 'gemm_fwd'),
             ('k_conv_dgrad', 'gemm_dgrad'), ('k_conv_wgrad', 'gemm_wgrad'), ('k_act_bwd', 'act_bwd'), ('k_bn', 'bn'),
             ('k_maxpool', 'pool'), ('k_copy', 'concat'), ('k_adam', 'adam'), ('k_loss', 'loss'), ('k_im2col', 'gather'),
             ('k_gather', 'gather')]
