@@ -1096,17 +1096,28 @@ static bool dense_tensor_maps(const Prob& p, int nb, int mode, int BN, CUtensorM
     return a_ok && g_ok && encode_matrix(&m[0], p.in, M, p.Cs, a_pitch, 64) && encode_matrix(&m[1], p.gout, M, p.Fs, g_pitch, 64);
 }
 
-// most k-splits a forward bucket asks for: about one tile per SM over the whole bucket.  (Every split costs an fp32 atomic
-// pass over its output tile, and in the overlapped step the other launches of the level hide a long tile: asking for four
-// tiles per SM measured 0.13 ms per step slower, no splits at all the same step but 0.6 ms more serialised time.)
-static int group_smax(const Group& g, int nb) {
-    if (g.tc != 1) return 1;
-    long long base = 0;
-    for (const Prob& p : g.h) base += tc_fwd_split_tiles(p, nb, TC_BN[g.cfgF]);
-    if (base == 0) return 1;
-    static const long long target = getenv("SRN_SPLIT_TARGET") ? atoll(getenv("SRN_SPLIT_TARGET")) : 1;      // A/B switch
-    const long long want = (target * 148 + base - 1) / base;
-    return (int)std::max(1LL, std::min(32LL, want));
+static int tc_grid(srn_engine* h, int total, int BN);
+// Target tile length (k-blocks) of the forward launch this bucket runs in = half the mean load of a CTA over all the
+// tensor-core buckets of its depth level with the same N tile (they are issued as one launch).  Long reductions are split
+// down to it (tc_fwd_split).  (Every split costs an fp32 atomic pass over its output tile: "four tiles per SM" for every
+// splittable problem measured 0.13 ms per step slower than one; no splits at all 0.6 ms more serialised time.  Unsplit,
+// single tiles of 140-230 k-blocks left their CTA with 2.4-3.9 times the mean load of the launch.)
+static int group_tstar(srn_engine* h, const Group& g, int nb) {
+    if (g.tc != 1) return 0;
+    static const int fixed = getenv("SRN_SPLIT_TSTAR") ? atoi(getenv("SRN_SPLIT_TSTAR")) : 0;      // A/B switch
+    if (fixed) return fixed;
+    const int BN = TC_BN[g.cfgF];
+    long long kblocks = 0;
+    for (const Group& o : h->groups) {
+        if (o.depth != g.depth || o.tc != 1 || o.cfgF != g.cfgF || o.lane != g.lane || !(o.mode & g.mode)) continue;
+        if (o.kind != SRN_KIND_DENSE && o.kind != SRN_KIND_CONV) continue;
+        for (const Prob& p : o.h) {
+            const long long mt = ((long long)nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM, tn = (p.F + BN - 1) / BN, nk = (tc_k_fwd(p) + TC_BK - 1) / TC_BK;
+            kblocks += mt * tn * nk;
+        }
+    }
+    const int G = tc_grid(h, 1 << 30, BN);
+    return (int)std::max(48LL, kblocks / G / 2);      // (fixed lengths 24 / 40 / 64 / 96 measured 8.22 / 8.17 / 8.14 / 8.13 ms per step: flat above 40)
 }
 
 static int pass_items(const Group& g, const Prob& p, int pass, int nb, int smax) {
@@ -1148,7 +1159,7 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
     if (it != g.cache.end()) { *out = &it->second; return SRN_OK; }
     Cached c;
     const int np = (int)g.h.size();
-    const int smax = group_smax(g, nb);
+    const int smax = group_tstar(h, g, nb);      // forward split-K: target tile length
     std::vector<int> host((size_t)P_COUNT * (np + 1));
     for (int pass = 0; pass < P_COUNT; ++pass) {
         int* pre = host.data() + (size_t)pass * (np + 1);
@@ -1427,6 +1438,23 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training, i
                         fin_blocks += c->fin_blocks;
                     }
                     std::stable_sort(all.begin(), all.end(), [](const TcTile& x, const TcTile& y) { return x.nk * x.nsub > y.nk * y.nsub; });
+                    if (getenv("SRN_DUMP_FWD")) {      // debug: what a merged forward launch holds
+                        const int BNd = TC_BN[b], G = tc_grid(h, (int)all.size(), BNd);
+                        long long sum = 0, mx = 0, nsplit_tiles = 0; std::vector<long long> load((size_t)std::max(G, 1), 0);
+                        for (size_t t = 0; t < all.size(); ++t) {
+                            const long long c = (long long)all[t].nk * all[t].nsub;
+                            sum += c; mx = std::max(mx, c); nsplit_tiles += all[t].nsplit > 1;
+                            const int j = (int)(t / G), r = (int)(t % G);
+                            load[(size_t)((j & 1) ? G - 1 - r : r)] += c;
+                        }
+                        long long lmax = 0; for (long long v : load) lmax = std::max(lmax, v);
+                        fprintf(stderr, "[fwd launch] depth %d BN %d buckets %zu tiles %zu grid %d kblocks %lld max_tile %lld max_cta %lld mean_cta %.1f split_tiles %lld\n",
+                                by_bn[b][0]->depth, BNd, by_bn[b].size(), all.size(), G, sum, mx, lmax, G ? (double)sum / G : 0.0, nsplit_tiles);
+                        for (Group* g : by_bn[b])
+                            for (const Prob& p : g->h)
+                                fprintf(stderr, "    bucket %d: H %d W %d C %d -> Ho %d Wo %d F %d k %dx%d s %d  K %d rows %d\n", (int)(g - h->groups.data()), p.H, p.W, p.C, p.Ho, p.Wo, p.F,
+                                        p.kh, p.kw, p.sh, p.kh * p.kw * p.Cs, nb * p.Ho * p.Wo);
+                    }
                     srn_engine::MergedFwd m;
                     m.total = (int)all.size();
                     m.first_group = (int)(by_bn[b][0] - h->groups.data());

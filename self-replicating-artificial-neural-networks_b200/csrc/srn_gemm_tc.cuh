@@ -79,7 +79,12 @@ __host__ __device__ inline int tc_fwd_sub(const Prob& p, int nb) {
     static const bool only_short = getenv("SRN_SUB_K64") != nullptr;       // A/B: sub-tiles only for one-k-block problems
     if (only_short && tc_k_fwd(p) > TC_BK) return 1;
 #endif
-    return mt >= 8 * TC_SUB ? TC_SUB : 1;
+    if (mt < 8 * TC_SUB) return 1;
+    // a descriptor should not carry much more than 64 k-blocks either: the tile table is dealt out by cost, and a
+    // descriptor of 8 sub-tiles x 29 k-blocks left its CTA with 2.4 times the mean load of the launch
+    const int nk = (tc_k_fwd(p) + TC_BK - 1) / TC_BK;
+    const int sub = (TC_SUB * 8) / (nk < 1 ? 1 : nk);
+    return sub < 1 ? 1 : (sub > TC_SUB ? TC_SUB : sub);
 }
 // Sub-tiles of such a problem whose reduction is at most 16 (32) elements are packed four (two) to a ring stage: row r of
 // the stage's 128-byte rows holds the k chunks of row r of every packed sub-tile side by side, the MMA of sub-tile q
@@ -95,14 +100,17 @@ __host__ __device__ inline int tc_fwd_pack(const Prob& p, int nb, bool scalar_a)
 // 25 000) are split along k so that the reduction runs on many SMs; the partial sums meet in an fp32 scratch tile.
 __host__ __device__ inline int tc_fwd_split_tiles(const Prob& p, int nb, int BN) {     // output tiles of a splittable problem, else 0
     const int mt = (nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM, tn = (p.F + BN - 1) / BN, nk = (tc_k_fwd(p) + TC_BK - 1) / TC_BK;
-    return (mt * tn > 48 || nk < 16) ? 0 : mt * tn;
+    return (mt >= 8 * TC_SUB || mt * tn > 256 || nk < 16) ? 0 : mt * tn;
 }
-// smax = the most splits the launch bucket wants (enough tiles to fill the machine about twice; every split costs an
-// fp32 atomic pass over the output tile, so a bucket that already has many tiles splits little)
-__host__ __device__ inline int tc_fwd_split(const Prob& p, int nb, int BN, int smax) {
-    if (tc_fwd_split_tiles(p, nb, BN) == 0) return 1;
+// tstar = the tile length (k-blocks) the launch this problem runs in aims at: about half the mean load of a CTA over all
+// the buckets merged into that launch (group_tstar in srn_engine.cu), so that no tile unbalances the launch; every split
+// costs an fp32 atomic pass over its output tile, so splits keep at least 8 k-blocks
+__host__ __device__ inline int tc_fwd_split(const Prob& p, int nb, int BN, int tstar) {
+    if (tstar <= 0 || tc_fwd_split_tiles(p, nb, BN) == 0) return 1;
     const int nk = (tc_k_fwd(p) + TC_BK - 1) / TC_BK;
-    const int s = nk / 8 < smax ? nk / 8 : smax;
+    int s = (nk + tstar - 1) / tstar;
+    if (s > nk / 8) s = nk / 8;
+    if (s > 32) s = 32;
     return s < 1 ? 1 : s;
 }
 __host__ __device__ inline int tc_tiles_fwd(const Prob& p, int nb, int BN, int smax) {
