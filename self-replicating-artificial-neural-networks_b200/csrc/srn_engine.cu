@@ -1194,15 +1194,11 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
                     const Prob& p = g.h[i];
                     const size_t rows = (size_t)nb * p.Ho * p.Wo;
                     const size_t acc_bytes = rows * p.Fs * sizeof(float);
-                    const size_t cnt_ints = 4 * ((rows + TC_BM - 1) / TC_BM) * ((p.F + BN - 1) / BN);
                     char* buf = nullptr;
-                    POOL_ALLOC(buf, char, acc_bytes + cnt_ints * sizeof(int));
-                    CK(cudaMemset(buf, 0, acc_bytes + cnt_ints * sizeof(int)));
-                    h->device_bytes += (long long)(acc_bytes + cnt_ints * sizeof(int));
-                    for (int t = pre[i]; t < pre[i + 1]; ++t) {
-                        tt[t].sk_acc = reinterpret_cast<float*>(buf);
-                        tt[t].sk_cnt = reinterpret_cast<int*>(buf + acc_bytes);
-                    }
+                    POOL_ALLOC(buf, char, acc_bytes);
+                    CK(cudaMemset(buf, 0, acc_bytes));
+                    h->device_bytes += (long long)acc_bytes;
+                    for (int t = pre[i]; t < pre[i + 1]; ++t) tt[t].sk_acc = reinterpret_cast<float*>(buf);
                     SplitFin f;
                     f.acc = reinterpret_cast<float*>(buf); f.out = p.out; f.bias = p.bias; f.rows = (int)rows; f.Fs = p.Fs; f.F = p.F; f.act = p.act;
                     f.HoWo = p.Ho * p.Wo; f.out_bs = p.out_bs; f.blk0 = c.fin_blocks;

@@ -343,11 +343,11 @@ struct __align__(16) TcTile {
     int klast;         // K = 16 steps of the last k-block (1..4): the tail of the reduction is neither loaded nor multiplied
     int nsub;          // 128-row sub-tiles m0, m0 + 128, .. covered by this descriptor (forward only, else 1)
     // split-K (forward, few output tiles and a long reduction): this tile covers k-blocks kb0 .. kb0 + nk - 1 of nsplit
-    // splits; partial sums meet in the fp32 scratch sk_acc [Mrows][Fs] (k_splitk_finish turns them into the output); sk_cnt is unused
+    // splits; partial sums meet in the fp32 scratch sk_acc [Mrows][Fs] (k_splitk_finish turns them into the output)
     int kb0, nsplit, sk_tile;
     int pack;          // forward sub-tiles per ring stage (tc_fwd_pack), else 1
     float* sk_acc;
-    int* sk_cnt;
+    int* reserved;     // (was the arrival counter of the in-kernel split-K finish)
     int ph, pw, Hc, Wc, khp, kwp;     // dgrad: residue class of this tile (tc_dgrad_class)
     // Dense problems whose operands are plain row-major matrices are loaded by TMA (2-D tiled mode, swizzle-128B):
     // tm -> two 128-byte tensor maps (A operand, B operand) of this pass, nullptr = cp.async gather path
@@ -366,7 +366,7 @@ inline void tc_describe_tile(TcTile& t, int tile, int nb, int BN, int MODE, bool
     const int Kf = SCALAR_A ? KK : KK * p.Cs;
     t.tm = nullptr;
     t.pack = 1;
-    t.r0 = 0; t.r1 = 0; t.nsub = 1; t.kb0 = 0; t.nsplit = 1; t.sk_tile = 0; t.sk_acc = nullptr; t.sk_cnt = nullptr;
+    t.r0 = 0; t.r1 = 0; t.nsub = 1; t.kb0 = 0; t.nsplit = 1; t.sk_tile = 0; t.sk_acc = nullptr; t.reserved = nullptr;
     int Kend = 0;                                           // end of this tile's part of the reduction (elements)
     if (MODE == TC_FWD) {
         t.Mrows = nb * HoWo; t.Ncols = p.F;
