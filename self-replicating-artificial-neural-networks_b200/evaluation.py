@@ -83,25 +83,43 @@ class B200SerannEvaluator:
         ``initial_weights`` (one Keras-layout weight list per copy) and ``perms`` (row order per epoch) replace the
         random initialisation and Keras' unseeded shuffle when given - the parity tests feed the same values to the
         CPU oracle."""
-        genotype = np.array(genotype)
-        if source_code is None:
-            if self._ae is None:
-                raise ValueError('a ribosomal autoencoder is needed to decode the genotype')
-            source_code = self._ae.decode_to_string(genotype[None])[0]
-        if loss_balance is None:
-            m = _LOSS_BALANCE_RE.search(source_code)
-            if m is None:
-                print('Invalid/overweight SeRANN received. Returning empty result.')
-                return empty_result()
-            loss_balance = float(m.group(1))
-        try:
-            ir = copy.copy(compile_cached(source_code, **self._kwargs()))     # the cached IR is shared: do not edit it
-        except InvalidSerann:
-            # the reference lets the Keras build exception escape here; an invalid source has no offspring either way
-            return empty_result()
-        ir.loss_balance = float(loss_balance)
+        return self.evaluate_many([genotype], [source_code], [loss_balance], initial_weights=initial_weights, perms=perms)[0]
+
+    def evaluate_many(self, genotypes, source_codes=None, loss_balances=None, initial_weights=None, perms=None) -> list:
+        """Several genotypes in ONE engine shard: the K copies of every genotype are built, trained and read out together
+        (a shard of 3 x 32 copies fills the GPU like a population of 100; one genotype's 32 copies alone do not).  Each
+        genotype's result is what ``evaluate`` returns for it; copies of different genotypes never interact."""
+        n = len(genotypes)
+        source_codes = list(source_codes) if source_codes is not None else [None] * n
+        loss_balances = list(loss_balances) if loss_balances is not None else [None] * n
+        results: list = [None] * n
+        items = []                                   # (position, genotype, ir, loss_balance) of the valid ones
+        for pos in range(n):
+            genotype = np.array(genotypes[pos])
+            source_code, loss_balance = source_codes[pos], loss_balances[pos]
+            if source_code is None:
+                if self._ae is None:
+                    raise ValueError('a ribosomal autoencoder is needed to decode the genotype')
+                source_code = self._ae.decode_to_string(genotype[None])[0]
+            if loss_balance is None:
+                m = _LOSS_BALANCE_RE.search(source_code)
+                if m is None:
+                    print('Invalid/overweight SeRANN received. Returning empty result.')
+                    results[pos] = empty_result()
+                    continue
+                loss_balance = float(m.group(1))
+            try:
+                ir = copy.copy(compile_cached(source_code, **self._kwargs()))     # the cached IR is shared: do not edit it
+            except InvalidSerann:
+                # the reference lets the Keras build exception escape here; an invalid source has no offspring either way
+                results[pos] = empty_result()
+                continue
+            ir.loss_balance = float(loss_balance)
+            items.append((pos, genotype, ir, float(loss_balance)))
+        if not items:
+            return results
         k, r, eng = self._k, self._r, self._engine
-        eng.build([ir] * k, seed=int(self._rng.integers(0, 2 ** 63)))
+        eng.build([ir for _, _, ir, _ in items for _ in range(k)], seed=int(self._rng.integers(0, 2 ** 63)))
         n_fit = int(self._n_train * (1.0 - VALIDATION_SPLIT))
         n_val = self._n_train - n_fit
         if initial_weights is not None:
@@ -110,34 +128,37 @@ class B200SerannEvaluator:
         res = eng.fit(int(self._params['training_epochs']), self._batch, n_val, perms=perms,
                       shuffle_seed=int(self._rng.integers(0, 2 ** 63)))
         val_sizes = _chunks(n_val, self._batch)
-        accuracies = [f16_accuracy(res['val_correct'][-1, :, i], val_sizes) for i in range(k)]
         # predict([x_test[:R], genotype repeated R times]) for every copy (logic.py:188-191)
-        parents = np.repeat(genotype_bits(genotype)[None], k, axis=0)
-        probs, _, _ = eng.replicate(parents, r, image_index=np.tile(np.arange(r), k))
-        self.last_probs = probs
-        genotypes = np.round(np.clip(probs.reshape(k * r, -1).astype(np.float32), 0, 1))
-        if self._nan_offspring == 'zero':
-            genotypes = np.nan_to_num(genotypes, nan=0.0)
-        fixed = probabilistic_proofreading(genotype, genotypes, self._params['error_correction_probability'])
+        parents = np.concatenate([np.repeat(genotype_bits(g)[None], k, axis=0) for _, g, _, _ in items], axis=0)
+        probs, _, _ = eng.replicate(parents, r, image_index=np.tile(np.arange(r), k * len(items)))
+        probs = probs.reshape(len(items), k * r, -1)
+        self.last_probs = probs[0].reshape(k, r, -1) if len(items) == 1 else probs
         if self._ae is None:
             raise ValueError('a ribosomal autoencoder is needed to decode the offspring')
-        sources = self._ae.decode_to_string(fixed)
-        survival, mutation = [], []
-        for i in range(k):
-            micro: Dict[int, int] = {}
-            for j in range(r):
-                s = sources[i * r + j]
-                # the reference's `cache.get(s) or ...` re-validates every cached invalid source (logic.py:216);
-                # a proper lookup gives the same counts without the rebuilds
-                valid = self._validity_cache.get(s)
-                if valid is None:
-                    valid = self._validity_cache[s] = int(self.is_valid_serann(s, loss_balance))
-                micro[valid] = micro.get(valid, 0) + 1
-            survival.append(micro)
-            # the reference slices [i : i + R], not [i*R : (i+1)*R] (logic.py:223) - kept for parity
-            mutations = np.sum(fixed[i: i + r] != genotype, axis=1)
-            mutation.append(dict(Counter(mutations / len(genotype))))
-        return {'classification_accuracy': accuracies, 'mutation_rate': mutation, 'offspring_survival': survival}
+        for gi, (pos, genotype, _, loss_balance) in enumerate(items):
+            accuracies = [f16_accuracy(res['val_correct'][-1, :, gi * k + i], val_sizes) for i in range(k)]
+            offspring = np.round(np.clip(probs[gi].astype(np.float32), 0, 1))
+            if self._nan_offspring == 'zero':
+                offspring = np.nan_to_num(offspring, nan=0.0)
+            fixed = probabilistic_proofreading(genotype, offspring, self._params['error_correction_probability'])
+            sources = self._ae.decode_to_string(fixed)
+            survival, mutation = [], []
+            for i in range(k):
+                micro: Dict[int, int] = {}
+                for j in range(r):
+                    s = sources[i * r + j]
+                    # the reference's `cache.get(s) or ...` re-validates every cached invalid source (logic.py:216);
+                    # a proper lookup gives the same counts without the rebuilds
+                    valid = self._validity_cache.get(s)
+                    if valid is None:
+                        valid = self._validity_cache[s] = int(self.is_valid_serann(s, loss_balance))
+                    micro[valid] = micro.get(valid, 0) + 1
+                survival.append(micro)
+                # the reference slices [i : i + R], not [i*R : (i+1)*R] (logic.py:223) - kept for parity
+                mutations = np.sum(fixed[i: i + r] != genotype, axis=1)
+                mutation.append(dict(Counter(mutations / len(genotype))))
+            results[pos] = {'classification_accuracy': accuracies, 'mutation_rate': mutation, 'offspring_survival': survival}
+        return results
 
 
 class B200EvaluationWorker(B200SerannEvaluator):

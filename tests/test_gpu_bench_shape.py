@@ -293,3 +293,35 @@ print("GUARDS", rc, rc2)
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert 'GUARDS 0 0' in r.stdout, r.stdout[-500:]
+
+
+def test_evaluate_many_equals_separate_evaluations():
+    """Two genotypes in one engine shard (evaluate_many) against the same two evaluated one after the other with the same
+    initial weights and row order: the copies of different genotypes never interact, so accuracies, mutation-rate
+    counters and survival counts are identical, and an invalid source in the batch gets the empty result."""
+    from serann_b200.codec import RibosomalAutoencoder
+    from serann_b200.evaluation import B200SerannEvaluator, empty_result
+    from serann_b200.synthetic import synthetic_decoder_weights
+    K, R = 4, 8
+    params = {'genotype_size': 100, 'classification_image_dimensions': [28, 28], 'num_classification_classes': 10,
+              'training_epochs': 1, 'training_batch_size': 40, 'error_correction_probability': 0}
+    data = U.small_dataset(n_train=200, n_test=64, seed=77)
+    irs = [frontend.compile_source(s) for s in EVAL_NETS]
+    rng = np.random.default_rng(9)
+    weights = [[O.init_weights(ir, rng) for _ in range(K)] for ir in irs]
+    perms = np.stack([np.random.default_rng(60).permutation(int(200 * 0.95))])
+    genotypes = [data['g_test'][1], data['g_test'][2]]
+    ae = RibosomalAutoencoder(350, synthetic_decoder_weights())
+    ev = B200SerannEvaluator(params, data, num_evaluations=K, replications_per_evaluation=R, ribosomal_ae=ae, shuffle_seed=1)
+    try:
+        single = [ev.evaluate(genotypes[i], source_code=EVAL_NETS[i], initial_weights=weights[i], perms=perms) for i in range(2)]
+        many = ev.evaluate_many([genotypes[0], genotypes[0], genotypes[1]], [EVAL_NETS[0], 'con = oops(', EVAL_NETS[1]],
+                                initial_weights=weights[0] + weights[1], perms=perms)
+        assert many[1] == empty_result()
+        for got, want in ((many[0], single[0]), (many[2], single[1])):
+            assert got['classification_accuracy'] == want['classification_accuracy']
+            assert got['mutation_rate'] == want['mutation_rate']
+            assert got['offspring_survival'] == want['offspring_survival']
+    finally:
+        ev.close()
+        ae.close()
