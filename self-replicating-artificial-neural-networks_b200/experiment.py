@@ -222,7 +222,8 @@ class Experiment:
         times: Dict[str, list] = {}
         infos, offspring_by_id = [], {}
         workers = self._workers_pool.get_workers_count()
-        batch_index = reference_batches(len(generation), workers, MAX_SERANN_PER_GPU)
+        per_job = getattr(self._workers_pool, 'max_seranns_per_job', MAX_SERANN_PER_GPU) or 10 ** 9     # None: the worker sizes its own waves
+        batch_index = reference_batches(len(generation), workers, per_job)
         batch_by_id = pd.Series(batch_index, index=generation.index).astype(int)
         total = batch_by_id.nunique()
         seeded = getattr(self._workers_pool, 'accepts_seeds', False)

@@ -82,10 +82,11 @@ class B200PopulationWorker:
                            'classification_test_accuracy', 'replication_mse']
 
     def __init__(self, experiment_params: dict, dataset: Optional[dict] = None, device: int = 0,
-                 memory_budget_bytes: float = 120e9, shuffle_seed: Optional[int] = None):
+                 memory_budget_bytes: float = 120e9, shuffle_seed: Optional[int] = None, max_wave: int = 512):
         self._parameters = experiment_params
         self._device = device
         self._budget = memory_budget_bytes
+        self._max_wave = int(max_wave)          # individuals that step together at most (launch tables grow with it)
         self._rng = np.random.default_rng(shuffle_seed if shuffle_seed is not None else int.from_bytes(os.urandom(8), 'little'))
         if dataset is None:
             raise ValueError('dataset is required: the MNIST download and the figshare encodings are not '
@@ -124,11 +125,11 @@ class B200PopulationWorker:
         return irs, info
 
     def _waves(self, ids: List[str], irs: Dict[str, SerannIR]) -> List[List[str]]:
-        """Split the shard so that each wave's activation arena fits the memory budget."""
+        """Split the shard so that each wave's activation arena fits the memory budget (and holds at most max_wave)."""
         waves, cur, used = [], [], 0
         for i in ids:
             need = _engine.activation_bytes_estimate(irs[i], self._batch) + 16 * irs[i].parameters_count
-            if cur and used + need > self._budget:
+            if cur and (used + need > self._budget or len(cur) >= self._max_wave):
                 waves.append(cur)
                 cur, used = [], 0
             cur.append(i)
@@ -231,6 +232,9 @@ class InProcessPool:
     """
 
     accepts_seeds = True         # jobs may carry kwargs (fit_seed, individual_seeds): the reference's farm passes args only
+    # Jobs need not be cut to the reference's 112 SeRANNs per GPU (evolutionary_experiment/config.py:8, sized for a 16 GB
+    # V100): a worker splits its job into waves that fit its own memory budget, and larger waves fill a B200 better.
+    max_seranns_per_job = None
 
     def __init__(self, worker_cls, init_args: Optional[dict] = None, *_pool_args, devices: Optional[Sequence[int]] = None,
                  **_pool_kwargs):
