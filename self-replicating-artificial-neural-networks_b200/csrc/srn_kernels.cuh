@@ -918,9 +918,12 @@ k_loss(const Prob* __restrict__ probs, int nprob, int nb, LossArgs a) {
     const int pi = blockIdx.x / ctas_per_prob;
     if (pi >= nprob) return;
     const Prob p = probs[pi];
-    const int b = (blockIdx.x - pi * ctas_per_prob) * warps_per_cta + (threadIdx.x >> 5);
+    const int b_raw = (blockIdx.x - pi * ctas_per_prob) * warps_per_cta + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (b >= nb) return;
+    // a warp past the end of the batch recomputes the last sample (its gradient stores repeat the same values) and is left
+    // out of the metrics: every warp reaches the block-wide combination of the metric sums below
+    const bool counted = b_raw < nb;
+    const int b = counted ? b_raw : nb - 1;
     const int NL = a.ncls + a.G;
     const __half* z = p.out + (long long)b * p.out_bs;
     const int label = a.labels[b];
@@ -986,13 +989,29 @@ k_loss(const Prob* __restrict__ probs, int nprob, int nb, LossArgs a) {
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sq_sum += __shfl_xor_sync(0xffffffffu, sq_sum, o);
+    // The 8 samples of a block belong to one individual: their metric sums are combined in shared memory and added with
+    // one set of atomics per block (750 same-address atomics per individual and metric serialised at the L2 otherwise).
+    __shared__ float s_ce[8], s_mse[8];
+    __shared__ int s_ok[8], s_slot[8];
+    const int w = threadIdx.x >> 5;
     if (lane == 0) {
-        const float mse = rh(sq_sum / (float)a.G);
-        const int slot = a.slot_base + (a.row0 + b) / a.chunk;
-        const long long mi = (long long)slot * a.n + p.indiv;
-        if (arg == label) atomicAdd(&a.met_correct[mi], 1);
-        atomicAdd(&a.met_ce[mi], ce);
-        atomicAdd(&a.met_mse[mi], mse);
+        s_mse[w] = counted ? rh(sq_sum / (float)a.G) : 0.f;
+        s_ce[w] = counted ? ce : 0.f;
+        s_ok[w] = counted && arg == label ? 1 : 0;
+        s_slot[w] = counted ? a.slot_base + (a.row0 + b) / a.chunk : -1;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int k = 0;
+        while (k < warps_per_cta && s_slot[k] >= 0) {          // runs of samples in the same metric slot (a chunk boundary can cut the block)
+            const int slot = s_slot[k];
+            float ce_sum = 0.f, mse_sum = 0.f; int ok = 0;
+            for (; k < warps_per_cta && s_slot[k] == slot; ++k) { ce_sum += s_ce[k]; mse_sum += s_mse[k]; ok += s_ok[k]; }
+            const long long mi = (long long)slot * a.n + p.indiv;
+            if (ok) atomicAdd(&a.met_correct[mi], ok);
+            atomicAdd(&a.met_ce[mi], ce_sum);
+            atomicAdd(&a.met_mse[mi], mse_sum);
+        }
     }
     (void)NL;
 }
