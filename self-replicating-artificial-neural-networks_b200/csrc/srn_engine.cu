@@ -24,6 +24,7 @@
 #include "../../include/serann_b200.h"
 #include "srn_gemm_simt.cuh"
 #include "srn_gemm_tc.cuh"
+#include "srn_conv_slab.cuh"
 #include "srn_kernels.cuh"
 #include "srn_host.h"
 #include "srn_tma.h"
@@ -181,6 +182,9 @@ struct Cached {
     std::vector<SplitFin> host_fin;   // split-K forward problems of this bucket (k_splitk_finish), blk0 relative to the bucket
     SplitFin* fin = nullptr;
     int fin_blocks = 0;
+    SlabProb* slab = nullptr;         // problems of the bucket that run forward on the slab kernel (srn_conv_slab.cuh)
+    int* slab_prefix = nullptr;       // their tile prefix (device, slab_np + 1 entries)
+    int slab_np = 0, slab_total = 0, slab_stride = 0, slab_wbytes = 0;
 };
 
 struct Group {
@@ -366,6 +370,8 @@ extern "C" int srn_create(const srn_config* cfg, srn_engine** out) {
         TC_ATTR4(TC_FWD, false); TC_ATTR4(TC_FWD, true); TC_ATTR4(TC_DGRAD, false); TC_ATTR4(TC_WGRAD, false); TC_ATTR4(TC_WGRAD, true);
 #undef TC_ATTR4
 #undef TC_ATTR
+        CK(cudaFuncSetAttribute(k_conv_slab<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CK(cudaFuncSetAttribute(k_conv_slab<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
     }
     srn_engine* h = new srn_engine();
     h->cfg = *cfg;
@@ -1097,6 +1103,18 @@ static bool dense_tensor_maps(const Prob& p, int nb, int mode, int BN, CUtensorM
 }
 
 static int tc_grid(srn_engine* h, int total, int BN);
+// Forward by the slab convolution kernel (srn_conv_slab.cuh): stride-1 windows over a dense tensor whose pixels are one
+// swizzle row, weights that fit the resident region.  Such problems get no tiles in the bucket's GEMM tile table.
+// OFF by default (SRN_SLAB=1 turns it on; parity-tested in that mode): on the benchmark population the eligible layers
+// cost 0.19 ms of the 3.0 ms forward GEMM time on the gather path and 0.36 ms here - with N <= 64 an MMA is 16-32 tensor
+// cycles, one issuing warp per CTA does not keep up, and the resident weights (128-byte rows) leave room for one CTA per
+// SM only.  The layers that dominate (7 x 7 x 64 windows, 8-channel inputs, strides) are not eligible yet.
+static bool slab_ok(const Group& g, const Prob& p) {
+    static const bool on = getenv("SRN_SLAB") != nullptr;
+    return on && g.tc == 1 && g.kind == SRN_KIND_CONV && p.kh * p.kw > 1 && p.sh == 1 && p.sw == 1 && p.in_sel == 0 && p.C == p.Cs &&
+           (p.C == 16 || p.C == 32 || p.C == 64) && p.F <= 64 && p.in_bs == p.H * p.W * p.Cs && p.kh * p.kw * p.C <= CS_KMAX &&
+           p.Ho == p.H - p.kh + 1 && p.Wo == p.W - p.kw + 1 && (p.kh - 1) * p.W + p.kw - 1 <= 384 && encode_tiled_fn() != nullptr;
+}
 // Target tile length (k-blocks) of the forward launch this bucket runs in = half the mean load of a CTA over all the
 // tensor-core buckets of its depth level with the same N tile (they are issued as one launch).  Long reductions are split
 // down to it (tc_fwd_split).  (Every split costs an fp32 atomic pass over its output tile: "four tiles per SM" for every
@@ -1112,6 +1130,7 @@ static int group_tstar(srn_engine* h, const Group& g, int nb) {
         if (o.depth != g.depth || o.tc != 1 || o.cfgF != g.cfgF || o.lane != g.lane || !(o.mode & g.mode)) continue;
         if (o.kind != SRN_KIND_DENSE && o.kind != SRN_KIND_CONV) continue;
         for (const Prob& p : o.h) {
+            if (slab_ok(o, p)) continue;
             const long long mt = ((long long)nb * p.Ho * p.Wo + TC_BM - 1) / TC_BM, tn = (p.F + BN - 1) / BN, nk = (tc_k_fwd(p) + TC_BK - 1) / TC_BK;
             kblocks += mt * tn * nk;
         }
@@ -1128,6 +1147,7 @@ static int pass_items(const Group& g, const Prob& p, int pass, int nb, int smax)
             if (pass == P_COL) return col_chunks(out_rows, p.Fs);
             if (g.tc == 3) return pass == P_FWD ? ew_blocks(out_rows, p.Fs) : 0;      // wgrad rides on the bias-gradient pass
             if (g.tc) {
+                if (pass == P_FWD && slab_ok(g, p)) return 0;      // forward by the slab kernel (its own table in plan_for)
                 if (pass == P_FWD) return tc_tiles_fwd(p, nb, TC_BN[g.cfgF], smax);
                 if (pass == P_DGRAD) return p.din ? tc_tiles_dgrad(p, nb, TC_BN[g.cfgC]) : 0;
                 if (pass == P_WGRAD) return tc_tiles_wgrad(p, nb, TC_BN[g.cfgF]);
@@ -1175,6 +1195,37 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
     CK(cudaStreamSynchronize(h->stream));      // host vector goes out of scope
     for (int pass = 0; pass < P_COUNT; ++pass) c.prefix[pass] = dev + (size_t)pass * (np + 1);
     if (g.tc == 1 || g.tc == 2) {
+        if (g.tc == 1 && g.kind == SRN_KIND_CONV) {
+            std::vector<SlabProb> sp;
+            std::vector<int> spre(1, 0);
+            const int MB = h->cfg.max_batch;
+            for (int i = 0; i < np; ++i) {
+                const Prob& p = g.h[i];
+                if (!slab_ok(g, p)) continue;
+                SlabProb q;
+                memset(&q, 0, sizeof(q));
+                q.bias = p.bias; q.out = p.out; q.H = p.H; q.W = p.W; q.Wo = p.Wo; q.P = (p.Ho - 1) * p.W + p.Wo; q.tps = (q.P + TC_BM - 1) / TC_BM;
+                q.C = p.C; q.F = p.F; q.Fs = p.Fs; q.K = p.kh * p.kw * p.C; q.kw = p.kw; q.out_bs = p.out_bs; q.act = p.act;
+                q.rowb = p.C * 2; q.layout = p.C == 16 ? 6 : (p.C == 32 ? 4 : 2); q.sbo = 8 * q.rowb;
+                const int rows = TC_BM + (p.kh - 1) * p.W + p.kw - 1;
+                q.nbox = rows <= 256 ? 1 : 2;
+                q.box_rows = (int)align_up((rows + q.nbox - 1) / q.nbox, 8);
+                q.slab_bytes = q.nbox * q.box_rows * q.rowb;
+                c.slab_stride = std::max(c.slab_stride, (int)align_up(q.slab_bytes, 1024));
+                c.slab_wbytes = std::max(c.slab_wbytes, ((q.K + 63) / 64) * CS_WCHUNK);
+                if (!encode_slab(&q.amap, p.in, (long long)MB * p.H * p.W, p.C, q.box_rows) || !encode_matrix(&q.wmap, p.w, q.K, p.ldw, p.ldw, 64))
+                    return fail(SRN_ERR_CUDA, "slab convolution: tensor map encoding failed");
+                sp.push_back(q);
+                spre.push_back(spre.back() + nb * q.tps);
+            }
+            if (!sp.empty()) {
+                c.slab_np = (int)sp.size(); c.slab_total = spre.back();
+                POOL_ALLOC(c.slab, SlabProb, sp.size() * sizeof(SlabProb));
+                CK(cudaMemcpy(c.slab, sp.data(), sp.size() * sizeof(SlabProb), cudaMemcpyHostToDevice));
+                POOL_ALLOC(c.slab_prefix, int, spre.size() * sizeof(int));
+                CK(cudaMemcpy(c.slab_prefix, spre.data(), spre.size() * sizeof(int), cudaMemcpyHostToDevice));
+            }
+        }
         for (int pass : {P_FWD, P_DGRAD, P_WGRAD}) {
             if (!c.total[pass]) continue;
             const int* pre = host.data() + (size_t)pass * (np + 1);
@@ -1316,6 +1367,18 @@ static int run_tasks(srn_engine* h, std::vector<std::function<int()>>& tasks) {
     return rc;
 }
 
+// the bucket's slab-eligible problems (forward only)
+static void launch_slab(srn_engine* h, Group& g, Cached* c) {
+    if (!c->slab_total) return;
+    const int smem = cs_smem_bytes(c->slab_stride, c->slab_wbytes);
+    const int per_sm = std::max(1, std::min(2, (228 * 1024) / (smem + 1024)));      // two CTAs per SM when slabs and weights are small
+    const int grid = std::min(c->slab_total, h->num_sms * per_sm);
+    if (TC_BN[g.cfgF] == 32)
+        LAUNCH_SMEM(SRN_CAT_GEMM_FWD, (k_conv_slab<32>), grid, CS_THREADS, smem, c->slab, c->slab_prefix, c->slab_np, c->slab_total, c->slab_stride, c->slab_wbytes);
+    else
+        LAUNCH_SMEM(SRN_CAT_GEMM_FWD, (k_conv_slab<64>), grid, CS_THREADS, smem, c->slab, c->slab_prefix, c->slab_np, c->slab_total, c->slab_stride, c->slab_wbytes);
+}
+
 static int fwd_group(srn_engine* h, Group& g, int nb, const Inputs& I, bool training) {
     Cached* c;
     h->cur_group = (int)(&g - h->groups.data());
@@ -1332,6 +1395,7 @@ static int fwd_group(srn_engine* h, Group& g, int nb, const Inputs& I, bool trai
             if (g.tc) {
                 const int BN = TC_BN[g.cfgF];
                 if (g.tc == 1) {
+                    launch_slab(h, g, c);
                     LAUNCH_TC(SRN_CAT_GEMM_FWD, TC_FWD, false, P_FWD, BN);
                     if (c->fin_blocks) LAUNCH(SRN_CAT_GEMM_FWD, k_splitk_finish, c->fin_blocks, 256, c->fin, (int)c->host_fin.size());
                 }
@@ -1464,6 +1528,10 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training, i
                         m.nfin = (int)fins.size(); m.fin_blocks = fin_blocks;
                     }
                     it = h->merged_fwd.emplace(key, m).first;
+                }
+                for (Group* g : by_bn[b]) {          // their slab-eligible problems: one launch per bucket, beside the merged GEMM launch
+                    Cached* c; rc = plan_for(h, *g, nb, &c); if (rc) return rc;
+                    if (c->slab_total) tasks.push_back([=]() { h->cur_group = (int)(g - h->groups.data()); launch_slab(h, *g, c); return (int)SRN_OK; });
                 }
                 const srn_engine::MergedFwd m = it->second;
                 if (!m.total) continue;

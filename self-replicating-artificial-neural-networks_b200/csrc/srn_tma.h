@@ -37,4 +37,18 @@ inline bool encode_matrix(CUtensorMap* m, const void* base, long long rows, long
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// input slab of the stride-1 convolution kernel (srn_conv_slab.cuh): rows of C channels (C * 2 = 32, 64 or 128 bytes, one
+// swizzle row per pixel) of a dense [rows][C] fp16 tensor, box = C x box_rows, swizzle span = the row
+inline bool encode_slab(CUtensorMap* m, const void* base, long long rows, int C, int box_rows) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn || !base || rows <= 0 || (C != 16 && C != 32 && C != 64) || box_rows <= 0 || box_rows > 256 || ((uintptr_t)base & 15) != 0) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t)C, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)C * 2};
+    const cuuint32_t box[2] = {(cuuint32_t)C, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1u, 1u};
+    const CUtensorMapSwizzle sw = C == 16 ? CU_TENSOR_MAP_SWIZZLE_32B : (C == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
+    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 }  // namespace srn

@@ -325,3 +325,17 @@ def test_evaluate_many_equals_separate_evaluations():
     finally:
         ev.close()
         ae.close()
+
+
+def test_slab_convolution_kernel_passes_the_parity_tests():
+    """The opt-in forward path for stride-1 convolutions (csrc/srn_conv_slab.cuh: one slab of input rows per tile, window
+    taps as shifted shared-memory views) under the same layerwise / step / fit parity tests as the default path.  The switch
+    is read once per process, hence the subprocess."""
+    import os
+    import subprocess
+    import sys
+    env = dict(os.environ, SRN_SLAB='1')
+    r = subprocess.run([sys.executable, '-m', 'pytest', 'tests/test_gpu_parity.py', '-x', '-q', '-p', 'no:cacheprovider'],
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))), env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert 'passed' in r.stdout

@@ -1,5 +1,5 @@
 # device-timed step under a few environment switches (A/B experiments)
-for e in "SRN_SPLIT_TSTAR=24" "SRN_SPLIT_TSTAR=40" "SRN_SPLIT_TSTAR=64" "SRN_SPLIT_TSTAR=96"; do
+for e in "SRN_NO_SLAB=1" "SRN_X=1"; do
   env $e python bench.py --no-e2e --no-cpu --no-pop1000 --steps 10 --warmup 3 2>/dev/null | python -c "
 import sys,json
 for l in sys.stdin:
