@@ -1,5 +1,5 @@
 # device-timed step under a few environment switches (A/B experiments)
-for e in "SRN_NO_SLAB=1" "SRN_X=1"; do
+for e in "SRN_X=0" "SRN_SLAB=1" "SRN_SPLIT_TSTAR=100000" "SRN_TMA_MASK=0"; do
   env $e python bench.py --no-e2e --no-cpu --no-pop1000 --steps 10 --warmup 3 2>/dev/null | python -c "
 import sys,json
 for l in sys.stdin:
