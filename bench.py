@@ -446,7 +446,9 @@ def main():
         n_job = args.pop * D.world
         # (every GPU's share is the N = 1 population of that generation: the same mix repeated once per GPU, as `value` does -
         # a fresh sample of pop x N would change the work per individual with N, the seed-0 hundred being lighter than the mean)
-        pools = [[s for s, _ in population(args.pop, args.mix, seed=g)] * D.world for g in range(G)]
+        # and every generation is re-seeded with the benchmark population itself (generator seed 0, the workload `value` is
+        # measured on): fresh samples per generation would time other, on average 1.4x heavier, mixes under the same name
+        pools = [[s for s, _ in population(args.pop, args.mix, seed=0)] * D.world for g in range(G)]
         r = run_generations(D, dict(PARAMS, num_seranns=n_job), pools, data, decoder_weights, tmpdir)
         trained = D.reduce(sum(r['trained']), 'sum')
         steps_gen = r['steps'][0]
@@ -460,7 +462,7 @@ def main():
                'what': 'Experiment.execute() over InProcessPool(B200PopulationWorker): H2D of the data set (once), then per generation '
                        'source compilation, build, 5 x 76 steps, validation, test, replication + readout (R = 10), D2H of metrics and '
                        'offspring, all-gather (N > 1), fertility, multinomial, statistics, SQLite, selection, decode of the offspring; '
-                       'a new generator-sampled population of pop individuals every generation, repeated once per GPU (pop x N individuals), LPT-sharded over the N ranks (a random-init autoencoder decodes no valid programs)'}
+                       'every generation starts from the benchmark population (generator seed 0, pop individuals, repeated once per GPU = pop x N individuals), LPT-sharded over the N ranks (a random-init autoencoder decodes no valid programs)'}
 
     # ---- BASELINE's second figure: one population of 1000 over the N GPUs ---------------------------
     p1000 = None
