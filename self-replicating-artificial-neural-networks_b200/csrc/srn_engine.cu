@@ -1174,6 +1174,17 @@ static int pass_items(const Group& g, const Prob& p, int pass, int nb, int smax)
     return 0;
 }
 
+// heaviest tiles first, ties in table order: sorts 4-byte indices and moves every 320-byte descriptor once (sorting the
+// descriptors themselves was most of the host time of a launch plan)
+static void sort_tiles_by_cost(std::vector<TcTile>& tt) {
+    std::vector<uint32_t> order(tt.size());
+    for (size_t i = 0; i < order.size(); ++i) order[i] = (uint32_t)i;
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return tt[a].nk * tt[a].nsub > tt[b].nk * tt[b].nsub; });
+    std::vector<TcTile> sorted(tt.size());
+    for (size_t i = 0; i < order.size(); ++i) sorted[i] = tt[order[i]];
+    tt.swap(sorted);
+}
+
 static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
     auto it = g.cache.find(nb);
     if (it != g.cache.end()) { *out = &it->second; return SRN_OK; }
@@ -1279,7 +1290,7 @@ static int plan_for(srn_engine* h, Group& g, int nb, Cached** out) {
                             for (int t = pre[i]; t < pre[i + 1]; ++t) tt[t].tm = dm + first[i];
                 }
             }
-            std::stable_sort(tt.begin(), tt.end(), [](const TcTile& a, const TcTile& b) { return a.nk * a.nsub > b.nk * b.nsub; });
+            sort_tiles_by_cost(tt);
             TcTile* dt = nullptr;
             POOL_ALLOC(dt, TcTile, tt.size() * sizeof(TcTile));
             CK(cudaMemcpy(dt, tt.data(), tt.size() * sizeof(TcTile), cudaMemcpyHostToDevice));
@@ -1497,7 +1508,7 @@ static int forward_pass(srn_engine* h, int nb, const Inputs& I, bool training, i
                         for (SplitFin f : c->host_fin) { f.blk0 += fin_blocks; fins.push_back(f); }
                         fin_blocks += c->fin_blocks;
                     }
-                    std::stable_sort(all.begin(), all.end(), [](const TcTile& x, const TcTile& y) { return x.nk * x.nsub > y.nk * y.nsub; });
+                    sort_tiles_by_cost(all);
                     if (getenv("SRN_DUMP_FWD")) {      // debug: what a merged forward launch holds
                         const int BNd = TC_BN[b], G = tc_grid(h, (int)all.size(), BNd);
                         long long sum = 0, mx = 0, nsplit_tiles = 0; std::vector<long long> load((size_t)std::max(G, 1), 0);
@@ -1792,7 +1803,9 @@ extern "C" int srn_fit(srn_engine* h, int32_t epochs, int32_t batch, int32_t n_v
     wait_adam(h);
     CK(cudaMemsetAsync(h->Gr, 0, (size_t)h->p_elems * sizeof(float), h->stream));
     // warm the launch plans outside the timed region
+    const auto tp0 = std::chrono::steady_clock::now();
     for (auto& g : h->groups) { Cached* c; rc = plan_for(h, g, batch, &c); if (rc) return rc; }
+    const double plan_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - tp0).count();
     for (int e = 0; e < epochs && !stop; ++e) {
         CK(cudaEventRecord(ev0, h->stream));
         for (int s = 0; s < S; ++s) {
@@ -1836,7 +1849,7 @@ extern "C" int srn_fit(srn_engine* h, int32_t epochs, int32_t batch, int32_t n_v
     if (val_mse_sum && vn) CK(cudaMemcpy(val_mse_sum, h->met_mse + tn, vn * sizeof(float), cudaMemcpyDeviceToHost));
     if (device_ms) *device_ms = ms_total;
     if (getenv("SRN_HOST_TIMING"))
-        fprintf(stderr, "srn_fit: %d steps, device %.3f ms, host enqueue %.3f ms\n", max_steps > 0 ? steps_done : epochs * S, ms_total, 1e3 * host_enqueue_s);
+        fprintf(stderr, "srn_fit: %d steps, device %.3f ms, host enqueue %.3f ms, launch plans %.3f ms\n", max_steps > 0 ? steps_done : epochs * S, ms_total, 1e3 * host_enqueue_s, 1e3 * plan_s);
     return SRN_OK;
 }
 
