@@ -24,6 +24,9 @@ from memory, to be re-checked against the named file when an install exists):
                         of a softmax Activation), nn_ops.softmax_cross_entropy_with_logits_v2 (fp16 logits are cast to
                         fp32, cost cast back), keras/losses.py mean_squared_error, math_grad._SquaredDifferenceGrad,
                         SigmoidGrad, keras/utils/losses_utils.py sum_over_batch_size
+  conv_like_forward     common/logic.py:17-35 (Keras layers as built); [TF2.6] conv_ops / matmul_op (fp32 accumulation, one
+                        rounding), bias_op, ReluGrad / SigmoidGrad (activation_backward)
+  maxpool_forward/bwd   [TF2.6] maxpooling_op (first maximum of a window receives the gradient - tie rule unverified)
   F16Mean / accuracy    experiment_worker.py:169-195,280; [TF2.6] keras/metrics.py Mean with floatx variables,
                         categorical_accuracy = argmax(y_true) == argmax(y_pred) on the fp16 softmax output
 """
@@ -208,3 +211,92 @@ class F16Mean:
     def result(self) -> float:
         with np.errstate(all='ignore'):
             return float(H(self.total / self.count)) if self.count != 0 else 0.0
+
+
+# --------------------------------------------------------------------------- Dense / Conv1D / Conv2D and max pooling
+# experiment_worker.py builds the layers with Keras defaults: 'valid' padding, channels last, kernels in HWIO layout
+# (Conv1D: (k, in, out)), Dense on the last axis.  [TF2.6] one rounding per op: contraction (fp32 accumulation) -> fp16,
+# BiasAdd -> fp16, activation -> fp16.  The contraction is an explicit im2col + matmul here (torch's conv2d in the other
+# restatement), so the two agree up to the fp32 summation order: equal after the fp16 rounding except for rare last-bit ties.
+
+def conv_like_forward(x16: np.ndarray, w16: np.ndarray, b16: np.ndarray, kernel=(1, 1), strides=(1, 1), act: str = 'linear'):
+    """x16 (B, H, W, C) [Conv1D: (B, W, C), Dense: (B, ..., C)], w16 Keras layout, returns (z, y): pre-activation and output."""
+    x = np.asarray(x16, dtype=H)
+    kh, kw = kernel
+    sh, sw = strides
+    if kh == 1 and kw == 1 and w16.ndim == 2:                      # Dense on the last axis
+        acc = x.astype(F).reshape(-1, x.shape[-1]) @ np.asarray(w16, dtype=H).astype(F)
+        z = acc.astype(H).reshape(x.shape[:-1] + (w16.shape[-1],))
+    else:
+        one_d = x.ndim == 3
+        x4 = x[:, None] if one_d else x
+        B, Hh, Ww, C = x4.shape
+        w4 = np.asarray(w16, dtype=H).reshape(kh, kw, C, -1)
+        Ho, Wo = (Hh - kh) // sh + 1, (Ww - kw) // sw + 1
+        cols = np.empty((B, Ho, Wo, kh, kw, C), dtype=F)
+        for i in range(kh):
+            for j in range(kw):
+                cols[:, :, :, i, j, :] = x4[:, i:i + (Ho - 1) * sh + 1:sh, j:j + (Wo - 1) * sw + 1:sw, :].astype(F)
+        acc = cols.reshape(B * Ho * Wo, kh * kw * C) @ w4.astype(F).reshape(kh * kw * C, -1)
+        z = acc.astype(H).reshape(B, Ho, Wo, -1)
+        if one_d:
+            z = z[:, 0]
+    z = (z + np.asarray(b16, dtype=H)).astype(H)                   # BiasAdd, one fp16 op
+    if act == 'relu':
+        y = np.where(np.isnan(z), z, np.maximum(z, H(0))).astype(H)
+    elif act == 'sigmoid':
+        y = sigmoid16(z)
+    else:
+        y = z
+    return z, y
+
+
+def activation_backward(dy16: np.ndarray, y16: np.ndarray, act: str) -> np.ndarray:
+    """[TF2.6] ReluGrad: dy where y > 0; SigmoidGrad: dy * y * (1 - y), each product one fp16 op."""
+    dy, y = np.asarray(dy16, dtype=H), np.asarray(y16, dtype=H)
+    if act == 'relu':
+        return np.where(y > H(0), dy, H(0)).astype(H)
+    if act == 'sigmoid':
+        return ((dy * y).astype(H) * (ONE - y).astype(H)).astype(H)
+    return dy
+
+
+def maxpool_forward(x16: np.ndarray, pool=(2, 2), strides=(2, 2)):
+    """(B, H, W, C) -> (y, arg): the FIRST maximum of a window in row-major scan order wins; NaN beats a number."""
+    x = np.asarray(x16, dtype=H)
+    B, Hh, Ww, C = x.shape
+    ph, pw = pool
+    sh, sw = strides
+    Ho, Wo = (Hh - ph) // sh + 1, (Ww - pw) // sw + 1
+    y = np.empty((B, Ho, Wo, C), dtype=H)
+    arg = np.zeros((B, Ho, Wo, C), dtype=np.int64)
+    for b in range(B):
+        for ho in range(Ho):
+            for wo in range(Wo):
+                for c in range(C):
+                    best, at = H(-np.inf), 0
+                    for i in range(ph):
+                        for j in range(pw):
+                            v = x[b, ho * sh + i, wo * sw + j, c]
+                            if v > best or (np.isnan(v) and not np.isnan(best)):
+                                best, at = v, i * pw + j
+                    y[b, ho, wo, c] = best
+                    arg[b, ho, wo, c] = at
+    return y, arg
+
+
+def maxpool_backward(dy16: np.ndarray, arg: np.ndarray, in_shape, pool=(2, 2), strides=(2, 2)) -> np.ndarray:
+    """The gradient of a window goes to its first maximum; overlapping windows add in window scan order (fp32, rounded once)."""
+    dy = np.asarray(dy16, dtype=H)
+    B, Hh, Ww, C = in_shape
+    ph, pw = pool
+    sh, sw = strides
+    dx = np.zeros(in_shape, dtype=F)
+    for i in range(ph):
+        for j in range(pw):
+            for b in range(B):
+                for ho in range(dy.shape[1]):
+                    for wo in range(dy.shape[2]):
+                        sel = arg[b, ho, wo] == i * pw + j
+                        dx[b, ho * sh + i, wo * sw + j] += np.where(sel, dy[b, ho, wo].astype(F), F(0))
+    return dx.astype(H)

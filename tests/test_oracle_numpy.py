@@ -189,3 +189,63 @@ def test_centred_bn_backward_is_the_accurate_one_on_ill_conditioned_channels():
     assert (err_x(dx_c) < 1e-5).all() and (err_g(dg_c) < 1e-5).all()
     assert (err_x(dx_g)[3:] < 1e-3).all() and (err_g(dg_g)[3:] < 5e-3).all()         # well conditioned: the forms agree
     assert (err_g(dg_g)[:3] > 0.05).all() and (err_x(dx_g)[:3] > 1e-3).all()          # ill conditioned: the graph form is noise
+
+
+# --------------------------------------------------------------------------- Dense / Conv1D / Conv2D, pooling
+def _layer(kind, units, kernel=(1, 1), strides=(1, 1), act=0, out_shape=None):
+    from types import SimpleNamespace
+    return SimpleNamespace(kind=kind, units=units, kernel=kernel, strides=strides, act=act, out_shape=out_shape)
+
+
+@pytest.mark.parametrize('case', [
+    dict(x=(4, 9, 8, 5), kernel=(3, 3), strides=(1, 1), units=7, act='relu'),        # Conv2D
+    dict(x=(3, 12, 10, 8), kernel=(5, 4), strides=(2, 3), units=6, act='linear'),    # strided, non-square window
+    dict(x=(5, 40, 3), kernel=(1, 7), strides=(1, 2), units=4, act='sigmoid'),       # Conv1D = 1 x k convolution
+    dict(x=(6, 17), kernel=(1, 1), strides=(1, 1), units=9, act='relu'),             # Dense
+    dict(x=(2, 11, 6), kernel=(1, 1), strides=(1, 1), units=5, act='linear'),        # Dense on the last axis of a 3-D tensor
+])
+def test_conv_like_forward_and_activation_grad(case):
+    """Kernel layouts (HWIO, Conv1D as H = 1), strides and the three roundings of a layer, through im2col + matmul in NumPy
+    against torch's conv2d in the other restatement: equal except for rare last-bit ties of the fp32 summation order."""
+    from serann_b200.frontend import KIND_CONV, KIND_DENSE, ACT_NONE, ACT_RELU, ACT_SIGMOID
+    r = np.random.default_rng(11)
+    x = r.standard_normal(case['x']).astype(H)
+    kh, kw = case['kernel']
+    cin = case['x'][-1]
+    dense = kh * kw == 1
+    wshape = (cin, case['units']) if dense else ((kw, cin, case['units']) if len(case['x']) == 3 else (kh, kw, cin, case['units']))
+    w = (0.3 * r.standard_normal(wshape)).astype(H)
+    b = (0.1 * r.standard_normal(case['units'])).astype(H)
+    z, y = N.conv_like_forward(x, w, b, case['kernel'], case['strides'], case['act'])
+    act = {'linear': ACT_NONE, 'relu': ACT_RELU, 'sigmoid': ACT_SIGMOID}[case['act']]
+    l = _layer(KIND_DENSE if dense else KIND_CONV, case['units'], case['kernel'], case['strides'], act, out_shape=y.shape[1:])
+    xt = _t(x).requires_grad_(True)
+    yo = O._conv_like(l, xt, _t(w), _t(b))
+    d = ulps(y, yo.detach().numpy())
+    assert y.shape == tuple(yo.shape)
+    assert d.max() <= 1 and (d > 0).mean() < 2e-3, (d.max(), (d > 0).mean())
+    # gradient of the activation alone (ReluGrad / SigmoidGrad), on the torch side through autograd of the same node
+    g = r.standard_normal(y.shape).astype(H)
+    zt = _t(z).requires_grad_(True)
+    yt = torch.relu(zt) if case['act'] == 'relu' else (O.sigmoid_q(zt) if case['act'] == 'sigmoid' else zt * 1.0)
+    yt.backward(_t(g))
+    want = O.f16(zt.grad).numpy()
+    got = N.activation_backward(g, yt.detach().numpy().astype(H), case['act']).astype(np.float32)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize('pool,strides', [((2, 2), (2, 2)), ((2, 3), (2, 2)), ((3, 3), (1, 1))])
+def test_maxpool_first_maximum_rule_bit_equal(pool, strides):
+    """Ties go to the first element of the window in scan order, NaN beats a number, overlapping windows add in window order."""
+    r = np.random.default_rng(5)
+    x = np.round(r.standard_normal((2, 9, 8, 3)) * 2).astype(H) / H(2)          # many exact ties
+    x[0, 0, 0, 0] = np.nan
+    x[1, 4, 4, 2] = np.nan
+    y, arg = N.maxpool_forward(x, pool, strides)
+    xt = _t(x).requires_grad_(True)
+    yt = O._MaxPoolFirst.apply(xt, pool[0], pool[1], strides[0], strides[1])
+    assert np.array_equal(y.astype(np.float32), yt.detach().numpy(), equal_nan=True)
+    g = r.standard_normal(y.shape).astype(H)
+    yt.backward(_t(g))
+    dx = N.maxpool_backward(g, arg, x.shape, pool, strides)
+    assert np.array_equal(dx.astype(np.float32), O.f16(xt.grad).numpy(), equal_nan=True)
