@@ -15,8 +15,9 @@
 //   warps 0-7  loaders: gather k-block p into ring stage p % S with cp.async, 4 rows x 8 chunks per warp-wide copy
 //              (a quarter warp reads 128 contiguous bytes of one row: one L1 wavefront per line); each thread's
 //              copies arrive on the stage's "full" barrier by themselves when they land (cp.async.mbarrier.arrive.noinc);
-//   warp 8     one thread waits "full", issues up to four K=16 tcgen05.mma into one of two TMEM accumulators and
-//              commits to the stage's "empty" barrier (and to "tmem_full" after a tile's last k-block);
+//   warp 8     MMA issuer: the converged warp waits "full", one lane elected by elect.sync issues up to four K=16
+//              tcgen05.mma into one of the TMEM accumulators and commits to the stage's "empty" barrier (and to
+//              "tmem_full" after a tile's last k-block);
 //   warps 9-12 epilogue: wait "tmem_full", read the accumulator with tcgen05.ld (warp w owns TMEM lanes
 //              32 (w % 4) ..), apply bias / activation / gradient stores, arrive on "tmem_empty".
 // Loads, MMAs and epilogues of neighbouring tiles therefore overlap; nothing in the loop is a CTA-wide barrier.
